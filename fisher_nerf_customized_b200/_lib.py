@@ -1,0 +1,88 @@
+"""ctypes binding of include/fisher_b200.h.  There is NO fallback: if the CUDA library is missing
+every operator raises (the product path never routes through oracle/ or a CPU implementation)."""
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libfisher_b200.so")
+
+FB_OK, FB_E_INVALID, FB_E_WORKSPACE, FB_E_CUDA, FB_E_CAPACITY, FB_E_PREFILTERED = 0, -1, -2, -3, -4, -5
+
+
+class fb_camera(C.Structure):
+    _fields_ = [("image_width", C.c_int), ("image_height", C.c_int), ("tanfovx", C.c_float), ("tanfovy", C.c_float),
+                ("scale_modifier", C.c_float), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int), ("prefiltered", C.c_int),
+                ("bg", C.c_float * 3), ("campos", C.c_float * 3), ("viewmatrix", C.c_float * 16),
+                ("projmatrix", C.c_float * 16)]
+
+
+class fb_gaussians(C.Structure):
+    _fields_ = [("P", C.c_int), ("means3D", C.c_void_p), ("opacities", C.c_void_p), ("shs", C.c_void_p),
+                ("colors_precomp", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+                ("cov3D_precomp", C.c_void_p)]
+
+
+class fb_map(C.Structure):
+    _fields_ = [("P", C.c_int), ("means3D", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+                ("rotations", C.c_void_p), ("colors", C.c_void_p)]
+
+
+# name -> (restype, argtypes); the single source of truth for tests/test_abi.py as well.
+vp, sz, ci, ll, cf = C.c_void_p, C.c_size_t, C.c_int, C.c_longlong, C.c_float
+SIGNATURES = {
+    "fb_error_string": (C.c_char_p, [ci]),
+    "fb_last_cuda_error": (ci, []),
+    "fb_version": (ci, []),
+    "fb_geom_bytes": (sz, [ci]),
+    "fb_image_bytes": (sz, [ci, ci]),
+    "fb_inst_bytes": (sz, [ci]),
+    "fb_forward_scratch_bytes": (sz, [ci, ci, ci, ci]),
+    "fb_backward_scratch_bytes": (sz, [ci, ci, ci, ci]),
+    "fb_raster_forward_bin": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, sz, vp, sz, vp, sz, vp,
+                                   C.POINTER(ci), vp]),
+    "fb_raster_forward_render": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, sz, vp, sz, vp, sz, vp, sz,
+                                      ci, vp, vp, vp]),
+    "fb_raster_backward": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, vp, sz, vp, sz, vp, sz, vp, sz, ci,
+                                vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "fb_mark_visible": (ci, [ci, vp, C.POINTER(cf), C.POINTER(cf), vp, vp]),
+    "fb_debug_export": (ci, [C.POINTER(fb_camera), ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "fb_score_workspace_bytes": (sz, [ci, ci, ci, ci, ll]),
+    "fb_score_candidates": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
+    "fb_accumulate_hessian": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
+    "fb_knn_workspace_bytes": (sz, [ci]),
+    "fb_dist2_knn3": (ci, [ci, vp, vp, vp, sz, vp]),
+    "fb_count_visible": (ci, [ci, vp, ci, vp, vp, ci, ci, vp, vp, vp]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library once; raise loudly if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m fisher_nerf_customized_b200.build` "
+                "(there is no CPU fallback)")
+        h = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = h
+    return _lib
+
+
+class FisherB200Error(RuntimeError):
+    pass
+
+
+def check(status, what=""):
+    if status == FB_OK:
+        return
+    L = lib()
+    msg = L.fb_error_string(status).decode()
+    if status == FB_E_CUDA:
+        msg += f" (cudaError {L.fb_last_cuda_error()})"
+    raise FisherB200Error(f"{what}: {msg}" if what else msg)

@@ -1,0 +1,196 @@
+// fb_api.cu -- the C ABI (include/fisher_b200.h) over the sm_100a kernels.  No torch types here.
+#include "fb_score.cuh"
+#include "fb_backward.cuh"
+#include "fb_stage5.cuh"
+#include <limits.h>
+#include <string.h>
+
+using namespace fb;
+
+static thread_local int g_last_cuda = 0;
+#define FB_CUDA(call)                                                   \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) { g_last_cuda = (int)e__; return FB_E_CUDA; } \
+    } while (0)
+#define FB_LAUNCH_CHECK() FB_CUDA(cudaGetLastError())
+
+extern "C" {
+
+const char* fb_error_string(int s) {
+    switch (s) {
+        case FB_OK: return "ok";
+        case FB_E_INVALID: return "invalid argument";
+        case FB_E_WORKSPACE: return "workspace too small";
+        case FB_E_CUDA: return "CUDA error";
+        case FB_E_CAPACITY: return "instance capacity exceeded";
+        case FB_E_PREFILTERED: return "Point is filtered although prefiltered is set";
+        default: return "unknown";
+    }
+}
+int fb_last_cuda_error(void) { return g_last_cuda; }
+int fb_version(void) { return 100; }
+
+size_t fb_geom_bytes(int P) { return geom_layout(P).total; }
+size_t fb_image_bytes(int w, int h) { return image_layout(w, h).total; }
+size_t fb_inst_bytes(int R) { return align_up((size_t)(R > 0 ? R : 1) * 8, 256); }
+size_t fb_forward_scratch_bytes(int, int, int, int) { return 256; }
+size_t fb_backward_scratch_bytes(int P, int, int, int) { return align_up((size_t)(P > 0 ? P : 1) * FB_NACC * 4, 256); }
+
+}  // extern "C"
+
+static int check_gauss(const fb_gaussians* g) {
+    if (!g || g->P < 0) return FB_E_INVALID;
+    if (g->P == 0) return FB_OK;
+    if (!g->means3D || !g->opacities) return FB_E_INVALID;
+    if ((g->shs == nullptr) == (g->colors_precomp == nullptr)) return FB_E_INVALID;
+    const bool sr = g->scales != nullptr && g->rotations != nullptr;
+    if (sr == (g->cov3D_precomp != nullptr)) return FB_E_INVALID;
+    if (!sr && (g->scales || g->rotations)) return FB_E_INVALID;
+    return FB_OK;
+}
+static GaussIn to_in(const fb_gaussians* g) {
+    GaussIn i;
+    i.means3D = g->means3D; i.opacities = g->opacities; i.shs = g->shs; i.colors = g->colors_precomp;
+    i.scales = g->scales; i.rotations = g->rotations; i.cov3D = g->cov3D_precomp;
+    return i;
+}
+static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* inst, long long cap) {
+    GeomLayout GL = geom_layout(P);
+    ImageLayout IL = image_layout(cam.W, cam.H);
+    char* gb = (char*)geom; char* ib = (char*)image;
+    Bins b;
+    b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr;
+    b.vis_list = (uint32_t*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
+    b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
+    b.total = (uint32_t*)(ib + IL.totals);
+    b.keys = (u64*)inst; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
+    return b;
+}
+
+#define FB_SORT_SMEM_KEYS 8192
+
+extern "C" {
+
+int fb_raster_forward_bin(const fb_camera* c, const fb_gaussians* g, void* geom, size_t geom_bytes, void* image,
+                          size_t image_bytes, void* scratch, size_t scratch_bytes, int* radii, int* num_rendered_host,
+                          void* stream_) {
+    (void)scratch; (void)scratch_bytes;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || !num_rendered_host || c->image_width <= 0 || c->image_height <= 0) return FB_E_INVALID;
+    int rc = check_gauss(g);
+    if (rc) return rc;
+    *num_rendered_host = 0;
+    const int P = g->P;
+    if (P == 0) return FB_OK;
+    if (!geom || !image || !radii) return FB_E_INVALID;
+    if (g->shs && (c->sh_coeffs <= 0 || c->sh_degree < 0 || c->sh_degree > 3 ||
+                   (c->sh_degree + 1) * (c->sh_degree + 1) > c->sh_coeffs)) return FB_E_INVALID;
+    if (geom_bytes < fb_geom_bytes(P) || image_bytes < fb_image_bytes(c->image_width, c->image_height)) return FB_E_WORKSPACE;
+    Cam cam = make_cam(c);
+    Bins b = single_bins(P, cam, geom, image, nullptr, LLONG_MAX);
+    GeomLayout GL = geom_layout(P);
+    FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 256, st));
+    FB_CUDA(cudaMemsetAsync(b.tile_count, 0, (size_t)b.tiles * 4, st));
+    FB_CUDA(cudaMemsetAsync(b.total, 0, 256, st));
+    k_preprocess<false, 0><<<(P + 255) / 256, 256, 0, st>>>(to_in(g), cam, nullptr, b, radii,
+                                                           (float*)((char*)geom + GL.rgb), (bool*)((char*)geom + GL.clamped), nullptr);
+    FB_LAUNCH_CHECK();
+    k_scan_tiles<<<1, 1024, 0, st>>>(b);
+    FB_LAUNCH_CHECK();
+    uint32_t tot[4];
+    FB_CUDA(cudaMemcpyAsync(tot, b.total, sizeof(tot), cudaMemcpyDeviceToHost, st));
+    FB_CUDA(cudaStreamSynchronize(st));   // the reference syncs here too (rasterizer_impl.cu:282)
+    if (tot[2]) return FB_E_PREFILTERED;
+    *num_rendered_host = (int)tot[0];
+    return FB_OK;
+}
+
+int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* geom, size_t geom_bytes, void* image,
+                             size_t image_bytes, void* inst, size_t inst_bytes, void* scratch, size_t scratch_bytes,
+                             int num_rendered, float* out_color, float* out_depth, void* stream_) {
+    (void)scratch; (void)scratch_bytes; (void)geom_bytes; (void)image_bytes;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || !g || !out_color || !out_depth || num_rendered < 0) return FB_E_INVALID;
+    const int P = g->P;
+    if (P == 0) return FB_OK;
+    if (!geom || !image || !inst) return FB_E_INVALID;
+    if (inst_bytes < fb_inst_bytes(num_rendered)) return FB_E_WORKSPACE;
+    Cam cam = make_cam(c);
+    Bins b = single_bins(P, cam, geom, image, inst, (long long)num_rendered);
+    GeomLayout GL = geom_layout(P);
+    ImageLayout IL = image_layout(cam.W, cam.H);
+    if (num_rendered > 0) {
+        int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
+        k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam);
+        FB_LAUNCH_CHECK();
+        static bool attr_set = false;
+        if (!attr_set) {
+            FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_KEYS * 8));
+            attr_set = true;
+        }
+        k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS);
+        FB_LAUNCH_CHECK();
+    }
+    const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);
+    k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
+        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth);
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* radii, const void* geom, size_t geom_bytes,
+                       const void* image, size_t image_bytes, const void* inst, size_t inst_bytes, void* scratch,
+                       size_t scratch_bytes, int num_rendered, const float* dL_dpix, int power, float* dL_dmeans2D,
+                       float* dL_dconic, float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D,
+                       float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream_) {
+    (void)geom_bytes; (void)image_bytes; (void)inst_bytes; (void)dL_dsh;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || !dL_dpix) return FB_E_INVALID;
+    int rc = check_gauss(g);
+    if (rc) return rc;
+    const int P = g->P;
+    if (P == 0 || num_rendered == 0) return FB_OK;
+    if (!geom || !image || !inst || !radii || !scratch) return FB_E_INVALID;
+    if (power != 1 && power != 2) return FB_E_INVALID;              // see DESIGN.md: other powers unsupported
+    if (g->shs && c->sh_degree > 0) return FB_E_INVALID;            // SH backward (degree>0) unsupported, DESIGN.md
+    if (scratch_bytes < fb_backward_scratch_bytes(P, num_rendered, power, 0)) return FB_E_WORKSPACE;
+    Cam cam = make_cam(c);
+    Bins b = single_bins(P, cam, (void*)geom, (void*)image, (void*)inst, (long long)num_rendered);
+    GeomLayout GL = geom_layout(P);
+    ImageLayout IL = image_layout(cam.W, cam.H);
+    float* mom = (float*)scratch;
+    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
+    const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((const char*)geom + GL.rgb);
+    const float* fT = (const float*)((const char*)image + IL.final_T);
+    const uint32_t* nc = (const uint32_t*)((const char*)image + IL.n_contrib);
+    dim3 grid(cam.tiles_x, cam.tiles_y);
+    GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations};
+    if (power == 2) {
+        k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom);
+        FB_LAUNCH_CHECK();
+        k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o);
+    } else {
+        k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom);
+        FB_LAUNCH_CHECK();
+        k_expand_grads<false><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o);
+    }
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+int fb_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                    void* stream_) {
+    if (P < 0 || !viewmatrix || !projmatrix) return FB_E_INVALID;
+    if (P == 0) return FB_OK;
+    if (!means3D || !present) return FB_E_INVALID;
+    Cam cam; memset(&cam, 0, sizeof(cam));
+    for (int i = 0; i < 16; ++i) { cam.view[i] = viewmatrix[i]; cam.proj[i] = projmatrix[i]; }
+    k_mark_visible<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, cam, present);
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+}  // extern "C"
+
+#include "fb_api_batched.inl"

@@ -1,0 +1,283 @@
+// fb_api_batched.inl -- debug export, batched scoring / H_train entry points, stage 5 entry points.
+// Included by fb_api.cu.
+
+namespace fb {
+
+__global__ void k_debug_geom(int P, Cam cam, const GRec* recs, const int* radii_or_null, const uint32_t* vis_list,
+                             uint32_t nvis_cap, const uint32_t* vis_count, uint32_t* tiles_touched, float* depths,
+                             float* means2D, float* conic_opacity) {
+    // Gaussians that are not visible keep zeros (outputs are pre-zeroed by the host wrapper).
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    (void)radii_or_null; (void)nvis_cap;
+    if (i >= vis_count[0]) return;
+    unsigned gid = vis_list[i];
+    if ((int)gid >= P) return;
+    GRec r = recs[gid];
+    int x0, y0, x1, y1;
+    tile_rect(r.a.x, r.a.y, __float_as_int(r.b.w), cam.tiles_x, cam.tiles_y, x0, y0, x1, y1);
+    if (tiles_touched) tiles_touched[gid] = (uint32_t)((x1 - x0) * (y1 - y0));
+    if (depths) depths[gid] = r.a.z;
+    if (means2D) { means2D[2 * gid] = r.a.x; means2D[2 * gid + 1] = r.a.y; }
+    if (conic_opacity) {
+        conic_opacity[4 * gid] = r.b.x; conic_opacity[4 * gid + 1] = r.b.y;
+        conic_opacity[4 * gid + 2] = r.b.z; conic_opacity[4 * gid + 3] = r.a.w;
+    }
+}
+__global__ void k_debug_inst(Bins b, uint32_t* point_list, u64* point_keys) {
+    const int t = blockIdx.x;
+    uint2 r = b.tile_range[t];
+    for (unsigned i = r.x + threadIdx.x; i < r.y; i += blockDim.x) {
+        u64 k = b.keys[i];
+        if (point_list) point_list[i] = (uint32_t)(k & 0xffffffffull);
+        if (point_keys) point_keys[i] = ((u64)t << 32) | (k >> 32);
+    }
+}
+
+__global__ void k_status_update(const uint32_t* total, int* status) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        if (total[1]) status[0] = FB_E_CAPACITY;
+        if ((int)total[0] > status[1]) status[1] = (int)total[0];
+        if ((int)total[3] > status[2]) status[2] = (int)total[3];
+    }
+}
+__global__ void k_fill(float* p, size_t n, float v) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+struct ScoreLayout {
+    size_t recs, recsB, vis_list, vis_count, tile_count, tile_range, totals, partial, final_T, n_contrib, color, depth,
+        dpix, keys, total;
+};
+static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
+    ScoreLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1), Vv = (size_t)(V > 0 ? V : 1);
+    size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y), HW = (size_t)W * H;
+    L.recs = o;       o = align_up(o + Vv * Pp * sizeof(GRec), 256);
+    L.recsB = o;      o = align_up(o + Vv * Pp * 64, 256);
+    L.vis_list = o;   o = align_up(o + Vv * Pp * 4, 256);
+    L.vis_count = o;  o = align_up(o + Vv * 4, 256);
+    L.tile_count = o; o = align_up(o + Vv * tiles * 4, 256);
+    L.tile_range = o; o = align_up(o + Vv * tiles * 8, 256);
+    L.totals = o;     o = align_up(o + 256, 256);
+    L.partial = o;    o = align_up(o + Vv * tiles * 4, 256);
+    L.final_T = o;    o = align_up(o + HW * 4, 256);
+    L.n_contrib = o;  o = align_up(o + HW * 4, 256);
+    L.color = o;      o = align_up(o + HW * 12, 256);
+    L.depth = o;      o = align_up(o + HW * 4, 256);
+    L.dpix = o;       o = align_up(o + HW * 12, 256);
+    L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.total = o;
+    return L;
+}
+static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& cam, long long cap) {
+    Bins b;
+    b.recs = (GRec*)(ws + L.recs); b.recsB = (float4*)(ws + L.recsB);
+    b.vis_list = (uint32_t*)(ws + L.vis_list); b.vis_count = (uint32_t*)(ws + L.vis_count);
+    b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
+    b.total = (uint32_t*)(ws + L.totals); b.keys = (u64*)(ws + L.keys);
+    b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
+    return b;
+}
+static GaussIn map_in(const fb_map* m) {
+    GaussIn i;
+    i.means3D = m->means3D; i.opacities = m->opacities; i.shs = nullptr; i.colors = m->colors;
+    i.scales = m->scales; i.rotations = m->rotations; i.cov3D = nullptr;
+    return i;
+}
+
+#define FB_SCORE_SMEM_KEYS 4096
+static size_t score_smem_bytes() { return (size_t)FB_SCORE_SMEM_KEYS * 8 + sizeof(ScoreBatch) + 8 * 4 + 16; }
+
+}  // namespace fb
+
+extern "C" {
+
+int fb_debug_export(const fb_camera* c, int P, int num_rendered, const void* geom, const void* image, const void* inst,
+                    uint32_t* tiles_touched, float* depths, float* means2D, float* conic_opacity, uint32_t* ranges,
+                    float* final_T, uint32_t* n_contrib, uint32_t* point_list, uint64_t* point_keys, void* stream_) {
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || P <= 0 || !geom || !image) return FB_E_INVALID;
+    Cam cam = make_cam(c);
+    Bins b = single_bins(P, cam, (void*)geom, (void*)image, (void*)inst, (long long)num_rendered);
+    ImageLayout IL = image_layout(cam.W, cam.H);
+    size_t HW = (size_t)cam.W * cam.H;
+    if (tiles_touched) FB_CUDA(cudaMemsetAsync(tiles_touched, 0, (size_t)P * 4, st));
+    if (depths) FB_CUDA(cudaMemsetAsync(depths, 0, (size_t)P * 4, st));
+    if (means2D) FB_CUDA(cudaMemsetAsync(means2D, 0, (size_t)P * 8, st));
+    if (conic_opacity) FB_CUDA(cudaMemsetAsync(conic_opacity, 0, (size_t)P * 16, st));
+    k_debug_geom<<<(P + 255) / 256, 256, 0, st>>>(P, cam, b.recs, nullptr, b.vis_list, (uint32_t)P, b.vis_count,
+                                                  tiles_touched, depths, means2D, conic_opacity);
+    FB_LAUNCH_CHECK();
+    if (ranges) FB_CUDA(cudaMemcpyAsync(ranges, b.tile_range, (size_t)b.tiles * 8, cudaMemcpyDeviceToDevice, st));
+    if (final_T) FB_CUDA(cudaMemcpyAsync(final_T, (const char*)image + IL.final_T, HW * 4, cudaMemcpyDeviceToDevice, st));
+    if (n_contrib) FB_CUDA(cudaMemcpyAsync(n_contrib, (const char*)image + IL.n_contrib, HW * 4, cudaMemcpyDeviceToDevice, st));
+    if ((point_list || point_keys) && inst && num_rendered > 0) {
+        k_debug_inst<<<b.tiles, 256, 0, st>>>(b, point_list, (u64*)point_keys);
+        FB_LAUNCH_CHECK();
+    }
+    return FB_OK;
+}
+
+size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk, long long inst_capacity) {
+    return score_layout(P, width, height, views_per_chunk, inst_capacity).total;
+}
+
+int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c, int K, const float* weight, int C_H,
+                        float grad_scale, float* scores, int* status_dev, void* workspace, size_t workspace_bytes,
+                        int views_per_chunk, long long inst_capacity, void* stream_) {
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
+        inst_capacity <= 0 || !status_dev) return FB_E_INVALID;
+    if (K == 0) return FB_OK;
+    const int P = map->P;
+    if (P <= 0 || !map->means3D || !map->opacities || !map->scales || !map->rotations || !map->colors || !w2c ||
+        !weight || !scores || !workspace) return FB_E_INVALID;
+    Cam cam = make_cam(c);
+    const int V = views_per_chunk;
+    ScoreLayout L = score_layout(P, cam.W, cam.H, V, inst_capacity);
+    if (workspace_bytes < L.total) return FB_E_WORKSPACE;
+    char* ws = (char*)workspace;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes()));
+        attr_set = true;
+    }
+    FB_CUDA(cudaMemsetAsync(status_dev, 0, 3 * sizeof(int), st));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4, st));
+    GaussIn gi = map_in(map);
+    for (int k0 = 0; k0 < K; k0 += V) {
+        const int Vc = (K - k0 < V) ? (K - k0) : V;
+        Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
+        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
+        const float* w2c_k = w2c + (size_t)k0 * 16;
+        if (C_H == 4)
+            k_preprocess<true, 4><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight);
+        else
+            k_preprocess<true, 11><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight);
+        FB_LAUNCH_CHECK();
+        k_scan_tiles<<<1, 1024, 0, st>>>(b);
+        FB_LAUNCH_CHECK();
+        k_status_update<<<1, 32, 0, st>>>(b.total, status_dev);
+        int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
+        k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam);
+        FB_LAUNCH_CHECK();
+        k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, score_smem_bytes(), st>>>(b, cam, grad_scale, FB_SCORE_SMEM_KEYS,
+                                                                                (float*)(ws + L.partial));
+        FB_LAUNCH_CHECK();
+        k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0);
+        FB_LAUNCH_CHECK();
+    }
+    return FB_OK;
+}
+
+int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2c, int K, int C_H, float grad_scale,
+                          float* H_out, int* status_dev, void* workspace, size_t workspace_bytes, int views_per_chunk,
+                          long long inst_capacity, void* stream_) {
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || inst_capacity <= 0 || !status_dev)
+        return FB_E_INVALID;
+    if (K == 0) return FB_OK;
+    const int P = map->P;
+    if (P <= 0 || !map->means3D || !map->opacities || !map->scales || !map->rotations || !map->colors || !w2c ||
+        !H_out || !workspace) return FB_E_INVALID;
+    Cam cam = make_cam(c);
+    ScoreLayout L = score_layout(P, cam.W, cam.H, views_per_chunk, inst_capacity);
+    if (workspace_bytes < L.total) return FB_E_WORKSPACE;
+    char* ws = (char*)workspace;
+    static bool attr_set = false;
+    if (!attr_set) {
+        FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_KEYS * 8));
+        attr_set = true;
+    }
+    const size_t HW = (size_t)cam.W * cam.H;
+    float* mom = (float*)(ws + L.recsB);   // P x 16 floats == one view's worth of the scoring-record region
+    float* dpix = (float*)(ws + L.dpix);
+    FB_CUDA(cudaMemsetAsync(status_dev, 0, 3 * sizeof(int), st));
+    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)cam.tiles_x * cam.tiles_y * 4, st));
+    k_fill<<<(unsigned)((3 * HW + 255) / 256), 256, 0, st>>>(dpix, 3 * HW, grad_scale);
+    FB_LAUNCH_CHECK();
+    GaussIn gi = map_in(map);
+    Bins b = score_bins(L, ws, P, 1, cam, inst_capacity);
+    dim3 grid(cam.tiles_x, cam.tiles_y);
+    for (int k = 0; k < K; ++k) {
+        const float* w2c_k = w2c + (size_t)k * 16;
+        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 4, st));
+        k_preprocess<true, 0><<<(P + 255) / 256, 256, 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr);
+        FB_LAUNCH_CHECK();
+        k_scan_tiles<<<1, 1024, 0, st>>>(b);
+        k_status_update<<<1, 32, 0, st>>>(b.total, status_dev);
+        int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
+        k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam);
+        k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS);
+        FB_LAUNCH_CHECK();
+        k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
+                                                   (float*)(ws + L.color), (float*)(ws + L.depth));
+        k_bwd_tiles<true, false><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (const float*)(ws + L.final_T),
+                                                              (const uint32_t*)(ws + L.n_contrib), dpix, mom);
+        FB_LAUNCH_CHECK();
+        if (C_H == 4) k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out);
+        else k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out);
+        FB_LAUNCH_CHECK();
+    }
+    return FB_OK;
+}
+
+// ---- stage 5 ---------------------------------------------------------------------------------
+static fb::KnnWs knn_ws(int P, void* workspace, size_t* total) {
+    using namespace fb;
+    KnnWs w; char* ws = (char*)workspace; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1);
+    unsigned cap = (unsigned)(4 * Pp + 64);
+    unsigned nblocks = (cap + 1 + 1024 * FB_SCAN_ITEMS - 1) / (1024 * FB_SCAN_ITEMS);
+    w.cap = cap;
+    w.bbox = (unsigned*)(ws + o);     o = align_up(o + 32, 256);
+    w.grid = (KnnGrid*)(ws + o);      o = align_up(o + sizeof(KnnGrid), 256);
+    w.cell = (unsigned*)(ws + o);     o = align_up(o + ((size_t)cap + 1) * 4, 256);
+    w.cursor = (unsigned*)(ws + o);   o = align_up(o + (size_t)cap * 4, 256);
+    w.blocksum = (unsigned*)(ws + o); o = align_up(o + (size_t)nblocks * 4, 256);
+    w.sorted = (float4*)(ws + o);     o = align_up(o + Pp * 16, 256);
+    *total = o;
+    return w;
+}
+size_t fb_knn_workspace_bytes(int P) { size_t t; knn_ws(P, nullptr, &t); return t; }
+
+int fb_dist2_knn3(int P, const float* points, float* mean_dist2, void* workspace, size_t workspace_bytes, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (P < 0) return FB_E_INVALID;
+    if (P == 0) return FB_OK;
+    if (!points || !mean_dist2 || !workspace) return FB_E_INVALID;
+    size_t need; KnnWs w = knn_ws(P, workspace, &need);
+    if (workspace_bytes < need) return FB_E_WORKSPACE;
+    const unsigned n = w.cap + 1, nb = (n + 1024 * FB_SCAN_ITEMS - 1) / (1024 * FB_SCAN_ITEMS);
+    k_knn_init<<<148 * 4, 256, 0, st>>>(w);
+    k_knn_bbox<<<148 * 4, 256, 0, st>>>(P, points, w);
+    k_knn_setup<<<1, 32, 0, st>>>(P, w);
+    k_knn_count<<<(P + 255) / 256, 256, 0, st>>>(P, points, w);
+    FB_LAUNCH_CHECK();
+    k_scan_block<<<nb, 1024, 0, st>>>(w.cell, n, w.blocksum);
+    k_scan_sums<<<1, 1024, 0, st>>>(w.blocksum, nb);
+    k_scan_add<<<nb, 1024, 0, st>>>(w.cell, n, w.blocksum);
+    k_knn_scatter<<<(P + 255) / 256, 256, 0, st>>>(P, points, w);
+    k_knn_query<<<(P + 127) / 128, 128, 0, st>>>(P, w, mean_dist2);
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+int fb_count_visible(int N, const float* points, int K, const double* w2c, const double* intr, int img_w, int img_h,
+                     int* counts, uint8_t* mask, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (N < 0 || K < 0 || K > 256) return FB_E_INVALID;
+    if (K == 0) return FB_OK;
+    if (!counts || !w2c || !intr) return FB_E_INVALID;
+    FB_CUDA(cudaMemsetAsync(counts, 0, (size_t)K * 4, st));
+    if (N == 0) return FB_OK;
+    if (!points) return FB_E_INVALID;
+    int blocks = (N + 255) / 256; if (blocks > 148 * 8) blocks = 148 * 8;
+    k_count_visible<<<blocks, 256, (size_t)K * (12 * 8 + 4), st>>>(N, points, K, w2c, intr, img_w, img_h, counts, mask);
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,213 @@
+// fb_common.cuh -- shared device math for the FisherRF candidate-view scoring path (sm_100a).
+//
+// Everything here is plain FP32 SIMT arithmetic: the path has no dense contraction,
+// so tensor cores are deliberately unused.  The per-Gaussian
+// projection follows the arithmetic ORDER of the reference so that integer
+// outputs (radii, tile rectangles, keys) come out identical:
+//   reference preprocess      DGR/cuda_rasterizer/forward.cu:155-256
+//   reference helpers         DGR/cuda_rasterizer/auxiliary.h:41-97,139-164
+//   GLM mat3*mat3 order       DGR/third_party/glm/glm/detail/type_mat3x3.inl:514-545
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "../../include/fisher_b200.h"
+
+#define FB_TILE_PIX (FB_TILE_X * FB_TILE_Y)
+
+namespace fb {
+
+typedef unsigned long long u64;
+
+// Column-major 3x3 with the reference's (GLM) element naming: c[col][row].
+struct M3 {
+    float c[3][3];
+};
+
+// (A*B)[col][row] = A[0][row]*B[col][0] (+)= A[1][row]*B[col][1] (+)= A[2][row]*B[col][2]
+__device__ __forceinline__ M3 m3_mul(const M3& A, const M3& B) {
+    M3 R;
+#pragma unroll
+    for (int col = 0; col < 3; ++col) {
+#pragma unroll
+        for (int row = 0; row < 3; ++row) {
+            float t = A.c[0][row] * B.c[col][0];
+            t += A.c[1][row] * B.c[col][1];
+            t += A.c[2][row] * B.c[col][2];
+            R.c[col][row] = t;
+        }
+    }
+    return R;
+}
+__device__ __forceinline__ M3 m3_T(const M3& A) {
+    M3 R;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) R.c[i][j] = A.c[j][i];
+    return R;
+}
+
+// Camera constants resident in constant-like kernel parameters (one per launch).
+struct Cam {
+    int   W, H;
+    int   tiles_x, tiles_y;
+    float tanfovx, tanfovy;
+    float focal_x, focal_y;
+    float scale_modifier;
+    int   sh_degree, sh_coeffs, prefiltered;
+    float bg[3];
+    float campos[3];
+    float view[16];
+    float proj[16];
+};
+
+__host__ inline Cam make_cam(const fb_camera* c) {
+    Cam k;
+    k.W = c->image_width; k.H = c->image_height;
+    k.tiles_x = (k.W + FB_TILE_X - 1) / FB_TILE_X;
+    k.tiles_y = (k.H + FB_TILE_Y - 1) / FB_TILE_Y;
+    k.tanfovx = c->tanfovx; k.tanfovy = c->tanfovy;
+    // rasterizer_impl.cu:222-223
+    k.focal_y = k.H / (2.0f * c->tanfovy);
+    k.focal_x = k.W / (2.0f * c->tanfovx);
+    k.scale_modifier = c->scale_modifier;
+    k.sh_degree = c->sh_degree; k.sh_coeffs = c->sh_coeffs; k.prefiltered = c->prefiltered;
+    for (int i = 0; i < 3; ++i) { k.bg[i] = c->bg[i]; k.campos[i] = c->campos[i]; }
+    for (int i = 0; i < 16; ++i) { k.view[i] = c->viewmatrix[i]; k.proj[i] = c->projmatrix[i]; }
+    return k;
+}
+
+// auxiliary.h:58-77 (matrices are consumed column-major: m[0],m[4],m[8],m[12] is row 0)
+__device__ __forceinline__ float3 xform4x3(const float3& p, const float* m) {
+    float3 r;
+    r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+    r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+    r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+    return r;
+}
+__device__ __forceinline__ float4 xform4x4(const float3& p, const float* m) {
+    float4 r;
+    r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
+    r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
+    r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+    r.w = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+    return r;
+}
+
+// auxiliary.h:41-44 -- the literals are double, so ((v + 1.0) * S - 1.0) * 0.5 is evaluated in
+// FP64 and rounded to FP32 once.
+__device__ __forceinline__ float ndc_to_pix_exact(float v, int S) {
+    double d = (((double)v + 1.0) * (double)S - 1.0) * 0.5;
+    return (float)d;
+}
+
+// auxiliary.h:46-56: float division, (int) truncation, clamp to [0, grid].
+__device__ __forceinline__ void tile_rect(float px, float py, int max_radius, int tiles_x, int tiles_y,
+                                          int& x0, int& y0, int& x1, int& y1) {
+    x0 = min(tiles_x, max(0, (int)((px - max_radius) / FB_TILE_X)));
+    y0 = min(tiles_y, max(0, (int)((py - max_radius) / FB_TILE_Y)));
+    x1 = min(tiles_x, max(0, (int)((px + max_radius + FB_TILE_X - 1) / FB_TILE_X)));
+    y1 = min(tiles_y, max(0, (int)((py + max_radius + FB_TILE_Y - 1) / FB_TILE_Y)));
+}
+
+// forward.cu:118-152.  Quaternion (w,x,y,z) is used UN-normalised.
+__device__ __forceinline__ void rot_scale_M(const float3& scale, float mod, const float4& q, M3& R, float3& s, M3& M) {
+    float r = q.x, x = q.y, y = q.z, z = q.w;
+    // GLM constructor fills columns: (a,b,c) is column 0.
+    R.c[0][0] = 1.f - 2.f * (y * y + z * z); R.c[0][1] = 2.f * (x * y - r * z); R.c[0][2] = 2.f * (x * z + r * y);
+    R.c[1][0] = 2.f * (x * y + r * z); R.c[1][1] = 1.f - 2.f * (x * x + z * z); R.c[1][2] = 2.f * (y * z - r * x);
+    R.c[2][0] = 2.f * (x * z - r * y); R.c[2][1] = 2.f * (y * z + r * x); R.c[2][2] = 1.f - 2.f * (x * x + y * y);
+    s.x = mod * scale.x; s.y = mod * scale.y; s.z = mod * scale.z;
+    M3 S;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) S.c[i][j] = 0.f;
+    S.c[0][0] = s.x; S.c[1][1] = s.y; S.c[2][2] = s.z;
+    M = m3_mul(S, R);
+}
+__device__ __forceinline__ void cov3d_from_scale_rot(const float3& scale, float mod, const float4& q, float* cov6) {
+    M3 R, M; float3 s;
+    rot_scale_M(scale, mod, q, R, s, M);
+    M3 Sigma = m3_mul(m3_T(M), M);
+    cov6[0] = Sigma.c[0][0]; cov6[1] = Sigma.c[0][1]; cov6[2] = Sigma.c[0][2];
+    cov6[3] = Sigma.c[1][1]; cov6[4] = Sigma.c[1][2]; cov6[5] = Sigma.c[2][2];
+}
+
+// Shared by forward (forward.cu:74-113) and backward (backward.cu:276-330): the clamped
+// camera-space point t, T = W*J and the 2D covariance (a,b,c) including the +0.3 low-pass.
+struct Cov2D {
+    float3 t;       // clamped
+    float  txtz, tytz;
+    M3     T;
+    float  a, b, c;
+};
+__device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const float* cov6) {
+    Cov2D o;
+    float3 t = xform4x3(mean, cam.view);
+    const float limx = 1.3f * cam.tanfovx;
+    const float limy = 1.3f * cam.tanfovy;
+    o.txtz = t.x / t.z;
+    o.tytz = t.y / t.z;
+    t.x = fminf(limx, fmaxf(-limx, o.txtz)) * t.z;
+    t.y = fminf(limy, fmaxf(-limy, o.tytz)) * t.z;
+    o.t = t;
+    M3 J;
+    J.c[0][0] = cam.focal_x / t.z; J.c[0][1] = 0.f; J.c[0][2] = -(cam.focal_x * t.x) / (t.z * t.z);
+    J.c[1][0] = 0.f; J.c[1][1] = cam.focal_y / t.z; J.c[1][2] = -(cam.focal_y * t.y) / (t.z * t.z);
+    J.c[2][0] = 0.f; J.c[2][1] = 0.f; J.c[2][2] = 0.f;
+    M3 Wm;
+    Wm.c[0][0] = cam.view[0]; Wm.c[0][1] = cam.view[4]; Wm.c[0][2] = cam.view[8];
+    Wm.c[1][0] = cam.view[1]; Wm.c[1][1] = cam.view[5]; Wm.c[1][2] = cam.view[9];
+    Wm.c[2][0] = cam.view[2]; Wm.c[2][1] = cam.view[6]; Wm.c[2][2] = cam.view[10];
+    o.T = m3_mul(Wm, J);
+    M3 V;
+    V.c[0][0] = cov6[0]; V.c[0][1] = cov6[1]; V.c[0][2] = cov6[2];
+    V.c[1][0] = cov6[1]; V.c[1][1] = cov6[3]; V.c[1][2] = cov6[4];
+    V.c[2][0] = cov6[2]; V.c[2][1] = cov6[4]; V.c[2][2] = cov6[5];
+    M3 cov = m3_mul(m3_mul(m3_T(o.T), m3_T(V)), o.T);
+    o.a = cov.c[0][0] + 0.3f;
+    o.b = cov.c[0][1];
+    o.c = cov.c[1][1] + 0.3f;
+    return o;
+}
+
+// Result of projecting one Gaussian (stage 1).
+struct Splat {
+    float px, py;     // pixel-space centre
+    float depth;      // p_view.z
+    float ca, cb, cc; // conic (inverse 2D covariance): x, y, z of the reference's float3
+    int   radius;
+    int   x0, y0, x1, y1; // tile rectangle [x0,x1) x [y0,y1)
+};
+
+// Returns 0 if dropped; 1 if visible.  `culled_near` reports the near-plane cull for the
+// prefiltered trap (auxiliary.h:154-160).
+__device__ __forceinline__ int project_splat(const float3& p_orig, const float* cov6, const Cam& cam,
+                                             Splat& s, int& culled_near) {
+    culled_near = 0;
+    float3 p_view = xform4x3(p_orig, cam.view);
+    if (p_view.z <= 0.001f) { culled_near = 1; return 0; }
+    float4 p_hom = xform4x4(p_orig, cam.proj);
+    float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    float projx = p_hom.x * p_w, projy = p_hom.y * p_w;
+    Cov2D c2 = cov2d(p_orig, cam, cov6);
+    float det = (c2.a * c2.c - c2.b * c2.b);
+    if (det == 0.0f) return 0;
+    float det_inv = 1.f / det;
+    s.ca = c2.c * det_inv; s.cb = -c2.b * det_inv; s.cc = c2.a * det_inv;
+    float mid = 0.5f * (c2.a + c2.c);
+    float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
+    float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+    float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+    s.px = ndc_to_pix_exact(projx, cam.W);
+    s.py = ndc_to_pix_exact(projy, cam.H);
+    s.radius = (int)my_radius;
+    tile_rect(s.px, s.py, s.radius, cam.tiles_x, cam.tiles_y, s.x0, s.y0, s.x1, s.y1);
+    if ((s.x1 - s.x0) * (s.y1 - s.y0) == 0) return 0;
+    s.depth = p_view.z;
+    return 1;
+}
+
+}  // namespace fb

@@ -1,0 +1,66 @@
+// fb_layout.cuh -- private HBM layouts of the per-call state (geom / image / inst) and of the
+// batched scoring workspace.  The reference keeps comparable state in three byte buffers
+// (DGR/cuda_rasterizer/rasterizer_impl.h:30-70); those layouts are opaque to its callers
+// (only round-tripped to backward), so this one is free to be B200-shaped:
+//   * one 32-byte record per visible Gaussian (exactly one DRAM sector): {px,py,depth,opacity |
+//     conic a,b,c, radius}
+//   * instances are 8-byte keys (depth_bits<<32 | gaussian_id) binned per tile, so a tile's
+//     whole work list is one contiguous segment that a CTA can pull into shared memory.
+#pragma once
+#include "fb_common.cuh"
+
+namespace fb {
+
+static inline __host__ __device__ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// One projected Gaussian of one view: 32 bytes, 32-byte aligned.
+struct __align__(16) GRec {
+    float4 a;  // px, py, depth, opacity
+    float4 b;  // conic.x, conic.y, conic.z, __int_as_float(radius)
+};
+
+// View-batched binning state.  All arrays are [V][...] with the given strides.
+struct Bins {
+    GRec*     recs;        // [V][P]
+    float4*   recsB;       // [V][P][4]  scoring only: {rgb, coef0 | coef1-4 | coef5-8 | coef9-12}
+    uint32_t* vis_list;    // [V][P]   ids of visible Gaussians, unordered
+    uint32_t* vis_count;   // [V]
+    uint32_t* tile_count;  // [V][tiles]   instances per tile (used as a cursor by the scatter)
+    uint2*    tile_range;  // [V][tiles]   [start,end) into keys
+    uint32_t* total;       // [4]: total instances (lo), overflow flag, prefiltered-trap flag, max tile count
+    u64*      keys;        // [capacity]
+    long long capacity;
+    int       P;
+    int       V;
+    int       tiles;
+};
+
+struct GeomLayout {
+    size_t recs, rgb, clamped, vis_list, vis_count, total;
+};
+static inline __host__ GeomLayout geom_layout(int P) {
+    GeomLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1);
+    L.recs = o;      o = align_up(o + Pp * sizeof(GRec), 256);
+    L.rgb = o;       o = align_up(o + Pp * 3 * sizeof(float), 256);
+    L.clamped = o;   o = align_up(o + Pp * 4, 256);
+    L.vis_list = o;  o = align_up(o + Pp * 4, 256);
+    L.vis_count = o; o = align_up(o + 256, 256);
+    L.total = o;
+    return L;
+}
+struct ImageLayout {
+    size_t final_T, n_contrib, tile_range, tile_count, totals, total;
+};
+static inline __host__ ImageLayout image_layout(int W, int H) {
+    ImageLayout L; size_t o = 0; size_t HW = (size_t)W * H;
+    size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y);
+    L.final_T = o;    o = align_up(o + HW * 4, 256);
+    L.n_contrib = o;  o = align_up(o + HW * 4, 256);
+    L.tile_range = o; o = align_up(o + tiles * 8, 256);
+    L.tile_count = o; o = align_up(o + tiles * 4, 256);
+    L.totals = o;     o = align_up(o + 256, 256);
+    L.total = o;
+    return L;
+}
+
+}  // namespace fb

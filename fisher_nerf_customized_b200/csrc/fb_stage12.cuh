@@ -1,0 +1,297 @@
+// fb_stage12.cuh -- stage 1 (Gaussian preprocess) and stage 2 (tile binning + depth sort).
+//
+// Replaces, for one view or a batch of V views sharing one resident map:
+//   preprocessCUDA<3>          DGR/cuda_rasterizer/forward.cu:155-256
+//   InclusiveSum + D2H sync    DGR/cuda_rasterizer/rasterizer_impl.cu:277-282
+//   duplicateWithKeys          DGR/cuda_rasterizer/rasterizer_impl.cu:70-111
+//   DeviceRadixSort::SortPairs DGR/cuda_rasterizer/rasterizer_impl.cu:304-309
+//   identifyTileRanges         DGR/cuda_rasterizer/rasterizer_impl.cu:116-138
+//
+// B200 shape: instead of one global 41-bit radix sort (>= 6 passes over 12 B/instance) the
+// instances are counted per tile while the Gaussian is still in registers, a single-CTA scan
+// turns counts into segment offsets, the keys are scattered straight into their tile's
+// segment, and each tile's segment (a few KB) is sorted once in shared memory by the CTA that
+// owns the tile.  Sorting (depth_bits<<32 | gaussian_id) reproduces exactly the order of the
+// reference's stable (tile|depth) radix sort: ascending depth, ties by ascending Gaussian id
+// (the reference's emission order, rasterizer_impl.cu:92-108).
+#pragma once
+#include "fb_layout.cuh"
+#include "fb_fisher.cuh"
+
+namespace fb {
+
+// ---- SH -> RGB (forward.cu:20-71); coefficients are the standard real SH constants -------------
+__device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float3& pos, const float* campos,
+                                            const float* sh_g, bool* clamped3) {
+    const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+    const float C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                         -1.0925484305920792f, 0.5462742152960396f};
+    const float C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                         -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f};
+    float3 d = make_float3(pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]);
+    float len = sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
+    d.x = d.x / len; d.y = d.y / len; d.z = d.z / len;
+    float res[3];
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        const float* sh = sh_g + ch;   // sh[k] is sh_g[3*k + ch]
+#define SHK(k) sh[3 * (k)]
+        float r = C0 * SHK(0);
+        if (deg > 0) {
+            float x = d.x, y = d.y, z = d.z;
+            r = r - C1 * y * SHK(1) + C1 * z * SHK(2) - C1 * x * SHK(3);
+            if (deg > 1) {
+                float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                r = r + C2[0] * xy * SHK(4) + C2[1] * yz * SHK(5) + C2[2] * (2.0f * zz - xx - yy) * SHK(6) +
+                    C2[3] * xz * SHK(7) + C2[4] * (xx - yy) * SHK(8);
+                if (deg > 2) {
+                    r = r + C3[0] * y * (3.0f * xx - yy) * SHK(9) + C3[1] * xy * z * SHK(10) +
+                        C3[2] * y * (4.0f * zz - xx - yy) * SHK(11) +
+                        C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHK(12) +
+                        C3[4] * x * (4.0f * zz - xx - yy) * SHK(13) + C3[5] * z * (xx - yy) * SHK(14) +
+                        C3[6] * x * (xx - 3.0f * yy) * SHK(15);
+                }
+            }
+        }
+#undef SHK
+        r += 0.5f;
+        clamped3[ch] = (r < 0);
+        res[ch] = fmaxf(r, 0.0f);
+    }
+    (void)M;
+    return make_float3(res[0], res[1], res[2]);
+}
+
+// Gaussian inputs as device pointers (fb_gaussians / fb_map).
+struct GaussIn {
+    const float* means3D; const float* opacities; const float* shs; const float* colors;
+    const float* scales; const float* rotations; const float* cov3D;
+};
+
+// ---- stage 1 -------------------------------------------------------------------------------
+// One thread per Gaussian; the Gaussian (44 B: mean 12 + scale 12 + quat 16 + opacity 4) is
+// loaded ONCE, its 3D covariance is built once, and it is then projected into every view of
+// the batch while still in registers.  w2c (BATCHED only): V row-major 4x4 matrices; the mean
+// is moved to the camera frame as torch's fp32 matmul does in the reference caller
+// (models/SLAM/gaussian.py:1523-1527), the rotation stays in the world frame.
+// CH > 0 (scoring): additionally emits the 64-byte scoring record {rgb, 13 polynomial coefficients}
+// built from weight[g, 0..CH) = 1/(H_train+lambda)  (fb_fisher.cuh: score_coefs).
+template <bool BATCHED, int CH>
+__global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const float* __restrict__ w2c, Bins bins,
+                                                    int* __restrict__ radii, float* __restrict__ rgb,
+                                                    bool* __restrict__ clamped, const float* __restrict__ weight) {
+    extern __shared__ float s_w2c[];  // V*12
+    const int P = bins.P, V = bins.V;
+    if (BATCHED) {
+        for (int i = threadIdx.x; i < V * 12; i += blockDim.x) s_w2c[i] = w2c[(i / 12) * 16 + (i % 12)];
+        __syncthreads();
+    }
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = idx < P;
+    const int lane = threadIdx.x & 31;
+    float3 p = make_float3(0.f, 0.f, 0.f);
+    float cov6[6] = {0, 0, 0, 0, 0, 0};
+    float opacity = 0.f;
+    if (live) {
+        p = make_float3(g.means3D[3 * idx], g.means3D[3 * idx + 1], g.means3D[3 * idx + 2]);
+        opacity = g.opacities[idx];
+        if (g.cov3D != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) cov6[i] = g.cov3D[6 * (size_t)idx + i];
+        } else {
+            float3 sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
+            float4 q = *reinterpret_cast<const float4*>(g.rotations + 4 * (size_t)idx);
+            cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov6);
+        }
+    }
+    for (int v = 0; v < V; ++v) {
+        float3 pc = p;
+        if (BATCHED) {
+            const float* m = s_w2c + v * 12;
+            pc.x = fmaf(m[2], p.z, fmaf(m[1], p.y, m[0] * p.x)) + m[3];
+            pc.y = fmaf(m[6], p.z, fmaf(m[5], p.y, m[4] * p.x)) + m[7];
+            pc.z = fmaf(m[10], p.z, fmaf(m[9], p.y, m[8] * p.x)) + m[11];
+        }
+        Splat s; int culled = 0; int vis = 0;
+        if (live) vis = project_splat(pc, cov6, cam, s, culled);
+        if (!BATCHED) {
+            if (live) radii[idx] = vis ? s.radius : 0;
+            if (live && culled && cam.prefiltered) bins.total[2] = 1u;
+        }
+        // warp-aggregated append to the view's visible list
+        unsigned m = __ballot_sync(0xffffffffu, vis);
+        if (m) {
+            int leader = __ffs(m) - 1;
+            unsigned base = 0;
+            if (lane == leader) base = atomicAdd(&bins.vis_count[v], (unsigned)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (vis) {
+                unsigned slot = base + __popc(m & ((1u << lane) - 1u));
+                bins.vis_list[(size_t)v * P + slot] = (unsigned)idx;
+                GRec r;
+                r.a = make_float4(s.px, s.py, s.depth, opacity);
+                r.b = make_float4(s.ca, s.cb, s.cc, __int_as_float(s.radius));
+                bins.recs[(size_t)v * P + idx] = r;
+                if (CH > 0) {
+                    float3 sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
+                    float4 q = *reinterpret_cast<const float4*>(g.rotations + 4 * (size_t)idx);
+                    SRCtx sr = make_sr(sc, cam.scale_modifier, q);
+                    GCtx ctx = make_ctx(pc, cov6, cam);
+                    float wv[CH > 0 ? CH : 1];
+#pragma unroll
+                    for (int k = 0; k < CH; ++k) wv[k] = weight[(size_t)idx * CH + k];
+                    float coef[13];
+                    score_coefs<CH>(ctx, cam, sr, s.ca, s.cb, s.cc, opacity, wv, coef);
+                    float4* rb = bins.recsB + ((size_t)v * P + idx) * 4;
+                    rb[0] = make_float4(g.colors[3 * idx], g.colors[3 * idx + 1], g.colors[3 * idx + 2], coef[0]);
+                    rb[1] = make_float4(coef[1], coef[2], coef[3], coef[4]);
+                    rb[2] = make_float4(coef[5], coef[6], coef[7], coef[8]);
+                    rb[3] = make_float4(coef[9], coef[10], coef[11], coef[12]);
+                }
+                uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles;
+                for (int y = s.y0; y < s.y1; ++y)
+                    for (int x = s.x0; x < s.x1; ++x) atomicAdd(&tc[y * cam.tiles_x + x], 1u);
+                if (!BATCHED && g.colors == nullptr) {
+                    bool cl[3];
+                    float3 c = sh_to_rgb(cam.sh_degree, cam.sh_coeffs, p, cam.campos,
+                                         g.shs + (size_t)idx * cam.sh_coeffs * 3, cl);
+                    rgb[3 * idx] = c.x; rgb[3 * idx + 1] = c.y; rgb[3 * idx + 2] = c.z;
+                    clamped[4 * idx] = cl[0]; clamped[4 * idx + 1] = cl[1]; clamped[4 * idx + 2] = cl[2];
+                }
+            }
+        }
+    }
+}
+
+// ---- stage 2a: counts -> segment offsets (one CTA, V*tiles entries) -------------------------
+// Empty tiles get range (0,0) as in the reference (cudaMemset + identifyTileRanges,
+// rasterizer_impl.cu:311-319).  total[0] = instance count, total[1] = overflow flag,
+// total[3] = largest tile segment.
+__global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
+    __shared__ unsigned warp_sums[32];
+    __shared__ unsigned carry_s;
+    __shared__ unsigned maxc_s;
+    const int n = bins.V * bins.tiles;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { carry_s = 0; maxc_s = 0; }
+    __syncthreads();
+    unsigned local_max = 0;
+    for (int base = 0; base < n; base += blockDim.x) {
+        int i = base + threadIdx.x;
+        unsigned c = (i < n) ? bins.tile_count[i] : 0u;
+        local_max = max(local_max, c);
+        unsigned x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sums[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            unsigned w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned y = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += y;
+            }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        unsigned incl = x + (wid > 0 ? warp_sums[wid - 1] : 0u) + carry_s;
+        if (i < n) {
+            unsigned start = incl - c;
+            bins.tile_range[i] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
+        }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry_s = incl;
+        __syncthreads();
+    }
+    atomicMax(&maxc_s, local_max);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        bins.total[0] = carry_s;
+        bins.total[1] = ((long long)carry_s > bins.capacity) ? 1u : 0u;
+        bins.total[3] = maxc_s;
+    }
+}
+
+// ---- stage 2b: scatter keys into tile segments ----------------------------------------------
+// One thread per visible Gaussian of a view.  tile_count doubles as the cursor (counted down).
+__global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
+    const int v = blockIdx.y;
+    uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles;
+    if (bins.total[1]) {
+        // capacity exceeded: the caller re-runs with a larger buffer.  Leave the cursors clean.
+        if (blockIdx.x == 0)
+            for (int i = threadIdx.x; i < bins.tiles; i += blockDim.x) tc[i] = 0u;
+        return;
+    }
+    const unsigned nvis = bins.vis_count[v];
+    const uint2* tr = bins.tile_range + (size_t)v * bins.tiles;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvis; i += gridDim.x * blockDim.x) {
+        unsigned gid = bins.vis_list[(size_t)v * bins.P + i];
+        GRec r = bins.recs[(size_t)v * bins.P + gid];
+        int x0, y0, x1, y1;
+        tile_rect(r.a.x, r.a.y, __float_as_int(r.b.w), cam.tiles_x, cam.tiles_y, x0, y0, x1, y1);
+        u64 key = ((u64)__float_as_uint(r.a.z) << 32) | (u64)gid;
+        for (int y = y0; y < y1; ++y)
+            for (int x = x0; x < x1; ++x) {
+                int t = y * cam.tiles_x + x;
+                unsigned slot = atomicSub(&tc[t], 1u) - 1u;
+                bins.keys[tr[t].x + slot] = key;
+            }
+    }
+}
+
+// ---- stage 2c: in-CTA sort of one tile segment ----------------------------------------------
+// Bitonic network in the all-ascending form (first step of each merge flips the partner inside
+// the block, later steps are plain xor), so indices >= n behave as +inf without being stored:
+// works in place on any n, in shared or global memory.
+__device__ __forceinline__ void cta_sort_u64(u64* a, int n) {
+    if (n < 2) return;
+    int np2 = 1;
+    while (np2 < n) np2 <<= 1;
+    for (int k = 2; k <= np2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (np2 >> 1); t += blockDim.x) {
+                int lo, hi;
+                if (j == (k >> 1)) {
+                    int blk = t / j, off = t % j;
+                    lo = blk * k + off;
+                    hi = blk * k + k - 1 - off;
+                } else {
+                    lo = ((t / j) * (j << 1)) + (t % j);
+                    hi = lo + j;
+                }
+                if (hi < n) {
+                    u64 x = a[lo], y = a[hi];
+                    if (x > y) { a[lo] = y; a[hi] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// Single-view path: sort every tile segment in place (shared memory when it fits).
+__global__ void __launch_bounds__(256) k_sort_tiles(Bins bins, int smem_keys) {
+    extern __shared__ u64 s_keys[];
+    const int v = blockIdx.y, t = blockIdx.x;
+    if (bins.total[1]) return;
+    uint2 r = bins.tile_range[(size_t)v * bins.tiles + t];
+    int n = (int)(r.y - r.x);
+    if (n < 2) return;
+    u64* seg = bins.keys + r.x;
+    if (n <= smem_keys) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = seg[i];
+        __syncthreads();
+        cta_sort_u64(s_keys, n);
+        for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = s_keys[i];
+    } else {
+        __syncthreads();
+        cta_sort_u64(seg, n);
+    }
+}
+
+}  // namespace fb

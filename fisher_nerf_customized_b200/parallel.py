@@ -1,0 +1,83 @@
+"""Candidate-pose sharding over the GPUs of one box (one process per GPU, torch.distributed).
+
+The reference has no multi-GPU path; this is the additive data-parallel layer of
+SURVEY 8(e): every rank holds a replica of the Gaussian map; candidates are split into contiguous
+blocks of ceil(K/G); keyframes for H_train are dealt round-robin and combined with one all-reduce;
+per-candidate scores are all-gathered so that every rank computes the same argmax.  The only
+collectives are the ones the path really has (map broadcast, H_train sum, score gather): there is
+no data-path exchange inside a view.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(K, world, rank):
+    """Contiguous block [lo, hi) of candidate indices owned by `rank`."""
+    per = (K + world - 1) // world if K > 0 else 0
+    lo = min(K, rank * per)
+    return lo, min(K, lo + per)
+
+
+def round_robin(n, world, rank):
+    return list(range(rank, n, world))
+
+
+class ShardedScorer:
+    """Wraps a local scorer (FisherScorer-like: .score_candidates, .compute_H_train) with the collectives.
+
+    `group` may be any torch.distributed backend: nccl over NVLink on the GPU box, gloo in the CPU tests
+    (where the local scorer is a stand-in; the product's local scorer is always the CUDA one)."""
+
+    def __init__(self, scorer, group=None):
+        self.scorer = scorer
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+
+    def broadcast_map(self, tensors, src=0):
+        """Map update: the owner's parameter tensors overwrite every replica (56*P bytes at init;
+        callers pass only appended rows in the active-mapping loop)."""
+        if self.world > 1:
+            for t in tensors:
+                dist.broadcast(t, src=src, group=self.group)
+        return tensors
+
+    def compute_H_train(self, gmap, keyframe_w2c):
+        n = keyframe_w2c.shape[0]
+        mine = round_robin(n, self.world, self.rank)
+        H = None
+        if len(mine) > 0:
+            H = self.scorer.compute_H_train(gmap, keyframe_w2c[mine])
+        if H is None:
+            H = torch.zeros((gmap.P, self.scorer.C_H), dtype=torch.float32, device=gmap.means3D.device)
+        if self.world > 1:
+            dist.all_reduce(H, op=dist.ReduceOp.SUM, group=self.group)
+        return H
+
+    def score_candidates(self, gmap, w2c, H_train_inv):
+        """Returns the full scores[K] on every rank."""
+        K = w2c.shape[0]
+        lo, hi = shard_bounds(K, self.world, self.rank)
+        per = (K + self.world - 1) // self.world if K > 0 else 0
+        dev = gmap.means3D.device
+        local = torch.zeros((per,), dtype=torch.float32, device=dev)
+        if hi > lo:
+            local[: hi - lo] = self.scorer.score_candidates(gmap, w2c[lo:hi], H_train_inv)
+        if self.world == 1:
+            return local[:K]
+        gathered = torch.empty((self.world * per,), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(gathered, local, group=self.group) if dev.type == "cuda" else \
+            self._gather_cpu(gathered, local)
+        return gathered[:K]
+
+    def _gather_cpu(self, out, local):
+        parts = [torch.empty_like(local) for _ in range(self.world)]
+        dist.all_gather(parts, local, group=self.group)
+        out.copy_(torch.cat(parts))
+
+    def pose_eval(self, gmap, poses_c2w, keyframe_w2c, H_reg_lambda=0.1):
+        H_train = self.compute_H_train(gmap, keyframe_w2c)
+        H_train_inv = torch.reciprocal(H_train + H_reg_lambda)
+        w2c = torch.linalg.inv(poses_c2w.float())
+        scores = self.score_candidates(gmap, w2c, H_train_inv)
+        return scores, int(torch.argmax(scores).item())

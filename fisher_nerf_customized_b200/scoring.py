@@ -1,0 +1,172 @@
+"""Batched FisherRF candidate-view scoring against a resident Gaussian map.
+
+Host-side mirror of the reference callers (names and arithmetic kept):
+  setup_camera                    models/SLAM/utils/recon_helpers.py:4-32
+  GaussianSLAM.compute_Hessian    models/SLAM/gaussian.py:1503-1570   (C_H = 4)
+  GaussianObjectSLAM.compute_Hessian  models/SLAM/gaussian_object.py:1940-2045  (C_H = 11)
+  GaussianSLAM.compute_H_train    models/SLAM/gaussian.py:1338-1348
+  GaussianSLAM.pose_eval          models/SLAM/gaussian.py:1354-1375
+The K-iteration Python loop with one host sync per pose becomes one launch sequence per chunk of
+poses (`fb_score_candidates`), with no host sync until the scores are read.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .rasterizer import GaussianRasterizationSettings, _camera, _f32c, _stream
+
+
+def setup_camera(w, h, k, w2c, near=0.01, far=100, device="cuda"):
+    """Same camera as the reference's setup_camera (OpenGL-style projection, matrices stored transposed)."""
+    fx, fy, cx, cy = float(k[0][0]), float(k[1][1]), float(k[0][2]), float(k[1][2])
+    w2c = torch.as_tensor(w2c, dtype=torch.float32).to(device)
+    cam_center = torch.inverse(w2c)[:3, 3]
+    w2c_t = w2c.unsqueeze(0).transpose(1, 2)
+    proj = torch.tensor([[2 * fx / w, 0.0, -(w - 2 * cx) / w, 0.0],
+                         [0.0, 2 * fy / h, -(h - 2 * cy) / h, 0.0],
+                         [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                         [0.0, 0.0, 1.0, 0.0]], dtype=torch.float32, device=device).unsqueeze(0).transpose(1, 2)
+    full_proj = w2c_t.bmm(proj)
+    return GaussianRasterizationSettings(
+        image_height=h, image_width=w, tanfovx=w / (2 * fx), tanfovy=h / (2 * fy),
+        bg=torch.tensor([0, 0, 0], dtype=torch.float32, device=device), scale_modifier=1.0,
+        viewmatrix=w2c_t, projmatrix=full_proj, sh_degree=0, campos=cam_center, prefiltered=False)
+
+
+class GaussianMap:
+    """The resident map in the activated form compute_Hessian feeds the rasteriser
+    (gaussian.py:1523-1543): world-frame means, normalised rotations, sigmoid opacities, exp scales, rgb."""
+
+    def __init__(self, means3D, rgb_colors, rotations, opacities, scales):
+        self.means3D = _f32c(means3D)
+        self.colors = _f32c(rgb_colors)
+        self.rotations = _f32c(rotations)
+        self.opacities = _f32c(opacities.reshape(-1))
+        scales = scales if scales.shape[-1] == 3 else scales.repeat(1, 3)   # isotropic: gaussian.py:1532-1533
+        self.scales = _f32c(scales)
+        self.P = self.means3D.shape[0]
+
+    @classmethod
+    def from_params(cls, params):
+        """From the reference's raw parameter dict (gaussian.py:156-168)."""
+        with torch.no_grad():
+            return cls(params["means3D"], params["rgb_colors"],
+                       torch.nn.functional.normalize(params["unnorm_rotations"]),
+                       torch.sigmoid(params["logit_opacities"]), torch.exp(params["log_scales"]))
+
+    def c_struct(self):
+        m = _lib.fb_map()
+        m.P = self.P
+        m.means3D, m.opacities = self.means3D.data_ptr(), self.opacities.data_ptr()
+        m.scales, m.rotations, m.colors = self.scales.data_ptr(), self.rotations.data_ptr(), self.colors.data_ptr()
+        return m
+
+    def tensors(self):
+        return [self.means3D, self.colors, self.rotations, self.opacities, self.scales]
+
+
+class FisherScorer:
+    """Scores candidate poses by expected information gain, sum(H_candidate * 1/(H_train + lambda))."""
+
+    def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=16,
+                 inst_capacity=None):
+        assert C_H in (4, 11)
+        self.cam, self.C_H, self.grad_scale = cam, C_H, float(grad_scale)
+        self.V = int(views_per_chunk)
+        self.inst_capacity = inst_capacity
+        self._ws = None
+        self._ws_key = None
+        self.last_status = None
+        self.launches = 0
+
+    def _c_cam(self):
+        rs = self.cam
+        return _camera(rs.bg, rs.scale_modifier, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                       rs.image_width, rs.sh_degree, 0, rs.campos, rs.prefiltered)
+
+    def _workspace(self, gmap, cap):
+        L = _lib.lib()
+        key = (gmap.P, self.V, cap, gmap.means3D.device)
+        if self._ws_key != key:
+            n = L.fb_score_workspace_bytes(gmap.P, self.cam.image_width, self.cam.image_height, self.V, cap)
+            self._ws = None
+            self._ws = torch.empty((n,), dtype=torch.uint8, device=gmap.means3D.device)
+            self._ws_key = key
+        return self._ws
+
+    def _capacity(self, gmap):
+        if self.inst_capacity is None:
+            # a projected Gaussian at 256^2 touches ~1-4 tiles; start generous, grow on overflow
+            self.inst_capacity = max(1 << 20, 2 * gmap.P) * max(1, self.V // 4)
+        return int(self.inst_capacity)
+
+    def _run(self, fn_name, gmap, w2c, extra):
+        """Common driver with grow-on-overflow.  Reads the 12-byte status once per call (the only sync)."""
+        L = _lib.lib()
+        w2c = _f32c(w2c.to(device=gmap.means3D.device, dtype=torch.float32).reshape(-1, 4, 4))
+        K = w2c.shape[0]
+        cam, m = self._c_cam(), gmap.c_struct()
+        status = torch.zeros((4,), dtype=torch.int32, device=gmap.means3D.device)
+        while True:
+            cap = self._capacity(gmap)
+            ws = self._workspace(gmap, cap)
+            rc = extra(L, cam, m, w2c, K, status, ws, cap)
+            _lib.check(rc, fn_name)
+            tiles = ((self.cam.image_width + 15) // 16) * ((self.cam.image_height + 15) // 16)
+            nchunks = (K + self.V - 1) // self.V if fn_name == "fb_score_candidates" else K
+            self.launches += nchunks * (6 if fn_name == "fb_score_candidates" else 8)
+            st = status.tolist()
+            self.last_status = st
+            if st[0] == 0:
+                return
+            if st[0] == _lib.FB_E_CAPACITY:
+                self.inst_capacity = int(st[1] * 1.25) + 1024
+                continue
+            _lib.check(st[0], fn_name)
+
+    @torch.no_grad()
+    def score_candidates(self, gmap: GaussianMap, w2c, H_train_inv):
+        """scores[k] = sum(H_k * H_train_inv), H_k the Fisher diagonal of pose k (gaussian.py:1362-1370).
+        w2c: [K,4,4] world-to-camera (already inverted).  Returns a CUDA float tensor [K]."""
+        K = w2c.reshape(-1, 4, 4).shape[0]
+        weight = _f32c(H_train_inv.reshape(gmap.P, self.C_H))
+        scores = torch.zeros((K,), dtype=torch.float32, device=gmap.means3D.device)
+
+        def call(L, cam, m, w2c_t, K_, status, ws, cap):
+            return L.fb_score_candidates(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, weight.data_ptr(), self.C_H,
+                                         self.grad_scale, scores.data_ptr(), status.data_ptr(), ws.data_ptr(),
+                                         ws.numel(), self.V, cap, _stream())
+        self._run("fb_score_candidates", gmap, w2c, call)
+        return scores
+
+    @torch.no_grad()
+    def compute_H_train(self, gmap: GaussianMap, keyframe_w2c, out=None):
+        """H_train[P,C_H] = sum over keyframes of the per-view Fisher diagonal (gaussian.py:1338-1348)."""
+        H = out if out is not None else torch.zeros((gmap.P, self.C_H), dtype=torch.float32, device=gmap.means3D.device)
+        H0 = H.clone() if out is not None else None
+
+        def call(L, cam, m, w2c_t, K_, status, ws, cap):
+            if H0 is not None:
+                H.copy_(H0)
+            else:
+                H.zero_()
+            return L.fb_accumulate_hessian(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, self.C_H, self.grad_scale,
+                                           H.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), self.V, cap,
+                                           _stream())
+        self._run("fb_accumulate_hessian", gmap, keyframe_w2c, call)
+        return H
+
+    @torch.no_grad()
+    def compute_Hessian(self, gmap: GaussianMap, rel_w2c):
+        """cur_H[P,C_H] for one pose (return_points=True form of the reference's compute_Hessian)."""
+        return self.compute_H_train(gmap, rel_w2c.reshape(1, 4, 4))
+
+    @torch.no_grad()
+    def pose_eval(self, gmap: GaussianMap, poses_c2w, keyframe_w2c, H_reg_lambda=0.1):
+        """Reference pose_eval: returns (scores [K] CPU tensor, poses)."""
+        H_train = self.compute_H_train(gmap, keyframe_w2c)
+        H_train_inv = torch.reciprocal(H_train + H_reg_lambda)
+        poses_c2w = torch.as_tensor(poses_c2w, dtype=torch.float32, device=gmap.means3D.device).reshape(-1, 4, 4)
+        w2c = torch.linalg.inv(poses_c2w)
+        return self.score_candidates(gmap, w2c, H_train_inv).cpu(), poses_c2w

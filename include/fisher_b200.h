@@ -1,0 +1,236 @@
+/*
+ * fisher_b200.h -- C ABI of the B200-native FisherRF candidate-view scoring path.
+ *
+ * Every entry point takes raw DEVICE pointers (unless the name says host), plain
+ * sizes, an explicit cudaStream_t (passed as void*) and returns an int status
+ * (FB_OK == 0, negative on error; fb_error_string() gives the text).  No torch
+ * types cross this boundary; all buffers are allocated by the caller.
+ *
+ * Reference interfaces replaced (paths relative to the upstream repo,
+ * DGR = thirdparty/diff-gaussian-rasterization-modified, KNN = thirdparty/simple-knn):
+ *
+ *   fb_raster_forward_bin + fb_raster_forward_render
+ *        <- CudaRasterizer::Rasterizer::forward      DGR/cuda_rasterizer/rasterizer.h:29-56,
+ *           bound by RasterizeGaussiansCUDA          DGR/rasterize_points.cu:35-115
+ *   fb_raster_backward
+ *        <- CudaRasterizer::Rasterizer::backward     DGR/cuda_rasterizer/rasterizer.h:58-84,
+ *           bound by RasterizeGaussiansBackwardCUDA  DGR/rasterize_points.cu:117-196
+ *   fb_mark_visible
+ *        <- CudaRasterizer::Rasterizer::markVisible  DGR/cuda_rasterizer/rasterizer.h:24-27
+ *   fb_dist2_knn3
+ *        <- SimpleKNN::knn(int P, float3*, float*)   KNN/simple_knn.h:18
+ *   fb_count_visible
+ *        <- count_visible_points (numpy)             tester_navigator.py:147-180
+ *   fb_score_candidates / fb_accumulate_hessian   (additive, batched)
+ *        <- the Python loops GaussianSLAM.pose_eval / compute_H_train / compute_Hessian
+ *           models/SLAM/gaussian.py:1338-1375,1503-1570 (11-column variant
+ *           models/SLAM/gaussian_object.py:1940-2045)
+ *
+ * The reference hands the rasteriser three std::function<char*(size_t)> resize
+ * callbacks (rasterizer.h:32-34).  That is not C-ABI safe; here the caller asks
+ * for sizes (fb_*_bytes) and allocates.  The one size that is only known on the
+ * device, num_rendered, is returned by fb_raster_forward_bin to the host exactly
+ * where the reference reads it back (rasterizer_impl.cu:282).
+ */
+#ifndef FISHER_B200_H
+#define FISHER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FB_OK                 0
+#define FB_E_INVALID        (-1)  /* bad argument (null pointer, non-positive size, unsupported combination) */
+#define FB_E_WORKSPACE      (-2)  /* caller-provided workspace too small */
+#define FB_E_CUDA           (-3)  /* a CUDA runtime call or launch failed; see fb_last_cuda_error() */
+#define FB_E_CAPACITY       (-4)  /* device-side instance capacity exceeded; *needed tells how much */
+#define FB_E_PREFILTERED    (-5)  /* prefiltered=1 but a point was culled (reference: device __trap, auxiliary.h:156-160) */
+
+/* Compile-time raster constants, identical to DGR/cuda_rasterizer/config.h:15-17. */
+#define FB_NUM_CHANNELS 3
+#define FB_TILE_X 16
+#define FB_TILE_Y 16
+
+/* Camera + raster constants: the numeric fields of GaussianRasterizationSettings
+ * (DGR/diff_gaussian_rasterization/__init__.py:140-151).  Matrices are the 16
+ * floats exactly as the reference passes them, i.e. the row-major memory of the
+ * TRANSPOSED matrix (column-major for the kernels; auxiliary.h:58-77). */
+typedef struct fb_camera {
+    int   image_width;
+    int   image_height;
+    float tanfovx;
+    float tanfovy;
+    float scale_modifier;
+    int   sh_degree;       /* D: active SH degree 0..3 */
+    int   sh_coeffs;       /* M: coefficients per Gaussian in `shs` (0 if none) */
+    int   prefiltered;
+    float bg[3];
+    float campos[3];
+    float viewmatrix[16];
+    float projmatrix[16];
+} fb_camera;
+
+/* Gaussian inputs of one rasterisation call.  Exactly one of shs / colors_precomp
+ * and exactly one of (scales, rotations) / cov3D_precomp is non-null, as enforced
+ * by GaussianRasterizer.forward (__init__.py:174-178). */
+typedef struct fb_gaussians {
+    int          P;
+    const float* means3D;        /* [P,3] */
+    const float* opacities;      /* [P]   */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3]   or NULL */
+    const float* scales;         /* [P,3]   or NULL */
+    const float* rotations;      /* [P,4] (w,x,y,z; used un-normalised) or NULL */
+    const float* cov3D_precomp;  /* [P,6]   or NULL */
+} fb_gaussians;
+
+const char* fb_error_string(int status);
+int         fb_last_cuda_error(void);     /* cudaError_t of the last FB_E_CUDA, as int */
+int         fb_version(void);
+
+/* ---- single-view drop-in path --------------------------------------------- */
+
+/* Per-call state sizes.  `geom` holds the per-Gaussian state kept for backward
+ * (the role of the reference's geomBuffer, rasterizer_impl.h:30-46); `image` the
+ * per-pixel + per-tile state (imgBuffer, :48-57); `inst` the sorted per-instance
+ * records (binningBuffer, :59-70).  Layouts are private to this library. */
+size_t fb_geom_bytes(int P);
+size_t fb_image_bytes(int width, int height);
+size_t fb_inst_bytes(int num_rendered);
+/* Scratch needed only during fb_raster_forward_* (unsorted keys, scan temp). */
+size_t fb_forward_scratch_bytes(int P, int width, int height, int num_rendered);
+/* Scratch needed only during fb_raster_backward (per-instance moment rows). */
+size_t fb_backward_scratch_bytes(int P, int num_rendered, int power, int has_sh);
+
+/* Stage 1 + first half of stage 2: preprocess all Gaussians, count instances per
+ * Gaussian and per tile, scan.  Writes radii[P] (int32).  Blocks until the total
+ * instance count is on the host and stores it in *num_rendered_host. */
+int fb_raster_forward_bin(const fb_camera* cam, const fb_gaussians* g,
+                          void* geom, size_t geom_bytes,
+                          void* image, size_t image_bytes,
+                          void* scratch, size_t scratch_bytes,
+                          int* radii,
+                          int* num_rendered_host,
+                          void* stream);
+
+/* Second half of stage 2 + stage 3: emit (depth|gaussian) keys per tile, sort each
+ * tile, gather the sorted per-instance records, alpha-blend.  Writes
+ * out_color[3,H,W], out_depth[1,H,W]. */
+int fb_raster_forward_render(const fb_camera* cam, const fb_gaussians* g,
+                             void* geom, size_t geom_bytes,
+                             void* image, size_t image_bytes,
+                             void* inst, size_t inst_bytes,
+                             void* scratch, size_t scratch_bytes,
+                             int num_rendered,
+                             float* out_color, float* out_depth,
+                             void* stream);
+
+/* Stage 4, drop-in form.  All nine outputs must be ZERO-FILLED by the caller
+ * (the reference glue uses torch::zeros, rasterize_points.cu:151-159) and have
+ * the reference's shapes: dL_dmeans2D[P,3], dL_dconic[P,2,2], dL_dopacity[P],
+ * dL_dcolors[P,3], dL_dmeans3D[P,3], dL_dcov3D[P,6], dL_dsh[P,M,3],
+ * dL_dscales[P,3], dL_drotations[P,4].  `power` is backward_power
+ * (__init__.py:154): every per-(pixel,Gaussian) partial is raised to it before
+ * accumulation (backward.cu:1093-1137). */
+int fb_raster_backward(const fb_camera* cam, const fb_gaussians* g,
+                       const int* radii,
+                       const void* geom, size_t geom_bytes,
+                       const void* image, size_t image_bytes,
+                       const void* inst, size_t inst_bytes,
+                       void* scratch, size_t scratch_bytes,
+                       int num_rendered,
+                       const float* dL_dpix,   /* [3,H,W] */
+                       int power,
+                       float* dL_dmeans2D, float* dL_dconic, float* dL_dopacity,
+                       float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D,
+                       float* dL_dsh, float* dL_dscales, float* dL_drotations,
+                       void* stream);
+
+/* present[i] = (viewmatrix * p_i).z > 0.001  (rasterizer_impl.cu:54-66). */
+int fb_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                    const float* projmatrix, uint8_t* present, void* stream);
+
+/* Introspection for parity tests: copies of the private state in the
+ * reference's vocabulary.  Any output pointer may be NULL.
+ *   tiles_touched[P] u32, depths[P], means2D[P,2], conic_opacity[P,4] (geom)
+ *   ranges[tiles,2] u32, final_T[HW], n_contrib[HW] u32            (image)
+ *   point_list[R] u32 (sorted Gaussian ids), point_keys[R] u64 (tile<<32|depth bits) (inst) */
+int fb_debug_export(const fb_camera* cam, int P, int num_rendered,
+                    const void* geom, const void* image, const void* inst,
+                    uint32_t* tiles_touched, float* depths, float* means2D, float* conic_opacity,
+                    uint32_t* ranges, float* final_T, uint32_t* n_contrib,
+                    uint32_t* point_list, uint64_t* point_keys,
+                    void* stream);
+
+/* ---- batched candidate scoring (resident map, many poses, no host sync) ---- */
+
+/* The resident Gaussian map in the activated form compute_Hessian feeds the
+ * rasteriser (gaussian.py:1523-1543): world-frame means, NORMALISED rotations,
+ * sigmoid opacities, exp scales, rgb colours. */
+typedef struct fb_map {
+    int          P;
+    const float* means3D;    /* [P,3] world frame */
+    const float* opacities;  /* [P]   */
+    const float* scales;     /* [P,3] */
+    const float* rotations;  /* [P,4] */
+    const float* colors;     /* [P,3] */
+} fb_map;
+
+/* Workspace for scoring `views_per_chunk` poses at a time with room for
+ * `inst_capacity` (Gaussian,tile) instances per chunk. */
+size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk,
+                                long long inst_capacity);
+
+/* scores[k] = sum_{g,c} H_k[g,c] * weight[g,c]   for k in [0,K)
+ * where H_k is the Fisher diagonal of pose k: the grads compute_Hessian
+ * concatenates (C_H = 4: d/dmeans3D(3), d/dopacity(1), gaussian.py:1554-1560;
+ * C_H = 11: + d/dscales(3) + d/drotations(4), gaussian_object.py:2024-2032) with
+ * backward_power = 2 and dL_dpix = grad_scale (1e-3 in the reference, gaussian.py:1549),
+ * and weight = 1/(H_train+lambda) (gaussian.py:1357,1367).
+ * w2c: K row-major 4x4 world-to-camera matrices (the poses AFTER torch.linalg.inv,
+ * gaussian.py:1364); means are moved to the camera frame with them while rotations
+ * stay in the world frame, exactly as the reference does (gaussian.py:1527-1529).
+ * status_dev[0] receives 0 or FB_E_CAPACITY, status_dev[1..2] the instance count (lo,hi)
+ * the largest chunk needed; read it whenever the scores are read.  No host sync inside. */
+int fb_score_candidates(const fb_camera* cam, const fb_map* map,
+                        const float* w2c, int K,
+                        const float* weight, int C_H, float grad_scale,
+                        float* scores, int* status_dev,
+                        void* workspace, size_t workspace_bytes,
+                        int views_per_chunk, long long inst_capacity,
+                        void* stream);
+
+/* H_out[g,c] += sum_k H_k[g,c]   (compute_H_train, gaussian.py:1338-1348).
+ * H_out is [P,C_H], caller-initialised.  Same status convention. */
+int fb_accumulate_hessian(const fb_camera* cam, const fb_map* map,
+                          const float* w2c, int K,
+                          int C_H, float grad_scale,
+                          float* H_out, int* status_dev,
+                          void* workspace, size_t workspace_bytes,
+                          int views_per_chunk, long long inst_capacity,
+                          void* stream);
+
+/* ---- stage 5 ------------------------------------------------------------- */
+
+size_t fb_knn_workspace_bytes(int P);
+/* mean_dist2[i] = mean of the 3 smallest squared distances from point i to any
+ * other point (self excluded by index), FLT_MAX terms if P < 4
+ * (KNN/simple_knn.cu:148-184). */
+int fb_dist2_knn3(int P, const float* points, float* mean_dist2,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* counts[k] = #{ i : z_cam > 0 and 0 <= u < img_w and 0 <= v < img_h } for pose k,
+ * evaluated in float64 like numpy does (tester_navigator.py:160-178).
+ * points: f32 [N,3]; w2c: f64 K x 16 row-major (already inverted on the host);
+ * intr: f64 {fx, fy, cx, cy}.  mask (optional, may be NULL): u8 [K,N]. */
+int fb_count_visible(int N, const float* points, int K, const double* w2c,
+                     const double* intr, int img_w, int img_h,
+                     int* counts, uint8_t* mask, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FISHER_B200_H */

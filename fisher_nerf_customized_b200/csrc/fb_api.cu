@@ -15,6 +15,34 @@ static thread_local int g_last_cuda = 0;
     } while (0)
 #define FB_LAUNCH_CHECK() FB_CUDA(cudaGetLastError())
 
+// ---- optional per-kernel timing (fb_profile_*): CUDA events recorded on the launching stream around
+// every kernel of a class while enabled; read back (with a sync) by fb_profile_read.  Off by default.
+#include <vector>
+enum { FB_K_PREPROCESS = 0, FB_K_SCAN, FB_K_SCATTER, FB_K_SORT, FB_K_RENDER, FB_K_BWD_TILES, FB_K_EXPAND,
+       FB_K_TILE_SCORE, FB_K_FINALIZE, FB_K_KNN, FB_K_VISIBLE, FB_K_CLASSES };
+static const char* const g_class_names[FB_K_CLASSES] = {"k_preprocess", "k_scan_tiles", "k_scatter_keys", "k_sort_tiles",
+    "k_render_fwd", "k_bwd_tiles", "k_expand", "k_tile_score", "k_score_finalize", "k_knn", "k_count_visible"};
+struct ProfRec { int cls; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::vector<cudaEvent_t> g_ev_pool;
+static cudaEvent_t prof_event() {
+    cudaEvent_t e;
+    if (!g_ev_pool.empty()) { e = g_ev_pool.back(); g_ev_pool.pop_back(); return e; }
+    cudaEventCreate(&e);
+    return e;
+}
+struct ProfScope {
+    int cls; cudaStream_t st; cudaEvent_t a;
+    ProfScope(int c, cudaStream_t s) : cls(c), st(s), a(nullptr) {
+        if (g_prof_on) { a = prof_event(); cudaEventRecord(a, st); }
+    }
+    ~ProfScope() {
+        if (a) { cudaEvent_t b = prof_event(); cudaEventRecord(b, st); g_prof.push_back({cls, a, b}); }
+    }
+};
+#define FB_PROF(cls) ProfScope prof_scope__(cls, st)
+
 extern "C" {
 
 const char* fb_error_string(int s) {
@@ -29,7 +57,24 @@ const char* fb_error_string(int s) {
     }
 }
 int fb_last_cuda_error(void) { return g_last_cuda; }
-int fb_version(void) { return 100; }
+int fb_version(void) { return 101; }
+
+int fb_profile_enable(int on) { g_prof_on = on != 0; return FB_OK; }
+int fb_profile_classes(void) { return FB_K_CLASSES; }
+const char* fb_profile_class_name(int cls) { return (cls >= 0 && cls < FB_K_CLASSES) ? g_class_names[cls] : ""; }
+int fb_profile_read(float* ms_total, int* launches) {
+    for (int i = 0; i < FB_K_CLASSES; ++i) { if (ms_total) ms_total[i] = 0.f; if (launches) launches[i] = 0; }
+    for (ProfRec& r : g_prof) {
+        FB_CUDA(cudaEventSynchronize(r.b));
+        float ms = 0.f;
+        FB_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+        if (ms_total) ms_total[r.cls] += ms;
+        if (launches) launches[r.cls] += 1;
+        g_ev_pool.push_back(r.a); g_ev_pool.push_back(r.b);
+    }
+    g_prof.clear();
+    return FB_OK;
+}
 
 size_t fb_geom_bytes(int P) { return geom_layout(P).total; }
 size_t fb_image_bytes(int w, int h) { return image_layout(w, h).total; }

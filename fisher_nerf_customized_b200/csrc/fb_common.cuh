@@ -7,6 +7,14 @@
 //   reference preprocess      DGR/cuda_rasterizer/forward.cu:155-256
 //   reference helpers         DGR/cuda_rasterizer/auxiliary.h:41-97,139-164
 //   GLM mat3*mat3 order       DGR/third_party/glm/glm/detail/type_mat3x3.inl:514-545
+//
+// Rounding.  The reference is compiled with nvcc's default -fmad=true, so which multiplies are
+// fused into FMAs is part of its observable behaviour (it moves radii / tile rectangles / depth
+// key bits by an ulp).  The fused sequence nvcc 12.9 -O3 emits for the reference source was read
+// from its PTX/SASS; it is written out here with explicit __fmul_rn/__fmaf_rn/__fadd_rn so that
+// it cannot drift with compiler heuristics.  Three-term dot products are
+//     t = a1*b1;  t = fma(a0,b0,t);  t = fma(a2,b2,t)        (dot3)
+// and a trailing "+ c" is a separate rounded add.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,18 +32,20 @@ struct M3 {
     float c[3][3];
 };
 
-// (A*B)[col][row] = A[0][row]*B[col][0] (+)= A[1][row]*B[col][1] (+)= A[2][row]*B[col][2]
+__device__ __forceinline__ float dot3(float a0, float b0, float a1, float b1, float a2, float b2) {
+    float t = __fmul_rn(a1, b1);
+    t = __fmaf_rn(a0, b0, t);
+    return __fmaf_rn(a2, b2, t);
+}
+
+// (A*B)[col][row] = A[0][row]*B[col][0] + A[1][row]*B[col][1] + A[2][row]*B[col][2], fused as dot3
 __device__ __forceinline__ M3 m3_mul(const M3& A, const M3& B) {
     M3 R;
 #pragma unroll
     for (int col = 0; col < 3; ++col) {
 #pragma unroll
-        for (int row = 0; row < 3; ++row) {
-            float t = A.c[0][row] * B.c[col][0];
-            t += A.c[1][row] * B.c[col][1];
-            t += A.c[2][row] * B.c[col][2];
-            R.c[col][row] = t;
-        }
+        for (int row = 0; row < 3; ++row)
+            R.c[col][row] = dot3(A.c[0][row], B.c[col][0], A.c[1][row], B.c[col][1], A.c[2][row], B.c[col][2]);
     }
     return R;
 }
@@ -81,24 +91,24 @@ __host__ inline Cam make_cam(const fb_camera* c) {
 // auxiliary.h:58-77 (matrices are consumed column-major: m[0],m[4],m[8],m[12] is row 0)
 __device__ __forceinline__ float3 xform4x3(const float3& p, const float* m) {
     float3 r;
-    r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
-    r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
-    r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
+    r.x = __fadd_rn(m[12], dot3(m[0], p.x, m[4], p.y, m[8], p.z));
+    r.y = __fadd_rn(m[13], dot3(m[1], p.x, m[5], p.y, m[9], p.z));
+    r.z = __fadd_rn(m[14], dot3(m[2], p.x, m[6], p.y, m[10], p.z));
     return r;
 }
 __device__ __forceinline__ float4 xform4x4(const float3& p, const float* m) {
     float4 r;
-    r.x = m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12];
-    r.y = m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13];
-    r.z = m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14];
-    r.w = m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15];
+    r.x = __fadd_rn(m[12], dot3(m[0], p.x, m[4], p.y, m[8], p.z));
+    r.y = __fadd_rn(m[13], dot3(m[1], p.x, m[5], p.y, m[9], p.z));
+    r.z = __fadd_rn(m[14], dot3(m[2], p.x, m[6], p.y, m[10], p.z));
+    r.w = __fadd_rn(m[15], dot3(m[3], p.x, m[7], p.y, m[11], p.z));
     return r;
 }
 
 // auxiliary.h:41-44 -- the literals are double, so ((v + 1.0) * S - 1.0) * 0.5 is evaluated in
 // FP64 and rounded to FP32 once.
 __device__ __forceinline__ float ndc_to_pix_exact(float v, int S) {
-    double d = (((double)v + 1.0) * (double)S - 1.0) * 0.5;
+    double d = __dmul_rn(__fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0), 0.5);   // one fma.rn.f64, as compiled
     return (float)d;
 }
 
@@ -115,10 +125,15 @@ __device__ __forceinline__ void tile_rect(float px, float py, int max_radius, in
 __device__ __forceinline__ void rot_scale_M(const float3& scale, float mod, const float4& q, M3& R, float3& s, M3& M) {
     float r = q.x, x = q.y, y = q.z, z = q.w;
     // GLM constructor fills columns: (a,b,c) is column 0.
-    R.c[0][0] = 1.f - 2.f * (y * y + z * z); R.c[0][1] = 2.f * (x * y - r * z); R.c[0][2] = 2.f * (x * z + r * y);
-    R.c[1][0] = 2.f * (x * y + r * z); R.c[1][1] = 1.f - 2.f * (x * x + z * z); R.c[1][2] = 2.f * (y * z - r * x);
-    R.c[2][0] = 2.f * (x * z - r * y); R.c[2][1] = 2.f * (y * z + r * x); R.c[2][2] = 1.f - 2.f * (x * x + y * y);
-    s.x = mod * scale.x; s.y = mod * scale.y; s.z = mod * scale.z;
+    // as compiled: yy+zz is mul,mul,add; xx+zz and xx+yy are fma(x,x,zz), fma(x,x,yy); products shared
+    // between entries are rounded once.
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xy = __fmul_rn(x, y), rz = __fmul_rn(r, z), xz = __fmul_rn(x, z), ry = __fmul_rn(r, y);
+    const float yz = __fmul_rn(y, z), rx = __fmul_rn(r, x);
+    R.c[0][0] = __fsub_rn(1.f, 2.f * __fadd_rn(yy, zz)); R.c[0][1] = 2.f * __fsub_rn(xy, rz); R.c[0][2] = 2.f * __fadd_rn(ry, xz);
+    R.c[1][0] = 2.f * __fadd_rn(xy, rz); R.c[1][1] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, zz)); R.c[1][2] = 2.f * __fsub_rn(yz, rx);
+    R.c[2][0] = 2.f * __fsub_rn(xz, ry); R.c[2][1] = 2.f * __fadd_rn(rx, yz); R.c[2][2] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, yy));
+    s.x = __fmul_rn(mod, scale.x); s.y = __fmul_rn(mod, scale.y); s.z = __fmul_rn(mod, scale.z);
     M3 S;
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -150,12 +165,13 @@ __device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const
     const float limy = 1.3f * cam.tanfovy;
     o.txtz = t.x / t.z;
     o.tytz = t.y / t.z;
-    t.x = fminf(limx, fmaxf(-limx, o.txtz)) * t.z;
-    t.y = fminf(limy, fmaxf(-limy, o.tytz)) * t.z;
+    t.x = __fmul_rn(fminf(limx, fmaxf(-limx, o.txtz)), t.z);
+    t.y = __fmul_rn(fminf(limy, fmaxf(-limy, o.tytz)), t.z);
     o.t = t;
     M3 J;
-    J.c[0][0] = cam.focal_x / t.z; J.c[0][1] = 0.f; J.c[0][2] = -(cam.focal_x * t.x) / (t.z * t.z);
-    J.c[1][0] = 0.f; J.c[1][1] = cam.focal_y / t.z; J.c[1][2] = -(cam.focal_y * t.y) / (t.z * t.z);
+    const float tzz = __fmul_rn(t.z, t.z);
+    J.c[0][0] = cam.focal_x / t.z; J.c[0][1] = 0.f; J.c[0][2] = -__fmul_rn(cam.focal_x, t.x) / tzz;
+    J.c[1][0] = 0.f; J.c[1][1] = cam.focal_y / t.z; J.c[1][2] = -__fmul_rn(cam.focal_y, t.y) / tzz;
     J.c[2][0] = 0.f; J.c[2][1] = 0.f; J.c[2][2] = 0.f;
     M3 Wm;
     Wm.c[0][0] = cam.view[0]; Wm.c[0][1] = cam.view[4]; Wm.c[0][2] = cam.view[8];
@@ -167,9 +183,9 @@ __device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const
     V.c[1][0] = cov6[1]; V.c[1][1] = cov6[3]; V.c[1][2] = cov6[4];
     V.c[2][0] = cov6[2]; V.c[2][1] = cov6[4]; V.c[2][2] = cov6[5];
     M3 cov = m3_mul(m3_mul(m3_T(o.T), m3_T(V)), o.T);
-    o.a = cov.c[0][0] + 0.3f;
+    o.a = __fadd_rn(cov.c[0][0], 0.3f);
     o.b = cov.c[0][1];
-    o.c = cov.c[1][1] + 0.3f;
+    o.c = __fadd_rn(cov.c[1][1], 0.3f);
     return o;
 }
 
@@ -190,17 +206,19 @@ __device__ __forceinline__ int project_splat(const float3& p_orig, const float* 
     float3 p_view = xform4x3(p_orig, cam.view);
     if (p_view.z <= 0.001f) { culled_near = 1; return 0; }
     float4 p_hom = xform4x4(p_orig, cam.proj);
-    float p_w = 1.0f / (p_hom.w + 0.0000001f);
-    float projx = p_hom.x * p_w, projy = p_hom.y * p_w;
+    float p_w = 1.0f / __fadd_rn(p_hom.w, 0.0000001f);
+    float projx = __fmul_rn(p_hom.x, p_w), projy = __fmul_rn(p_hom.y, p_w);
     Cov2D c2 = cov2d(p_orig, cam, cov6);
-    float det = (c2.a * c2.c - c2.b * c2.b);
+    // as compiled: mul, mul, sub (no fusion) for the determinant and for mid*mid - det
+    float det = __fsub_rn(__fmul_rn(c2.a, c2.c), __fmul_rn(c2.b, c2.b));
     if (det == 0.0f) return 0;
     float det_inv = 1.f / det;
-    s.ca = c2.c * det_inv; s.cb = -c2.b * det_inv; s.cc = c2.a * det_inv;
-    float mid = 0.5f * (c2.a + c2.c);
-    float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-    float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
-    float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+    s.ca = __fmul_rn(c2.c, det_inv); s.cb = __fmul_rn(-c2.b, det_inv); s.cc = __fmul_rn(c2.a, det_inv);
+    float mid = __fmul_rn(0.5f, __fadd_rn(c2.a, c2.c));
+    float root = sqrtf(fmaxf(0.1f, __fsub_rn(__fmul_rn(mid, mid), det)));
+    float lambda1 = __fadd_rn(mid, root);
+    float lambda2 = __fsub_rn(mid, root);
+    float my_radius = ceilf(__fmul_rn(3.f, sqrtf(fmaxf(lambda1, lambda2))));
     s.px = ndc_to_pix_exact(projx, cam.W);
     s.py = ndc_to_pix_exact(projy, cam.H);
     s.radius = (int)my_radius;
@@ -208,6 +226,13 @@ __device__ __forceinline__ int project_splat(const float3& p_orig, const float* 
     if ((s.x1 - s.x0) * (s.y1 - s.y0) == 0) return 0;
     s.depth = p_view.z;
     return 1;
+}
+
+// Exponent of a (pixel, Gaussian) pair, forward.cu:341 / backward.cu:968:
+//   -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy   as compiled:  q = fma(dx, dx*A, dy*(dy*C));  q*(-0.5f) - dy*(dx*B)
+__device__ __forceinline__ float pair_power(float A, float B, float C, float dx, float dy) {
+    const float q = __fmaf_rn(dx, __fmul_rn(dx, A), __fmul_rn(dy, __fmul_rn(dy, C)));
+    return __fsub_rn(__fmul_rn(q, -0.5f), __fmul_rn(dy, __fmul_rn(dx, B)));
 }
 
 }  // namespace fb

@@ -69,7 +69,7 @@ __device__ __forceinline__ void tile_backward(BwdSmem& sm, const u64* sorted, in
                 const float4 xy = sm.sb.xyo[j];
                 const float4 co = sm.sb.con[j];
                 const float dx = xy.x - pxf, dy = xy.y - pyf;
-                const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+                const float power = pair_power(co.x, co.y, co.z, dx, dy);
                 if (power <= 0.0f) {
                     const float G = expf(power);
                     const float alpha = fminf(0.99f, xy.w * G);

@@ -53,15 +53,15 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_render_fwd(Bins bins, Cam cam, 
             float4 xy = sb.xyo[j];
             float4 co = sb.con[j];
             float dx = xy.x - pxf, dy = xy.y - pyf;
-            float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+            float power = pair_power(co.x, co.y, co.z, dx, dy);
             if (power > 0.0f) continue;
             float alpha = fminf(0.99f, xy.w * expf(power));
             if (alpha < 1.0f / 255.0f) continue;
-            float test_T = T * (1 - alpha);
+            float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
             if (test_T < 0.0001f) { done = true; continue; }
             const float* f = features + 3 * (size_t)sb.gid[j];
 #pragma unroll
-            for (int ch = 0; ch < 3; ++ch) C[ch] += f[ch] * alpha * T;
+            for (int ch = 0; ch < 3; ++ch) C[ch] = __fmaf_rn(T, __fmul_rn(alpha, f[ch]), C[ch]);   // as compiled
             if (T > 0.5f && (double)test_T < 0.5) D = xy.z;
             T = test_T;
             last_contributor = contributor;
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_render_fwd(Bins bins, Cam cam, 
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
 #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) out_color[(size_t)ch * H * W + pix_id] = C[ch] + T * cam.bg[ch];
+        for (int ch = 0; ch < 3; ++ch) out_color[(size_t)ch * H * W + pix_id] = __fmaf_rn(T, cam.bg[ch], C[ch]);
         out_depth[pix_id] = D;
     }
 }

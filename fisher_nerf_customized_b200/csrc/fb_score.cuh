@@ -75,11 +75,11 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
             const float4 xy = sb.xyo[j];
             const float4 co = sb.con[j];
             const float dx = xy.x - pxf, dy = xy.y - pyf;
-            const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+            const float power = pair_power(co.x, co.y, co.z, dx, dy);
             if (power > 0.0f) continue;
             const float alpha = fminf(0.99f, xy.w * expf(power));
             if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
+            const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
             if (test_T < 0.0001f) { done = true; continue; }
             T = test_T;
             last = base + j + 1;
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
             const float4 xy = sb.xyo[j];
             const float4 co = sb.con[j];
             const float dx = xy.x - pxf, dy = xy.y - pyf;
-            const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+            const float power = pair_power(co.x, co.y, co.z, dx, dy);
             if (power > 0.0f) continue;
             const float G = expf(power);
             const float alpha = fminf(0.99f, xy.w * G);

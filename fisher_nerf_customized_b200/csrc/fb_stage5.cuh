@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(128) k_knn_query(int P, KnnWs ws, float* __res
                         const float4 o = ws.sorted[k];
                         if (__float_as_int(o.w) == my_idx) continue;
                         const float dx = o.x - me.x, dy = o.y - me.y, dz = o.z - me.z;
-                        k3_update(dx * dx + dy * dy + dz * dz, best);
+                        k3_update(dot3(dx, dx, dy, dy, dz, dz), best);
                     }
                 } else {
                     // interior row: only the two end cells belong to the shell
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(128) k_knn_query(int P, KnnWs ws, float* __res
                             const float4 o = ws.sorted[k];
                             if (__float_as_int(o.w) == my_idx) continue;
                             const float dx = o.x - me.x, dy = o.y - me.y, dz = o.z - me.z;
-                            k3_update(dx * dx + dy * dy + dz * dz, best);
+                            k3_update(dot3(dx, dx, dy, dy, dz, dz), best);
                         }
                     }
                 }

@@ -240,3 +240,34 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                                    self.raster_settings, self.backward_power)
+
+
+def debug_export(raster_settings, P, num_rendered, geomBuffer, binningBuffer, imgBuffer):
+    """Parity-test introspection (fb_debug_export): the private per-call state translated into the
+    reference's vocabulary (GeometryState / BinningState / ImageState, rasterizer_impl.h:30-70) as numpy."""
+    rs = raster_settings
+    L = _lib.lib()
+    H, W = int(rs.image_height), int(rs.image_width)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    dev = geomBuffer.device
+    cam = _camera(rs.bg, rs.scale_modifier, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, rs.sh_degree, 0,
+                  rs.campos, rs.prefiltered)
+    R = int(num_rendered)
+    out = dict(tiles_touched=torch.zeros(P, dtype=torch.int32, device=dev), depths=torch.zeros(P, device=dev),
+               means2D=torch.zeros((P, 2), device=dev), conic_opacity=torch.zeros((P, 4), device=dev),
+               ranges=torch.zeros((tiles, 2), dtype=torch.int32, device=dev), final_T=torch.zeros(H * W, device=dev),
+               n_contrib=torch.zeros(H * W, dtype=torch.int32, device=dev),
+               point_list=torch.zeros(max(R, 1), dtype=torch.int32, device=dev),
+               point_keys=torch.zeros(max(R, 1), dtype=torch.int64, device=dev))
+    _lib.check(L.fb_debug_export(C.byref(cam), P, R, geomBuffer.data_ptr(), imgBuffer.data_ptr(),
+                                 _ptr(binningBuffer) if R > 0 else None, out["tiles_touched"].data_ptr(),
+                                 out["depths"].data_ptr(), out["means2D"].data_ptr(), out["conic_opacity"].data_ptr(),
+                                 out["ranges"].data_ptr(), out["final_T"].data_ptr(), out["n_contrib"].data_ptr(),
+                                 out["point_list"].data_ptr(), out["point_keys"].data_ptr(), _stream()), "debug_export")
+    res = {k: v.cpu().numpy() for k, v in out.items()}
+    res["tiles_touched"] = res["tiles_touched"].view("uint32")
+    res["ranges"] = res["ranges"].view("uint32")
+    res["n_contrib"] = res["n_contrib"].view("uint32")
+    res["point_list"] = res["point_list"].view("uint32")[:R]
+    res["point_keys"] = res["point_keys"].view("uint64")[:R]
+    return res

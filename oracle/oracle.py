@@ -1,0 +1,285 @@
+"""Python face of the CPU oracle (oracle/fisher_oracle.cpp) -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / reference legs may import this
+module, and only as the checker.  The product package never does.
+
+Parity status: the reference has no tests or fixtures for this path; the oracle
+is pinned against outputs of the reference CUDA extension itself (rebuilt by oracle/build_ref.py,
+run by tests/golden/make_golden.py on the GPU box, fixtures committed under tests/golden/).
+
+Everything is numpy in / numpy out.  Function names follow the reference:
+  rasterize_forward / rasterize_backward   DGR/rasterize_points.cu:35-196
+  compute_Hessian / pose_eval               models/SLAM/gaussian.py:1503-1570, 1354-1375
+  distCUDA2                                 KNN/simple_knn.cu:186-222
+  count_visible_points                      tester_navigator.py:147-180
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "fisher_oracle.cpp")
+LIB = os.path.join(HERE, "liboracle.so")
+
+
+def build(force=False):
+    """g++ -O2 -ffp-contract=off (the file spells out the reference's FMA placement itself)."""
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < os.path.getmtime(SRC):
+        subprocess.run(["g++", "-O2", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC", "-o", LIB, SRC],
+                       check=True)
+    return LIB
+
+
+class Camera(C.Structure):   # field order of fb_camera / oracle Camera
+    _fields_ = [("W", C.c_int), ("H", C.c_int), ("tanfovx", C.c_float), ("tanfovy", C.c_float),
+                ("scale_modifier", C.c_float), ("D", C.c_int), ("M", C.c_int), ("prefiltered", C.c_int),
+                ("bg", C.c_float * 3), ("campos", C.c_float * 3), ("view", C.c_float * 16), ("proj", C.c_float * 16)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(LIB)
+        vp = C.c_void_p
+        L.orc_forward.restype = vp
+        L.orc_forward.argtypes = [vp, C.c_int] + [vp] * 7
+        L.orc_num_rendered.restype = C.c_longlong
+        L.orc_num_rendered.argtypes = [vp]
+        L.orc_prefiltered_trap.restype = C.c_int
+        L.orc_prefiltered_trap.argtypes = [vp]
+        L.orc_export.restype = None
+        L.orc_export.argtypes = [vp] * 16
+        L.orc_backward.restype = C.c_int
+        L.orc_backward.argtypes = [vp, vp, C.c_int] + [vp] * 12
+        L.orc_free.restype = None
+        L.orc_free.argtypes = [vp]
+        L.orc_mark_visible.restype = None
+        L.orc_mark_visible.argtypes = [C.c_int, vp, vp, vp]
+        L.orc_knn3.restype = None
+        L.orc_knn3.argtypes = [C.c_int, vp, vp]
+        L.orc_count_visible.restype = None
+        L.orc_count_visible.argtypes = [C.c_int, vp, C.c_int, vp, C.c_double, C.c_double, C.c_double, C.c_double,
+                                        C.c_int, C.c_int, vp]
+        _lib = L
+    return _lib
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+
+
+def _p(a):
+    return None if a is None or a.size == 0 else a.ctypes.data_as(C.c_void_p)
+
+
+def make_camera(W, H, tanfovx, tanfovy, viewmatrix, projmatrix, bg=(0, 0, 0), scale_modifier=1.0, sh_degree=0, M=0,
+                campos=(0, 0, 0), prefiltered=False):
+    """viewmatrix / projmatrix: the 16 floats exactly as the reference passes them (transposed matrices)."""
+    cam = Camera()
+    cam.W, cam.H, cam.tanfovx, cam.tanfovy = int(W), int(H), float(tanfovx), float(tanfovy)
+    cam.scale_modifier, cam.D, cam.M, cam.prefiltered = float(scale_modifier), int(sh_degree), int(M), int(prefiltered)
+    cam.bg[:] = [float(x) for x in bg]
+    cam.campos[:] = [float(x) for x in campos]
+    cam.view[:] = [float(x) for x in np.asarray(viewmatrix, dtype=np.float32).reshape(-1)]
+    cam.proj[:] = [float(x) for x in np.asarray(projmatrix, dtype=np.float32).reshape(-1)]
+    return cam
+
+
+def setup_camera_np(w, h, k, w2c, near=0.01, far=100):
+    """numpy restatement of setup_camera (models/SLAM/utils/recon_helpers.py:4-32): returns the dict of
+    GaussianRasterizationSettings fields with viewmatrix/projmatrix as the transposed float32 matrices."""
+    fx, fy, cx, cy = float(k[0][0]), float(k[1][1]), float(k[0][2]), float(k[1][2])
+    w2c = np.asarray(w2c, dtype=np.float32)
+    cam_center = np.linalg.inv(w2c)[:3, 3]
+    opengl_proj = np.array([[2 * fx / w, 0.0, -(w - 2 * cx) / w, 0.0],
+                            [0.0, 2 * fy / h, -(h - 2 * cy) / h, 0.0],
+                            [0.0, 0.0, far / (far - near), -(far * near) / (far - near)],
+                            [0.0, 0.0, 1.0, 0.0]], dtype=np.float32)
+    view_t = np.ascontiguousarray(w2c.T)
+    full_proj = (view_t @ opengl_proj.T).astype(np.float32)
+    return dict(image_height=h, image_width=w, tanfovx=w / (2 * fx), tanfovy=h / (2 * fy),
+                bg=np.zeros(3, np.float32), scale_modifier=1.0, viewmatrix=view_t, projmatrix=full_proj, sh_degree=0,
+                campos=cam_center.astype(np.float32), prefiltered=False)
+
+
+def camera_from_settings(rs, M=0):
+    return make_camera(rs["image_width"], rs["image_height"], rs["tanfovx"], rs["tanfovy"], rs["viewmatrix"],
+                       rs["projmatrix"], rs["bg"], rs["scale_modifier"], rs["sh_degree"], M, rs["campos"],
+                       rs["prefiltered"])
+
+
+class Forward:
+    """Result of one oracle forward; holds the native state for backward()."""
+
+    def __init__(self, cam, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                 cov3D_precomp=None):
+        L = lib()
+        self.cam = cam
+        self.P = P = int(np.asarray(means3D).shape[0])
+        self._in = [_f32(means3D), _f32(np.asarray(opacities).reshape(-1)), _f32(shs), _f32(colors_precomp),
+                    _f32(scales), _f32(rotations), _f32(cov3D_precomp)]
+        self._h = L.orc_forward(C.byref(cam), P, *[_p(a) for a in self._in])
+        if not self._h:
+            raise ValueError("oracle: invalid argument combination")
+        self.num_rendered = int(L.orc_num_rendered(self._h))
+        self.prefiltered_trap = bool(L.orc_prefiltered_trap(self._h))
+        W, H = cam.W, cam.H
+        tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        R = self.num_rendered
+        self.radii = np.zeros(P, np.int32)
+        self.tiles_touched = np.zeros(P, np.uint32)
+        self.depths = np.zeros(P, np.float32)
+        self.means2D = np.zeros((P, 2), np.float32)
+        self.cov3D = np.zeros((P, 6), np.float32)
+        self.conic_opacity = np.zeros((P, 4), np.float32)
+        self.rgb = np.zeros((P, 3), np.float32)
+        self.clamped = np.zeros((P, 3), np.uint8)
+        self.keys = np.zeros(R, np.uint64)
+        self.point_list = np.zeros(R, np.uint32)
+        self.ranges = np.zeros((tiles, 2), np.uint32)
+        self.final_T = np.zeros(H * W, np.float32)
+        self.n_contrib = np.zeros(H * W, np.uint32)
+        self.color = np.zeros((3, H, W), np.float32)
+        self.depth = np.zeros((1, H, W), np.float32)
+        L.orc_export(self._h, *[_p(a) for a in (self.radii, self.tiles_touched, self.depths, self.means2D, self.cov3D,
+                                                self.conic_opacity, self.rgb, self.clamped, self.keys, self.point_list,
+                                                self.ranges, self.final_T, self.n_contrib, self.color, self.depth)])
+
+    def backward(self, dL_dpix, power=1, f64=False):
+        """Returns dict of the reference's gradient tensors (float32; with f64=True also the FP64 sums
+        of means3D / opacity / scales / rotations under the keys '*_f64')."""
+        L = lib()
+        P = self.P
+        g = dict(dL_dmeans2D=np.zeros((P, 3), np.float32), dL_dconic=np.zeros((P, 2, 2), np.float32),
+                 dL_dopacity=np.zeros((P, 1), np.float32), dL_dcolors=np.zeros((P, 3), np.float32),
+                 dL_dmeans3D=np.zeros((P, 3), np.float32), dL_dcov3D=np.zeros((P, 6), np.float32),
+                 dL_dscales=np.zeros((P, 3), np.float32), dL_drotations=np.zeros((P, 4), np.float32))
+        d = dict(dL_dmeans3D_f64=np.zeros((P, 3)), dL_dopacity_f64=np.zeros((P, 1)), dL_dscales_f64=np.zeros((P, 3)),
+                 dL_drotations_f64=np.zeros((P, 4)))
+        dpix = _f32(dL_dpix)
+        assert dpix.shape == (3, self.cam.H, self.cam.W)
+        rc = L.orc_backward(self._h, _p(dpix), int(power), *[_p(g[k]) for k in
+                            ("dL_dmeans2D", "dL_dconic", "dL_dopacity", "dL_dcolors", "dL_dmeans3D", "dL_dcov3D",
+                             "dL_dscales", "dL_drotations")],
+                            *[_p(d[k]) if f64 else None for k in
+                              ("dL_dmeans3D_f64", "dL_dopacity_f64", "dL_dscales_f64", "dL_drotations_f64")])
+        if rc != 0:
+            raise NotImplementedError("oracle backward: SH degree > 0 is not restated")
+        if f64:
+            g.update(d)
+        return g
+
+    def close(self):
+        if self._h:
+            lib().orc_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def mark_visible(means3D, viewmatrix):
+    m = _f32(means3D)
+    v = _f32(np.asarray(viewmatrix).reshape(-1))
+    out = np.zeros(m.shape[0], np.uint8)
+    lib().orc_mark_visible(m.shape[0], _p(m), _p(v), _p(out))
+    return out.astype(bool)
+
+
+def distCUDA2(points):
+    p = _f32(points)
+    out = np.zeros(p.shape[0], np.float32)
+    lib().orc_knn3(p.shape[0], _p(p), _p(out))
+    return out
+
+
+def count_visible_points(global_pts, c2w, intrinsics, img_size):
+    """numpy restatement of count_visible_points (tester_navigator.py:147-180), same operations in
+    the same order so that numpy's float64 promotion and BLAS matmul are the ones the reference uses:
+    inv(c2w); (R @ pts.T + t).T; keep z > 0; u = fx*x/z + cx, v = fy*y/z + cy; keep 0<=u<W, 0<=v<H.
+    Returns the visible subset of global_pts, input order."""
+    fx, fy, cx, cy = intrinsics[0, 0], intrinsics[1, 1], intrinsics[0, 2], intrinsics[1, 2]
+    H = W = img_size
+    w2c = np.linalg.inv(c2w)
+    cam_pts = (w2c[:3, :3] @ global_pts.T + w2c[:3, 3:4]).T
+    front = cam_pts[:, 2] > 0
+    cam_pts, kept = cam_pts[front], global_pts[front]
+    u = fx * cam_pts[:, 0] / cam_pts[:, 2] + cx
+    v = fy * cam_pts[:, 1] / cam_pts[:, 2] + cy
+    return kept[(u >= 0) & (u < W) & (v >= 0) & (v < H)]
+
+
+def count_visible_counts_c(global_pts, c2w_list, intrinsics, img_size):
+    """C port of the same test for many poses (counts only); used where numpy would be slow."""
+    p = _f32(global_pts)
+    w2c = np.ascontiguousarray(np.stack([np.linalg.inv(np.asarray(m)) for m in c2w_list]).astype(np.float64))
+    out = np.zeros(w2c.shape[0], np.int32)
+    k = np.asarray(intrinsics)
+    lib().orc_count_visible(p.shape[0], _p(p), w2c.shape[0], w2c.ctypes.data_as(C.c_void_p), float(k[0, 0]),
+                            float(k[1, 1]), float(k[0, 2]), float(k[1, 2]), int(img_size), int(img_size), _p(out))
+    return out
+
+
+# ---- caller arithmetic (models/SLAM/gaussian.py) ----------------------------------------------------
+
+def transform_points_f32(rel_w2c, pts):
+    """(rel_w2c @ [pts|1].T).T[:, :3] in float32 (gaussian.py:1523-1527).  torch evaluates this with
+    an FP32 GEMM over k = 4; a k-sequential FMA accumulation is fma(m3,1,fma(m2,z,fma(m1,y,m0*x)))."""
+    m = np.asarray(rel_w2c, dtype=np.float32)
+    p = np.asarray(pts, dtype=np.float32)
+    out = np.empty_like(p)
+    for r in range(3):
+        acc = (m[r, 0] * p[:, 0]).astype(np.float32)
+        # fused multiply-adds emulated in float64 (exact product, one rounding)
+        acc = (m[r, 1].astype(np.float64) * p[:, 1].astype(np.float64) + acc.astype(np.float64)).astype(np.float32)
+        acc = (m[r, 2].astype(np.float64) * p[:, 2].astype(np.float64) + acc.astype(np.float64)).astype(np.float32)
+        out[:, r] = acc + m[r, 3]
+    return out
+
+
+def compute_Hessian(rs, params, rel_w2c, C_H=4, grad_scale=1e-3, f64=True):
+    """cur_H[P, C_H] of one pose: compute_Hessian(return_points=True), gaussian.py:1503-1570 (C_H = 4:
+    means3D grad (3) + opacity grad (1)); gaussian_object.py:2024-2032 for C_H = 11 (+ scales (3) +
+    rotations (4)).  rs: settings dict from setup_camera_np (identity view matrix in the reference);
+    params: dict(means3D, rgb_colors, rotations (normalised), opacities, scales) in activated form."""
+    cam = camera_from_settings(rs)
+    pts_cam = transform_points_f32(rel_w2c, params["means3D"])
+    fwd = Forward(cam, pts_cam, params["opacities"], colors_precomp=params["rgb_colors"], scales=params["scales"],
+                  rotations=params["rotations"])
+    dpix = np.full((3, cam.H, cam.W), grad_scale, np.float32)
+    g = fwd.backward(dpix, power=2, f64=f64)
+    sfx = "_f64" if f64 else ""
+    cols = [g["dL_dmeans3D" + sfx], g["dL_dopacity" + sfx]]
+    if C_H == 11:
+        cols += [g["dL_dscales" + sfx], g["dL_drotations" + sfx]]
+    H = np.concatenate([c.reshape(fwd.P, -1) for c in cols], axis=1)
+    vis = fwd.radii > 0
+    fwd.close()
+    return H, vis
+
+
+def compute_H_train(rs, params, keyframe_w2c, C_H=4, grad_scale=1e-3):
+    """gaussian.py:1338-1348: sum of per-keyframe Hessians."""
+    H = None
+    for w2c in keyframe_w2c:
+        h, _ = compute_Hessian(rs, params, w2c, C_H, grad_scale)
+        H = h if H is None else H + h
+    return H
+
+
+def pose_eval(rs, params, poses_w2c, H_train_inv, C_H=4, grad_scale=1e-3):
+    """gaussian.py:1362-1370: scores[k] = sum(cur_H_k * H_train_inv)."""
+    out = []
+    for w2c in poses_w2c:
+        h, _ = compute_Hessian(rs, params, w2c, C_H, grad_scale)
+        out.append(float(np.sum(h * np.asarray(H_train_inv, dtype=np.float64))))
+    return np.array(out)

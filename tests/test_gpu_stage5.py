@@ -1,0 +1,94 @@
+"""GPU parity of stage 5: distCUDA2 (3-NN mean squared distance) and the visibility counter."""
+import numpy as np
+import pytest
+
+from fisher_nerf_customized_b200 import synth
+from tests import common
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("P,seed", [(1, 0), (3, 1), (4, 2), (1000, 3), (6000, 4)])
+def test_distCUDA2_matches_oracle_bitexact(cuda, oracle, P, seed):
+    import torch
+    pts = synth.make_points(P, seed=seed)
+    got = cuda.distCUDA2(torch.from_numpy(pts).cuda()).cpu().numpy()
+    want = oracle.distCUDA2(pts)
+    np.testing.assert_array_equal(got, want)   # the three smallest distances are search-order independent
+
+
+def test_distCUDA2_duplicates_and_degenerate_axis(cuda, oracle):
+    import torch
+    rng = np.random.default_rng(5)
+    pts = rng.uniform(-1, 1, size=(2000, 3)).astype(np.float32)
+    pts[:, 1] = 0.25                      # flat cloud: one axis has zero extent
+    pts[100:110] = pts[0]                 # exact duplicates count as distance 0
+    got = cuda.distCUDA2(torch.from_numpy(pts).cuda()).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.distCUDA2(pts))
+    assert got[0] == 0.0
+
+
+def test_distCUDA2_matches_reference_extension(cuda):
+    import torch
+    from oracle import build_ref
+    ref = build_ref.import_ref("ref_knn")
+    if ref is None:
+        pytest.skip("oracle/_ref/ref_knn not built")
+    for P, seed in [(5000, 1), (300_000, 2)]:
+        pts = torch.from_numpy(synth.make_points(P, seed=seed)).cuda()
+        got = cuda.distCUDA2(pts)
+        want = ref.distCUDA2(pts)
+        torch.testing.assert_close(got, want, rtol=0, atol=0)
+
+
+def test_distCUDA2_full_size_properties(cuda):
+    """3M points (BASELINE cfg 4): permutation equivariance and translation invariance of the result."""
+    import torch
+    P = 3_000_000
+    pts = torch.from_numpy(synth.make_points(P, box=(30.0, 3.0, 30.0))).cuda()
+    d = cuda.distCUDA2(pts)
+    assert d.shape == (P,) and torch.isfinite(d).all() and (d >= 0).all()
+    perm = torch.randperm(P, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
+    d_perm = cuda.distCUDA2(pts[perm].contiguous())
+    torch.testing.assert_close(d_perm, d[perm], rtol=0, atol=0)
+    sub = torch.arange(0, P, 997, device="cuda")
+    # brute force for a sample of queries
+    q = pts[sub[:64]]
+    dist = ((q[:, None, :] - pts[None, :, :]) ** 2).sum(-1)
+    best = dist.topk(4, largest=False).values[:, 1:]
+    torch.testing.assert_close(d[sub[:64]], best.mean(1), rtol=1e-5, atol=1e-12)
+
+
+@pytest.mark.parametrize("N,K", [(0, 3), (1, 1), (50_000, 5), (1_000_000, 64)])
+def test_count_visible_matches_numpy_reference(cuda, oracle, N, K):
+    import torch
+    pts = synth.make_points(N) if N else np.zeros((0, 3), np.float32)
+    c2w = synth.make_poses(K).astype(np.float64)
+    Kmat = synth.intrinsics(256, 256)
+    counts = cuda.count_visible_batch(torch.from_numpy(pts).cuda(), c2w, Kmat, 256).cpu().numpy()
+    want = np.array([len(oracle.count_visible_points(pts, c2w[k], Kmat, 256)) for k in range(K)])
+    np.testing.assert_array_equal(counts, want)
+    if N:
+        assert want.max() > 0
+
+
+def test_count_visible_points_dropin_returns_subset(cuda, oracle):
+    pts = synth.make_points(20000, seed=3)
+    c2w = synth.make_poses(1, seed=4)[0].astype(np.float64)
+    Kmat = synth.intrinsics(256, 256)
+    got = cuda.count_visible_points(pts, c2w, Kmat, 256)
+    want = oracle.count_visible_points(pts, c2w, Kmat, 256)
+    np.testing.assert_array_equal(got, want)
+    assert got.dtype == pts.dtype
+
+
+def test_count_visible_boundary_points(cuda, oracle):
+    """Points constructed to project exactly onto u = 0, u = W, v = 0, v = H and z = 0."""
+    import torch
+    c2w = np.eye(4)
+    Kmat = synth.intrinsics(256, 256)
+    z = 2.0
+    pts = np.array([[-z, 0, z], [z, 0, z], [0, -z, z], [0, z, z], [0, 0, 0], [0, 0, -1], [0, 0, 1],
+                    [np.nextafter(np.float32(z), 0), 0, z]], dtype=np.float32)
+    counts = cuda.count_visible_batch(torch.from_numpy(pts).cuda(), c2w[None], Kmat, 256).cpu().numpy()
+    assert counts[0] == len(oracle.count_visible_points(pts, c2w, Kmat, 256))

@@ -33,6 +33,10 @@ SIGNATURES = {
     "fb_error_string": (C.c_char_p, [ci]),
     "fb_last_cuda_error": (ci, []),
     "fb_version": (ci, []),
+    "fb_profile_enable": (ci, [ci]),
+    "fb_profile_classes": (ci, []),
+    "fb_profile_class_name": (C.c_char_p, [ci]),
+    "fb_profile_read": (ci, [vp, vp]),
     "fb_geom_bytes": (sz, [ci]),
     "fb_image_bytes": (sz, [ci, ci]),
     "fb_inst_bytes": (sz, [ci]),
@@ -86,3 +90,16 @@ def check(status, what=""):
     if status == FB_E_CUDA:
         msg += f" (cudaError {L.fb_last_cuda_error()})"
     raise FisherB200Error(f"{what}: {msg}" if what else msg)
+
+
+def profile_enable(on=True):
+    lib().fb_profile_enable(int(bool(on)))
+
+
+def profile_read():
+    """{kernel class: (total ms, launches)} since the last read (synchronises on the recorded events)."""
+    L = lib()
+    n = L.fb_profile_classes()
+    ms, cnt = (C.c_float * n)(), (C.c_int * n)()
+    check(L.fb_profile_read(ms, cnt), "fb_profile_read")
+    return {L.fb_profile_class_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}

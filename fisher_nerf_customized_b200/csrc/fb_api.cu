@@ -138,10 +138,10 @@ int fb_raster_forward_bin(const fb_camera* c, const fb_gaussians* g, void* geom,
     FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 256, st));
     FB_CUDA(cudaMemsetAsync(b.tile_count, 0, (size_t)b.tiles * 4, st));
     FB_CUDA(cudaMemsetAsync(b.total, 0, 256, st));
-    k_preprocess<false, 0><<<(P + 255) / 256, 256, 0, st>>>(to_in(g), cam, nullptr, b, radii,
-                                                           (float*)((char*)geom + GL.rgb), (bool*)((char*)geom + GL.clamped), nullptr);
+    { FB_PROF(FB_K_PREPROCESS); k_preprocess<false, 0><<<(P + 255) / 256, 256, 0, st>>>(to_in(g), cam, nullptr, b, radii,
+                                                           (float*)((char*)geom + GL.rgb), (bool*)((char*)geom + GL.clamped), nullptr); }
     FB_LAUNCH_CHECK();
-    k_scan_tiles<<<1, 1024, 0, st>>>(b);
+    { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
     FB_LAUNCH_CHECK();
     uint32_t tot[4];
     FB_CUDA(cudaMemcpyAsync(tot, b.total, sizeof(tot), cudaMemcpyDeviceToHost, st));
@@ -167,19 +167,19 @@ int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* ge
     ImageLayout IL = image_layout(cam.W, cam.H);
     if (num_rendered > 0) {
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
-        k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam);
+        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
         FB_LAUNCH_CHECK();
         static bool attr_set = false;
         if (!attr_set) {
             FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_KEYS * 8));
             attr_set = true;
         }
-        k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS);
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);
-    k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
-        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth);
+    { FB_PROF(FB_K_RENDER); k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
+        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
     FB_LAUNCH_CHECK();
     return FB_OK;
 }
@@ -212,13 +212,13 @@ int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* rad
     dim3 grid(cam.tiles_x, cam.tiles_y);
     GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations};
     if (power == 2) {
-        k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom);
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
         FB_LAUNCH_CHECK();
-        k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o);
+        { FB_PROF(FB_K_EXPAND); k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     } else {
-        k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom);
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
         FB_LAUNCH_CHECK();
-        k_expand_grads<false><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o);
+        { FB_PROF(FB_K_EXPAND); k_expand_grads<false><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     }
     FB_LAUNCH_CHECK();
     return FB_OK;

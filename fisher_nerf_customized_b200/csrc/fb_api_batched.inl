@@ -33,11 +33,13 @@ __global__ void k_debug_inst(Bins b, uint32_t* point_list, u64* point_keys) {
     }
 }
 
-__global__ void k_status_update(const uint32_t* total, int* status) {
+__global__ void k_status_update(const uint32_t* total, const uint32_t* vis_count, int V, int* status) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
+        for (int v = 0; v < V; ++v) status[4] += (int)vis_count[v];
         if (total[1]) status[0] = FB_E_CAPACITY;
         if ((int)total[0] > status[1]) status[1] = (int)total[0];
         if ((int)total[3] > status[2]) status[2] = (int)total[3];
+        status[3] += (int)total[0];
     }
 }
 __global__ void k_fill(float* p, size_t n, float v) {
@@ -142,7 +144,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes()));
         attr_set = true;
     }
-    FB_CUDA(cudaMemsetAsync(status_dev, 0, 3 * sizeof(int), st));
+    FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4, st));
     GaussIn gi = map_in(map);
     for (int k0 = 0; k0 < K; k0 += V) {
@@ -151,20 +153,20 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
         const float* w2c_k = w2c + (size_t)k0 * 16;
         if (C_H == 4)
-            k_preprocess<true, 4><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight);
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 4><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight); }
         else
-            k_preprocess<true, 11><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight);
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 11><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight); }
         FB_LAUNCH_CHECK();
-        k_scan_tiles<<<1, 1024, 0, st>>>(b);
+        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();
-        k_status_update<<<1, 32, 0, st>>>(b.total, status_dev);
+        k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
-        k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam);
+        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         FB_LAUNCH_CHECK();
-        k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, score_smem_bytes(), st>>>(b, cam, grad_scale, FB_SCORE_SMEM_KEYS,
-                                                                                (float*)(ws + L.partial));
+        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, score_smem_bytes(), st>>>(b, cam, grad_scale, FB_SCORE_SMEM_KEYS,
+                                                                                (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
-        k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0);
+        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0); }
         FB_LAUNCH_CHECK();
     }
     return FB_OK;
@@ -192,7 +194,7 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     const size_t HW = (size_t)cam.W * cam.H;
     float* mom = (float*)(ws + L.recsB);   // P x 16 floats == one view's worth of the scoring-record region
     float* dpix = (float*)(ws + L.dpix);
-    FB_CUDA(cudaMemsetAsync(status_dev, 0, 3 * sizeof(int), st));
+    FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
     FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)cam.tiles_x * cam.tiles_y * 4, st));
     k_fill<<<(unsigned)((3 * HW + 255) / 256), 256, 0, st>>>(dpix, 3 * HW, grad_scale);
@@ -203,21 +205,21 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     for (int k = 0; k < K; ++k) {
         const float* w2c_k = w2c + (size_t)k * 16;
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 4, st));
-        k_preprocess<true, 0><<<(P + 255) / 256, 256, 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr);
+        { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<(P + 255) / 256, 256, 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
         FB_LAUNCH_CHECK();
-        k_scan_tiles<<<1, 1024, 0, st>>>(b);
-        k_status_update<<<1, 32, 0, st>>>(b.total, status_dev);
+        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
+        k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
-        k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam);
-        k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS);
+        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
-                                                   (float*)(ws + L.color), (float*)(ws + L.depth));
-        k_bwd_tiles<true, false><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (const float*)(ws + L.final_T),
-                                                              (const uint32_t*)(ws + L.n_contrib), dpix, mom);
+        { FB_PROF(FB_K_RENDER); k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
+                                                   (float*)(ws + L.color), (float*)(ws + L.depth)); }
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, false><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (const float*)(ws + L.final_T),
+                                                              (const uint32_t*)(ws + L.n_contrib), dpix, mom); }
         FB_LAUNCH_CHECK();
-        if (C_H == 4) k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out);
-        else k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out);
+        if (C_H == 4) { FB_PROF(FB_K_EXPAND); k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }
+        else { FB_PROF(FB_K_EXPAND); k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }
         FB_LAUNCH_CHECK();
     }
     return FB_OK;
@@ -259,7 +261,7 @@ int fb_dist2_knn3(int P, const float* points, float* mean_dist2, void* workspace
     k_scan_sums<<<1, 1024, 0, st>>>(w.blocksum, nb);
     k_scan_add<<<nb, 1024, 0, st>>>(w.cell, n, w.blocksum);
     k_knn_scatter<<<(P + 255) / 256, 256, 0, st>>>(P, points, w);
-    k_knn_query<<<(P + 127) / 128, 128, 0, st>>>(P, w, mean_dist2);
+    { FB_PROF(FB_K_KNN); k_knn_query<<<(P + 127) / 128, 128, 0, st>>>(P, w, mean_dist2); }
     FB_LAUNCH_CHECK();
     return FB_OK;
 }
@@ -275,7 +277,7 @@ int fb_count_visible(int N, const float* points, int K, const double* w2c, const
     if (N == 0) return FB_OK;
     if (!points) return FB_E_INVALID;
     int blocks = (N + 255) / 256; if (blocks > 148 * 8) blocks = 148 * 8;
-    k_count_visible<<<blocks, 256, (size_t)K * (12 * 8 + 4), st>>>(N, points, K, w2c, intr, img_w, img_h, counts, mask);
+    { FB_PROF(FB_K_VISIBLE); k_count_visible<<<blocks, 256, (size_t)K * (12 * 8 + 4), st>>>(N, points, K, w2c, intr, img_w, img_h, counts, mask); }
     FB_LAUNCH_CHECK();
     return FB_OK;
 }

@@ -78,6 +78,8 @@ class FisherScorer:
         self._ws = None
         self._ws_key = None
         self.last_status = None
+        self.last_instances = 0
+        self.last_visible = 0
         self.launches = 0
 
     def _c_cam(self):
@@ -107,7 +109,7 @@ class FisherScorer:
         w2c = _f32c(w2c.to(device=gmap.means3D.device, dtype=torch.float32).reshape(-1, 4, 4))
         K = w2c.shape[0]
         cam, m = self._c_cam(), gmap.c_struct()
-        status = torch.zeros((4,), dtype=torch.int32, device=gmap.means3D.device)
+        status = torch.zeros((8,), dtype=torch.int32, device=gmap.means3D.device)
         while True:
             cap = self._capacity(gmap)
             ws = self._workspace(gmap, cap)
@@ -118,6 +120,8 @@ class FisherScorer:
             self.launches += nchunks * (6 if fn_name == "fb_score_candidates" else 8)
             st = status.tolist()
             self.last_status = st
+            self.last_instances = st[3]   # sum of num_rendered over the poses of this call
+            self.last_visible = st[4]     # sum of (radii > 0) over the poses of this call
             if st[0] == 0:
                 return
             if st[0] == _lib.FB_E_CAPACITY:

@@ -91,6 +91,14 @@ const char* fb_error_string(int status);
 int         fb_last_cuda_error(void);     /* cudaError_t of the last FB_E_CUDA, as int */
 int         fb_version(void);
 
+/* Optional per-kernel timing for bench.py's roofline: while enabled, CUDA events are recorded on the
+ * launching stream around every kernel launch; fb_profile_read synchronises on them, sums the elapsed
+ * milliseconds and launch counts per kernel class (arrays of fb_profile_classes() entries) and resets. */
+int         fb_profile_enable(int on);
+int         fb_profile_classes(void);
+const char* fb_profile_class_name(int cls);
+int         fb_profile_read(float* ms_total, int* launches);
+
 /* ---- single-view drop-in path --------------------------------------------- */
 
 /* Per-call state sizes.  `geom` holds the per-Gaussian state kept for backward
@@ -193,8 +201,10 @@ size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chun
  * w2c: K row-major 4x4 world-to-camera matrices (the poses AFTER torch.linalg.inv,
  * gaussian.py:1364); means are moved to the camera frame with them while rotations
  * stay in the world frame, exactly as the reference does (gaussian.py:1527-1529).
- * status_dev[0] receives 0 or FB_E_CAPACITY, status_dev[1..2] the instance count (lo,hi)
- * the largest chunk needed; read it whenever the scores are read.  No host sync inside. */
+ * status_dev (8 ints): [0] 0 or FB_E_CAPACITY, [1] the instance count the largest chunk needed,
+ * [2] the longest per-tile list seen, [3] total (Gaussian,tile) instances over all K poses
+ * (the reference's num_rendered summed), [4] total visible Gaussians (radii > 0) over all K poses,
+ * [5..7] reserved; read it whenever the scores are read.  No host sync inside. */
 int fb_score_candidates(const fb_camera* cam, const fb_map* map,
                         const float* w2c, int K,
                         const float* weight, int C_H, float grad_scale,

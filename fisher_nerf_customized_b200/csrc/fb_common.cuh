@@ -11,7 +11,7 @@
 // Rounding.  The reference is compiled with nvcc's default -fmad=true, so which multiplies are
 // fused into FMAs is part of its observable behaviour (it moves radii / tile rectangles / depth
 // key bits by an ulp).  The fused sequence nvcc 12.9 -O3 emits for the reference source was read
-// from its PTX/SASS; it is written out here with explicit __fmul_rn/__fmaf_rn/__fadd_rn so that
+// from its SASS (ptxas fuses further than the PTX shows); it is written out here with explicit __fmul_rn/__fmaf_rn/__fadd_rn so that
 // it cannot drift with compiler heuristics.  Three-term dot products are
 //     t = a1*b1;  t = fma(a0,b0,t);  t = fma(a2,b2,t)        (dot3)
 // and a trailing "+ c" is a separate rounded add.
@@ -125,14 +125,14 @@ __device__ __forceinline__ void tile_rect(float px, float py, int max_radius, in
 __device__ __forceinline__ void rot_scale_M(const float3& scale, float mod, const float4& q, M3& R, float3& s, M3& M) {
     float r = q.x, x = q.y, y = q.z, z = q.w;
     // GLM constructor fills columns: (a,b,c) is column 0.
-    // as compiled: yy+zz is mul,mul,add; xx+zz and xx+yy are fma(x,x,zz), fma(x,x,yy); products shared
-    // between entries are rounded once.
+    // as compiled (SASS): of each +/- pair of products one is rounded and shared, the other is fused:
+    //   yy+zz: mul,mul,add;  xx+zz, xx+yy: fma(x,x,zz), fma(x,x,yy);
+    //   xy-/+rz: fma(x,y,-/+rz);  yz-/+rx: fma(y,z,-/+rx);  xz+ry: fma(r,y,xz);  xz-ry: fma(-r,y,xz)
     const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
-    const float xy = __fmul_rn(x, y), rz = __fmul_rn(r, z), xz = __fmul_rn(x, z), ry = __fmul_rn(r, y);
-    const float yz = __fmul_rn(y, z), rx = __fmul_rn(r, x);
-    R.c[0][0] = __fsub_rn(1.f, 2.f * __fadd_rn(yy, zz)); R.c[0][1] = 2.f * __fsub_rn(xy, rz); R.c[0][2] = 2.f * __fadd_rn(ry, xz);
-    R.c[1][0] = 2.f * __fadd_rn(xy, rz); R.c[1][1] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, zz)); R.c[1][2] = 2.f * __fsub_rn(yz, rx);
-    R.c[2][0] = 2.f * __fsub_rn(xz, ry); R.c[2][1] = 2.f * __fadd_rn(rx, yz); R.c[2][2] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, yy));
+    const float rz = __fmul_rn(r, z), xz = __fmul_rn(x, z), rx = __fmul_rn(r, x);
+    R.c[0][0] = __fsub_rn(1.f, 2.f * __fadd_rn(yy, zz)); R.c[0][1] = 2.f * __fmaf_rn(x, y, -rz); R.c[0][2] = 2.f * __fmaf_rn(r, y, xz);
+    R.c[1][0] = 2.f * __fmaf_rn(x, y, rz); R.c[1][1] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, zz)); R.c[1][2] = 2.f * __fmaf_rn(y, z, -rx);
+    R.c[2][0] = 2.f * __fmaf_rn(-r, y, xz); R.c[2][1] = 2.f * __fmaf_rn(y, z, rx); R.c[2][2] = __fsub_rn(1.f, 2.f * __fmaf_rn(x, x, yy));
     s.x = __fmul_rn(mod, scale.x); s.y = __fmul_rn(mod, scale.y); s.z = __fmul_rn(mod, scale.z);
     M3 S;
 #pragma unroll
@@ -209,13 +209,13 @@ __device__ __forceinline__ int project_splat(const float3& p_orig, const float* 
     float p_w = 1.0f / __fadd_rn(p_hom.w, 0.0000001f);
     float projx = __fmul_rn(p_hom.x, p_w), projy = __fmul_rn(p_hom.y, p_w);
     Cov2D c2 = cov2d(p_orig, cam, cov6);
-    // as compiled: mul, mul, sub (no fusion) for the determinant and for mid*mid - det
-    float det = __fsub_rn(__fmul_rn(c2.a, c2.c), __fmul_rn(c2.b, c2.b));
+    // as compiled (SASS): det = fma(a, c, -(b*b)); mid*mid - det = fma(mid, mid, -det)
+    float det = __fmaf_rn(c2.a, c2.c, -__fmul_rn(c2.b, c2.b));
     if (det == 0.0f) return 0;
     float det_inv = 1.f / det;
     s.ca = __fmul_rn(c2.c, det_inv); s.cb = __fmul_rn(-c2.b, det_inv); s.cc = __fmul_rn(c2.a, det_inv);
     float mid = __fmul_rn(0.5f, __fadd_rn(c2.a, c2.c));
-    float root = sqrtf(fmaxf(0.1f, __fsub_rn(__fmul_rn(mid, mid), det)));
+    float root = sqrtf(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
     float lambda1 = __fadd_rn(mid, root);
     float lambda2 = __fsub_rn(mid, root);
     float my_radius = ceilf(__fmul_rn(3.f, sqrtf(fmaxf(lambda1, lambda2))));
@@ -229,10 +229,11 @@ __device__ __forceinline__ int project_splat(const float3& p_orig, const float* 
 }
 
 // Exponent of a (pixel, Gaussian) pair, forward.cu:341 / backward.cu:968:
-//   -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy   as compiled:  q = fma(dx, dx*A, dy*(dy*C));  q*(-0.5f) - dy*(dx*B)
+//   -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy   as compiled (SASS):
+//   q = fma(dx, dx*A, dy*(dy*C));  power = fma(q, -0.5f, -(dy*(dx*B)))
 __device__ __forceinline__ float pair_power(float A, float B, float C, float dx, float dy) {
     const float q = __fmaf_rn(dx, __fmul_rn(dx, A), __fmul_rn(dy, __fmul_rn(dy, C)));
-    return __fsub_rn(__fmul_rn(q, -0.5f), __fmul_rn(dy, __fmul_rn(dx, B)));
+    return __fmaf_rn(q, -0.5f, -__fmul_rn(dy, __fmul_rn(dx, B)));
 }
 
 }  // namespace fb

@@ -57,6 +57,8 @@ class ShardedScorer:
     def score_candidates(self, gmap, w2c, H_train_inv):
         """Returns the full scores[K] on every rank."""
         K = w2c.shape[0]
+        if K == 0:
+            return torch.zeros((0,), dtype=torch.float32, device=gmap.means3D.device)
         lo, hi = shard_bounds(K, self.world, self.rank)
         per = (K + self.world - 1) // self.world if K > 0 else 0
         dev = gmap.means3D.device
@@ -80,4 +82,4 @@ class ShardedScorer:
         H_train_inv = torch.reciprocal(H_train + H_reg_lambda)
         w2c = torch.linalg.inv(poses_c2w.float())
         scores = self.score_candidates(gmap, w2c, H_train_inv)
-        return scores, int(torch.argmax(scores).item())
+        return scores, (int(torch.argmax(scores).item()) if scores.numel() else -1)

@@ -38,15 +38,21 @@ _cam_cache = {}
 
 
 def _host_floats(t, n):
-    key = (t.data_ptr(), t._version, t.device.type, n)
-    v = _cam_cache.get(key)
-    if v is None:
-        v = t.detach().reshape(-1).to(dtype=torch.float32, device="cpu").tolist()
-        if len(v) != n:
-            raise RuntimeError(f"camera tensor must have {n} elements, got {len(v)}")
-        if len(_cam_cache) > 4096:
+    """Cached per tensor OBJECT (weak reference) and in-place version, never per address: a freed camera
+    tensor's address is reused by the allocator."""
+    import weakref
+    ent = _cam_cache.get(id(t))
+    if ent is not None and ent[0]() is t and ent[1] == t._version:
+        return ent[2]
+    v = t.detach().reshape(-1).to(dtype=torch.float32, device="cpu").tolist()
+    if len(v) != n:
+        raise RuntimeError(f"camera tensor must have {n} elements, got {len(v)}")
+    if len(_cam_cache) > 1024:
+        for k in [k for k, e in _cam_cache.items() if e[0]() is None]:
+            del _cam_cache[k]
+        if len(_cam_cache) > 1024:
             _cam_cache.clear()
-        _cam_cache[key] = v
+    _cam_cache[id(t)] = (weakref.ref(t), t._version, v)
     return v
 
 

@@ -17,8 +17,8 @@
 // -fmad=true, so a*b+c*d+e*f is NOT three roundings: nvcc fuses some of the multiplies into
 // FMAs.  For the arithmetic that decides INTEGER outputs (radii, tile rectangles, depth key
 // bits, n_contrib) this file spells out the exact fused sequence that nvcc 12.9 -O3 emits for
-// the reference source (read from the PTX/SASS of the reference's forward.cu built here; ptxas
-// adds no further fusion: the FADD/FMUL counts of the SASS equal the add/mul counts of the PTX).
+// the reference source (read from the SASS of the reference's forward.cu built here -- cuobjdump -sass; ptxas
+// fuses mul+add/sub pairs that the PTX still shows separately, so the PTX alone is not enough).
 // It must therefore be compiled with -ffp-contract=off so that the host compiler adds none of
 // its own.  The observed rule for a three-term dot product  a0*b0 + a1*b1 + a2*b2  is
 //     t = a1*b1;  t = fma(a0, b0, t);  t = fma(a2, b2, t)                      ("dot3")
@@ -113,19 +113,20 @@ inline mat3 mul(const mat3& A, const mat3& B) {
 }
 
 // Rotation matrix of the UN-normalised quaternion (r,x,y,z); DGR/cr/forward.cu:126-138 (fwd) and
-// DGR/cr/backward.cu:415-425 (bwd).  As compiled: y*y+z*z is mul,mul,add; x*x+z*z and x*x+y*y are
-// fma(x,x,z*z) / fma(x,x,y*y); 2.f*(..) is an exact doubling.
+// DGR/cr/backward.cu:415-425 (bwd).  As compiled (SASS): of each +/- pair of products one is rounded and
+// shared, the other fused: yy+zz is mul,mul,add; xx+zz = fma(x,x,zz); xx+yy = fma(x,x,yy);
+// xy-/+rz = fma(x,y,-/+rz); yz-/+rx = fma(y,z,-/+rx); xz+ry = fma(r,y,xz); xz-ry = fma(-r,y,xz).
 inline mat3 quat_R(float r, float x, float y, float z) {
     mat3 R;
-    const float yy = y * y, zz = z * z;
+    const float yy = y * y, zz = z * z, rz = r * z, xz = x * z, rx = r * x;
     R.m[0][0] = 1.f - 2.f * (yy + zz);
-    R.m[0][1] = 2.f * (x * y - r * z);
-    R.m[0][2] = 2.f * (r * y + x * z);
-    R.m[1][0] = 2.f * (x * y + r * z);
+    R.m[0][1] = 2.f * fma_(x, y, -rz);
+    R.m[0][2] = 2.f * fma_(r, y, xz);
+    R.m[1][0] = 2.f * fma_(x, y, rz);
     R.m[1][1] = 1.f - 2.f * fma_(x, x, zz);
-    R.m[1][2] = 2.f * (y * z - r * x);
-    R.m[2][0] = 2.f * (x * z - r * y);
-    R.m[2][1] = 2.f * (r * x + y * z);
+    R.m[1][2] = 2.f * fma_(y, z, -rx);
+    R.m[2][0] = 2.f * fma_(-r, y, xz);
+    R.m[2][1] = 2.f * fma_(y, z, rx);
     R.m[2][2] = 1.f - 2.f * fma_(x, x, yy);
     return R;
 }
@@ -267,15 +268,14 @@ void preprocess(State& s) {
         }
         Cov2DState c2 = cov2d_state(p_orig, s.focal_x, s.focal_y, c.tanfovx, c.tanfovy, cov3D, c.view);
         const float cx = c2.cov.m[0][0], cy = c2.cov.m[0][1], cz = c2.cov.m[1][1];
-        // as compiled: mul, mul, sub (no fusion)
-        const float cxz = cx * cz, cyy = cy * cy;
-        float det = cxz - cyy;
+        // as compiled (SASS): det = fma(x, z, -(y*y)); mid*mid - det = fma(mid, mid, -det)
+        const float cyy = cy * cy;
+        float det = fma_(cx, cz, -cyy);
         if (det == 0.0f) continue;
         float det_inv = 1.f / det;
         float conic[3] = {cz * det_inv, -cy * det_inv, cx * det_inv};
         float mid = 0.5f * (cx + cz);
-        const float mm = mid * mid;
-        float disc = std::max(0.1f, mm - det);
+        float disc = std::max(0.1f, fma_(mid, mid, -det));
         float lambda1 = mid + std::sqrt(disc);
         float lambda2 = mid - std::sqrt(disc);
         float my_radius = std::ceil(3.f * std::sqrt(std::max(lambda1, lambda2)));
@@ -343,14 +343,13 @@ void bin_and_sort(State& s) {
 
 // The pair exponent of renderCUDA / renderCUDAFused (forward.cu:341, backward.cu:968), fused as
 // nvcc compiles it:  -0.5f*(A*dx*dx + C*dy*dy) - B*dx*dy  ->
-//   q = fma(dx, dx*A, dy*(dy*C));  power = q*(-0.5f) - dy*(dx*B)
+//   q = fma(dx, dx*A, dy*(dy*C));  power = fma(q, -0.5f, -(dy*(dx*B)))      (SASS)
 inline float pair_power(float A, float B, float C, float dx, float dy) {
     const float t0 = dx * A;
     const float t1 = dy * (dy * C);
     const float q = fma_(dx, t0, t1);
-    const float h = q * -0.5f;
     const float t2 = dy * (dx * B);
-    return h - t2;
+    return fma_(q, -0.5f, -t2);
 }
 
 // renderCUDA<3>  DGR/cr/forward.cu:261-393.  One pixel at a time; the batch/`done` voting of the

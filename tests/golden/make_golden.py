@@ -1,0 +1,124 @@
+"""Generate the golden fixtures under tests/golden/ from THE REFERENCE ITSELF.
+
+  python tests/golden/make_golden.py gpu   # on the GPU box: runs the unmodified reference CUDA extensions
+                                           # (oracle/_ref/ref_dgr, ref_knn; built by oracle/build_ref.py from
+                                           # /root/reference) on seeded inputs -> gpurun_out/golden/*.npz
+  python tests/golden/make_golden.py cpu   # in the build container: executes the reference's own numpy
+                                           # count_visible_points, taken from /root/reference/tester_navigator.py
+                                           # by AST (the module itself imports habitat and cannot be imported)
+
+Inputs are NOT stored: they are regenerated from the seeds by tests/common.py / synth.py; each fixture
+records the seed and shape it was made with.  The fixtures pin the CPU oracle (tests/test_oracle.py) and
+are compared with the CUDA path in the -m gpu tests.
+"""
+import ast
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+RASTER_CASES = [   # name, P, W, H, seed, identity view?
+    ("raster_a", 2500, 64, 64, 101, True),
+    ("raster_b", 4000, 96, 80, 102, False),
+]
+KNN_CASES = [("knn_a", 5000, 201), ("knn_b", 3, 202), ("knn_c", 4, 203)]
+VIS_CASES = [("vis_a", 200_000, 16, 301)]
+
+
+def _img_state(img, HW):
+    """ImageState::fromChunk (DGR/cuda_rasterizer/rasterizer_impl.cu:177-185): accum_alpha f32[N],
+    n_contrib u32[N], ranges uint2[N], each 128-byte aligned from the (aligned) chunk base."""
+    import torch
+    base = img.data_ptr()
+
+    def al(p):
+        return (p + 127) // 128 * 128
+    o0 = al(base) - base
+    accum = img[o0:o0 + 4 * HW].view(torch.float32)
+    o1 = al(base + o0 + 4 * HW) - base
+    ncon = img[o1:o1 + 4 * HW].view(torch.int32)
+    o2 = al(base + o1 + 4 * HW) - base
+    ranges = img[o2:o2 + 8 * HW].view(torch.int32)
+    return accum.cpu().numpy(), ncon.cpu().numpy().view(np.uint32), ranges.cpu().numpy().view(np.uint32)
+
+
+def gpu(out_dir):
+    import torch
+    from oracle import build_ref, oracle as O
+    from tests import common
+    from fisher_nerf_customized_b200 import synth
+    os.makedirs(out_dir, exist_ok=True)
+    dgr, knn = build_ref.import_ref("ref_dgr"), build_ref.import_ref("ref_knn")
+    assert dgr is not None and knn is not None, "oracle/_ref not built"
+    e = torch.Tensor([])
+    for name, P, W, H, seed, ident in RASTER_CASES:
+        sc = common.random_view_scene(P, seed, W, H)
+        w2c = np.eye(4, dtype=np.float32) if ident else common.look_at_w2c((0.3, -0.2, -0.5), (0.1, 0.0, 3.0))
+        rs = O.setup_camera_np(W, H, common.K_for(W, H), w2c)
+        t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+        bg = torch.zeros(3, device="cuda")
+        view = torch.from_numpy(rs["viewmatrix"]).cuda().unsqueeze(0)
+        proj = torch.from_numpy(rs["projmatrix"]).cuda().unsqueeze(0)
+        campos = torch.from_numpy(rs["campos"]).cuda()
+        R, color, radii, geom, binning, img, depth = dgr.rasterize_gaussians(
+            bg, t["means3D"], t["rgb_colors"], t["opacities"], t["scales"], t["rotations"], 1.0, e, view, proj,
+            rs["tanfovx"], rs["tanfovy"], H, W, e, 0, campos, False)
+        final_T, n_contrib, ranges = _img_state(img, H * W)
+        tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        out = dict(P=P, W=W, H=H, seed=seed, ident=ident, num_rendered=R, color=color.cpu().numpy(),
+                   radii=radii.cpu().numpy(), depth=depth.cpu().numpy(), final_T=final_T, n_contrib=n_contrib,
+                   ranges=ranges[:2 * tiles].reshape(tiles, 2))
+        rng = np.random.default_rng(seed)
+        dpix1 = (rng.normal(size=(3, H, W)) * 1e-3).astype(np.float32)
+        for power, dpix in ((1, dpix1), (2, np.full((3, H, W), 1e-3, np.float32))):
+            g = dgr.rasterize_gaussians_backward(bg, t["means3D"], radii, t["rgb_colors"], t["scales"], t["rotations"],
+                                                 1.0, e, view, proj, rs["tanfovx"], rs["tanfovy"],
+                                                 torch.from_numpy(dpix).cuda(), e, 0, campos, geom, R, binning, img, power)
+            names = ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+                     "dL_drotations")
+            for n, v in zip(names, g):
+                if n != "dL_dsh":
+                    out[f"p{power}_{n}"] = v.cpu().numpy()
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), **out)
+        print(name, "R", R, "visible", int((radii > 0).sum()))
+    for name, P, seed in KNN_CASES:
+        pts = synth.make_points(P, seed=seed)
+        d = knn.distCUDA2(torch.from_numpy(pts).cuda()).cpu().numpy()
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), P=P, seed=seed, dist2=d)
+        print(name, d[:3])
+
+
+def _reference_count_visible_points():
+    src = open("/root/reference/tester_navigator.py").read()
+    tree = ast.parse(src)
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "count_visible_points")
+    ns = {"np": np}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "tester_navigator.py", "exec"), ns)
+    return ns["count_visible_points"]
+
+
+def cpu(out_dir):
+    from fisher_nerf_customized_b200 import synth
+    os.makedirs(out_dir, exist_ok=True)
+    ref_fn = _reference_count_visible_points()
+    for name, N, K, seed in VIS_CASES:
+        pts = synth.make_points(N, seed=seed)
+        c2w = synth.make_poses(K, seed=seed + 1).astype(np.float64)
+        Kmat = synth.intrinsics(256, 256)
+        counts = np.array([len(ref_fn(pts, c2w[k], Kmat, 256)) for k in range(K)], dtype=np.int64)
+        first = ref_fn(pts, c2w[0], Kmat, 256)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), N=N, K=K, seed=seed, counts=counts,
+                            first_pose_checksum=np.float64(first.astype(np.float64).sum()), first_pose_n=len(first))
+        print(name, counts)
+
+
+if __name__ == "__main__":
+    mode = sys.argv[1]
+    if mode == "gpu":
+        gpu(os.path.join(ROOT, "gpurun_out", "golden"))
+    else:
+        cpu(HERE)

@@ -1,0 +1,208 @@
+"""CPU: pin the oracle (oracle/fisher_oracle.cpp, oracle/oracle.py) against
+  (i)  golden outputs of the REFERENCE ITSELF (tests/golden/*.npz, made by tests/golden/make_golden.py:
+       the unmodified reference CUDA extensions on a B200, and the reference's own numpy function), and
+  (ii) analytic / self-consistency cases: closed-form single Gaussian, near-plane cull,
+       equal-depth tie order, alpha clamp and T termination, finite differences of the forward for
+       power = 1, power = 2 as an independent sum of squared per-pixel gradients.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from fisher_nerf_customized_b200 import synth
+from tests import common
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _cam(O, W, H, w2c=None):
+    rs = O.setup_camera_np(W, H, common.K_for(W, H), np.eye(4) if w2c is None else w2c)
+    return O.camera_from_settings(rs)
+
+
+def _fwd(O, cam, sc):
+    return O.Forward(cam, sc["means3D"], sc["opacities"], colors_precomp=sc["rgb_colors"], scales=sc["scales"],
+                     rotations=sc["rotations"])
+
+
+@pytest.mark.parametrize("name", ["raster_a", "raster_b"])
+def test_forward_matches_reference_golden(oracle, name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    P, W, H, seed = int(g["P"]), int(g["W"]), int(g["H"]), int(g["seed"])
+    sc = common.random_view_scene(P, seed, W, H)
+    w2c = None if bool(g["ident"]) else common.look_at_w2c((0.3, -0.2, -0.5), (0.1, 0.0, 3.0))
+    f = _fwd(oracle, _cam(oracle, W, H, w2c), sc)
+    # integer / index work: bit-exact against the reference's own output
+    assert f.num_rendered == int(g["num_rendered"])
+    np.testing.assert_array_equal(f.radii, g["radii"])
+    np.testing.assert_array_equal(f.ranges, g["ranges"])
+    # n_contrib / images: the only arithmetic not reproduced bit-for-bit on the CPU is expf (glibc vs CUDA,
+    # <= 2 ulp), which flips an alpha >= 1/255 or T < 1e-4 decision for a vanishing fraction of pixels
+    assert (f.n_contrib != g["n_contrib"]).mean() < 2e-3
+    ok = np.abs(f.color - g["color"]) <= 1e-6 + 1e-4 * np.abs(g["color"])
+    assert ok.mean() > 1 - 2e-3
+    ok = np.abs(f.final_T - g["final_T"]) <= 1e-7 + 1e-4 * np.abs(g["final_T"])
+    assert ok.mean() > 1 - 2e-3
+    assert (f.depth == g["depth"]).mean() > 1 - 2e-3
+
+
+@pytest.mark.parametrize("name", ["raster_a", "raster_b"])
+@pytest.mark.parametrize("power", [1, 2])
+def test_backward_matches_reference_golden(oracle, name, power):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    P, W, H, seed = int(g["P"]), int(g["W"]), int(g["H"]), int(g["seed"])
+    sc = common.random_view_scene(P, seed, W, H)
+    w2c = None if bool(g["ident"]) else common.look_at_w2c((0.3, -0.2, -0.5), (0.1, 0.0, 3.0))
+    f = _fwd(oracle, _cam(oracle, W, H, w2c), sc)
+    rng = np.random.default_rng(seed)
+    dpix = (rng.normal(size=(3, H, W)) * 1e-3).astype(np.float32) if power == 1 else np.full((3, H, W), 1e-3, np.float32)
+    got = f.backward(dpix, power)
+    for n in ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dscales", "dL_drotations"):
+        w = g[f"p{power}_{n}"].reshape(P, -1).astype(np.float64)
+        a = got[n].reshape(P, -1).astype(np.float64)
+        scale = np.abs(w).max()
+        if power == 1:      # signed sums (cancellation): error relative to the tensor's magnitude
+            bad = np.abs(a - w) > 2e-3 * scale + 1e-12
+            assert bad.mean() < 1e-3 and np.abs(a - w).max() <= 2e-2 * scale, (n, bad.sum(), np.abs(a - w).max(), scale)
+        else:               # rtol 1e-3 on Hessian diagonals, all but a vanishing fraction (threshold flips)
+            bad = np.abs(a - w) > 1e-3 * np.abs(w) + 1e-6 * scale
+            assert bad.mean() < 2e-3, (n, bad.sum())
+
+
+@pytest.mark.parametrize("name", ["knn_a", "knn_b", "knn_c"])
+def test_knn_matches_reference_golden(oracle, name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    pts = synth.make_points(int(g["P"]), seed=int(g["seed"]))
+    np.testing.assert_array_equal(oracle.distCUDA2(pts), g["dist2"])   # bit-exact
+
+
+def test_count_visible_matches_reference_golden(oracle):
+    g = np.load(os.path.join(GOLD, "vis_a.npz"))
+    N, K, seed = int(g["N"]), int(g["K"]), int(g["seed"])
+    pts = synth.make_points(N, seed=seed)
+    c2w = synth.make_poses(K, seed=seed + 1).astype(np.float64)
+    Kmat = synth.intrinsics(256, 256)
+    counts = np.array([len(oracle.count_visible_points(pts, c2w[k], Kmat, 256)) for k in range(K)])
+    np.testing.assert_array_equal(counts, g["counts"])
+    first = oracle.count_visible_points(pts, c2w[0], Kmat, 256)
+    assert len(first) == int(g["first_pose_n"]) and first.astype(np.float64).sum() == float(g["first_pose_checksum"])
+    np.testing.assert_array_equal(oracle.count_visible_counts_c(pts, c2w, Kmat, 256), g["counts"])
+
+
+# ---- analytic cases ---------------------------------------------------------------------------------
+
+def _one(mean, scale=0.05, op=0.8, col=(1.0, 0.5, 0.25)):
+    return dict(means3D=np.array([mean], np.float32), rgb_colors=np.array([col], np.float32),
+                rotations=np.array([[1, 0, 0, 0]], np.float32), opacities=np.array([[op]], np.float32),
+                scales=np.full((1, 3), scale, np.float32))
+
+
+def test_single_isotropic_gaussian_closed_form(oracle):
+    W = H = 64
+    z, s, op = 2.0, 0.05, 0.8
+    f = _fwd(oracle, _cam(oracle, W, H), _one((0, 0, z), s, op))
+    focal = W / 2.0
+    var = (s * focal / z) ** 2 + 0.3
+    # isotropic: mid^2 - det = 0 is floored at 0.1 (forward.cu:229-232), so lambda_max = var + sqrt(0.1)
+    assert f.radii[0] == int(np.ceil(3 * np.sqrt(var + np.sqrt(0.1))))
+    np.testing.assert_allclose(f.means2D[0], [(W - 1) / 2.0, (H - 1) / 2.0], atol=1e-5)   # ndc2Pix of 0
+    np.testing.assert_allclose(f.conic_opacity[0], [1 / var, 0, 1 / var, op], rtol=1e-5, atol=1e-7)
+    # pixel (32, 32): d = 31.5 - 32 = -0.5 in both axes
+    alpha = min(0.99, op * np.exp(-0.5 * (0.25 + 0.25) / var))
+    np.testing.assert_allclose(f.color[:, 32, 32], np.array([1.0, 0.5, 0.25]) * alpha, rtol=1e-5)
+    np.testing.assert_allclose(f.final_T[32 * W + 32], 1 - alpha, rtol=1e-5)
+    assert f.depth[0, 32, 32] == 15.0 or f.depth[0, 32, 32] == np.float32(z)   # median latched only if T crosses 0.5
+    assert f.depth[0, 0, 0] == 15.0
+
+
+def test_near_plane_cull_and_tie_order_and_termination(oracle):
+    W = H = 32
+    cam = _cam(oracle, W, H)
+    behind = _one((0, 0, 0.001))
+    assert _fwd(oracle, cam, behind).num_rendered == 0            # p_view.z <= 0.001f is culled
+    assert _fwd(oracle, cam, _one((0, 0, 0.0011), scale=0.0001)).radii[0] > 0
+    # equal depth: ascending Gaussian index (stable sort, emission order)
+    sc = {k: np.concatenate([v, v, v]) for k, v in _one((0, 0, 1.5)).items()}
+    f = _fwd(oracle, cam, sc)
+    for t in range(f.ranges.shape[0]):
+        lst = f.point_list[f.ranges[t, 0]:f.ranges[t, 1]]
+        assert list(lst) == sorted(lst)
+    # opaque stack: alpha clamps at 0.99f, T: 1 -> 0.01; the second one would give 0.01f*0.01f = 9.99999e-5
+    # < 1e-4f, so the pixel terminates BEFORE blending it: one contributor, final T = 1 - 0.99f
+    sc = {k: np.concatenate([v] * 5) for k, v in _one((0, 0, 1.5), scale=0.5, op=1.0).items()}
+    f = _fwd(oracle, cam, sc)
+    c = 16 * W + 16
+    assert f.n_contrib[c] == 1
+    assert f.final_T[c] == np.float32(1) - np.float32(0.99)
+    np.testing.assert_allclose(f.color[:, 16, 16], np.float32(0.99) * np.array([1.0, 0.5, 0.25], np.float32), rtol=1e-6)
+
+
+def test_power1_gradient_matches_finite_differences(oracle):
+    W = H = 32
+    rng = np.random.default_rng(0)
+    sc = common.random_view_scene(40, 7, W, H)
+    sc["means3D"][:, 2] = rng.uniform(1.0, 3.0, 40)
+    sc["means3D"][:, :2] = rng.uniform(-0.8, 0.8, (40, 2))
+    sc["scales"][:] = rng.uniform(0.05, 0.2, (40, 3))
+    cam = _cam(oracle, W, H)
+    dpix = rng.normal(size=(3, H, W)).astype(np.float32)
+    f = _fwd(oracle, cam, sc)
+    g = f.backward(dpix, 1, f64=True)
+
+    def loss(s):
+        return float((_fwd(oracle, cam, s).color.astype(np.float64) * dpix).sum())
+
+    checked = 0
+    for key, gname, idxs in (("opacities", "dL_dopacity_f64", [(3, 0), (11, 0)]), ("means3D", "dL_dmeans3D_f64", [(5, 0), (8, 2)]),
+                             ("scales", "dL_dscales_f64", [(2, 1), (9, 0)]), ("rotations", "dL_drotations_f64", [(4, 1)])):
+        for i, j in idxs:
+            if f.radii[i] == 0:
+                continue
+            an = g[gname][i, j]
+            best = np.inf
+            for h in (3e-3, 1e-3, 3e-4):     # the forward has pops (tile rectangles, 1/255 cut): any clean step will do
+                sp = {k: v.copy() for k, v in sc.items()}
+                sm = {k: v.copy() for k, v in sc.items()}
+                sp[key][i, j] += h
+                sm[key][i, j] -= h
+                fd = (loss(sp) - loss(sm)) / (sp[key][i, j].astype(np.float64) - sm[key][i, j].astype(np.float64))
+                best = min(best, abs(fd - an))
+            assert best <= 1e-2 * abs(an) + 1e-3 * np.abs(g[gname]).max(), (key, i, j, best, an)
+            checked += 1
+    assert checked >= 5
+
+
+def test_power2_is_sum_of_squared_per_pixel_gradients(oracle):
+    """Independent slow path: backward(power=1) with dL_dpix = delta at one pixel and one channel-uniform
+    value gives that pixel's per-pair partials; squaring and summing over pixels must equal backward(power=2)."""
+    W = H = 16
+    sc = common.random_view_scene(12, 3, W, H)
+    sc["means3D"][:, 2] = np.abs(sc["means3D"][:, 2]) + 1.0
+    sc["means3D"][:, :2] *= 0.2
+    cam = _cam(oracle, W, H)
+    f = _fwd(oracle, cam, sc)
+    want = f.backward(np.full((3, H, W), 1e-3, np.float32), 2, f64=True)
+    acc = {k: np.zeros_like(want[k]) for k in ("dL_dmeans3D_f64", "dL_dopacity_f64", "dL_dscales_f64", "dL_drotations_f64")}
+    for py in range(H):
+        for px in range(W):
+            d = np.zeros((3, H, W), np.float32)
+            d[:, py, px] = 1e-3
+            g = f.backward(d, 1, f64=True)
+            for k in acc:
+                acc[k] += g[k].astype(np.float32).astype(np.float64) ** 2
+    for k in acc:
+        np.testing.assert_allclose(acc[k], want[k], rtol=2e-4, atol=1e-6 * np.abs(want[k]).max())
+
+
+def test_argument_validation(oracle):
+    cam = _cam(oracle, 16, 16)
+    sc = _one((0, 0, 1))
+    with pytest.raises(ValueError):
+        oracle.Forward(cam, sc["means3D"], sc["opacities"], scales=sc["scales"], rotations=sc["rotations"])
+    with pytest.raises(ValueError):
+        oracle.Forward(cam, sc["means3D"], sc["opacities"], colors_precomp=sc["rgb_colors"])
+    f = oracle.Forward(cam, np.zeros((0, 3), np.float32), np.zeros((0,), np.float32),
+                       colors_precomp=np.zeros((0, 3), np.float32), scales=np.zeros((0, 3), np.float32),
+                       rotations=np.zeros((0, 4), np.float32))
+    assert f.num_rendered == 0 and not f.color.any()

@@ -1,0 +1,89 @@
+"""CPU, world_size 2 over gloo: the candidate sharding / H_train reduction / score gather logic of
+ShardedScorer with a stand-in local scorer (the product's local scorer is always CUDA)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from fisher_nerf_customized_b200.parallel import ShardedScorer, round_robin, shard_bounds
+
+
+class FakeMap:
+    def __init__(self, P):
+        self.P = P
+        self.means3D = torch.zeros((P, 3))
+
+
+class FakeScorer:
+    """score(pose) = sum(weight) * pose[0,3]; Hessian(pose) = pose[0,3] * ones: linear, so sums are checkable."""
+    C_H = 4
+
+    def score_candidates(self, gmap, w2c, weight):
+        return weight.sum() * w2c[:, 0, 3]
+
+    def compute_H_train(self, gmap, kf):
+        return kf[:, 0, 3].sum() * torch.ones((gmap.P, self.C_H))
+
+
+def _poses(n, off=0.0):
+    p = torch.eye(4).repeat(n, 1, 1)
+    p[:, 0, 3] = torch.arange(n, dtype=torch.float32) + 1 + off
+    return p
+
+
+def _worker(rank, world, port, K, NKF, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        gmap = FakeMap(10)
+        sh = ShardedScorer(FakeScorer())
+        H = sh.compute_H_train(gmap, _poses(NKF))
+        w = torch.full((10, 4), 0.5)
+        s = sh.score_candidates(gmap, _poses(K, 0.25), w)
+        t = [torch.full((3,), float(rank))]
+        sh.broadcast_map(t, src=0)
+        scores, best = sh.pose_eval(gmap, torch.linalg.inv(_poses(K, 0.25)), _poses(NKF), 0.1)
+        out[rank] = (H.numpy(), s.numpy(), t[0].numpy(), scores.numpy(), best)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("K,NKF", [(7, 3), (2, 1), (1, 5), (0, 2)])
+def test_sharded_scorer_world2(K, NKF):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, port, K, NKF, out), nprocs=2, join=True)
+    H_want = float(sum(range(1, NKF + 1)))
+    s_want = 20.0 * (np.arange(K, dtype=np.float32) + 1.25)
+    for r in (0, 1):
+        H, sc, t, scores, best = out[r]
+        np.testing.assert_allclose(H, H_want * np.ones((10, 4)))
+        np.testing.assert_allclose(sc, s_want, rtol=1e-6)
+        assert sc.shape == (K,)
+        np.testing.assert_array_equal(t, np.zeros(3))          # rank 0's map overwrote the replica
+        if K:
+            assert best == K - 1
+    if K:
+        np.testing.assert_array_equal(out[0][3], out[1][3])    # identical scores (and argmax) on every rank
+
+
+def test_partition_helpers():
+    for K in (0, 1, 5, 8, 256, 257):
+        for world in (1, 2, 3, 8):
+            got = []
+            for r in range(world):
+                lo, hi = shard_bounds(K, world, r)
+                assert 0 <= lo <= hi <= K
+                got += list(range(lo, hi))
+            assert got == list(range(K))
+            rr = sorted(sum((round_robin(K, world, r) for r in range(world)), []))
+            assert rr == list(range(K))

@@ -144,8 +144,10 @@ def algorithmic_bytes(cls, P, V, vis, R, HW, tiles):
         return 12.0 * V * tiles
     if cls == "k_scatter_keys":    # stage 2a: write (key,value) 12 B per instance
         return 12.0 * R
-    if cls == "k_tile_score":      # stages 2b + 3 + 4 fused: sort read+write 24 R, fwd gather 32 R, bwd gather 40 R, 44 HW
-        return 96.0 * R + 44.0 * HW * V
+    if cls == "k_sort_tiles":      # stage 2b: sort read + write, 12 B per instance each (8(d))
+        return 24.0 * R
+    if cls == "k_tile_score":      # stages 3 + 4 fused: fwd gather 32 R, bwd gather 40 R, per-pixel state 44 HW
+        return 72.0 * R + 44.0 * HW * V
     if cls == "k_score_finalize":
         return 4.0 * V * tiles + 4.0 * V
     return 0.0

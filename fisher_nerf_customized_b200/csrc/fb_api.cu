@@ -78,7 +78,8 @@ int fb_profile_read(float* ms_total, int* launches) {
 
 size_t fb_geom_bytes(int P) { return geom_layout(P).total; }
 size_t fb_image_bytes(int w, int h) { return image_layout(w, h).total; }
-size_t fb_inst_bytes(int R) { return align_up((size_t)(R > 0 ? R : 1) * 8, 256); }
+// sorted keys + an equally sized ping-pong area for tile lists longer than the shared-memory sort capacity
+size_t fb_inst_bytes(int R) { return 2 * align_up((size_t)(R > 0 ? R : 1) * 8, 256); }
 size_t fb_forward_scratch_bytes(int, int, int, int) { return 256; }
 size_t fb_backward_scratch_bytes(int P, int, int, int) { return align_up((size_t)(P > 0 ? P : 1) * FB_NACC * 4, 256); }
 
@@ -106,14 +107,15 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     char* gb = (char*)geom; char* ib = (char*)image;
     Bins b;
     b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr;
-    b.vis_list = (uint32_t*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
+    b.vis_list = (uint4*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
     b.total = (uint32_t*)(ib + IL.totals);
     b.keys = (u64*)inst; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
 
-#define FB_SORT_SMEM_KEYS 8192
+#define FB_SORT_SMEM_KEYS 4096
+#define FB_SORT_SMEM_BYTES (2 * FB_SORT_SMEM_KEYS * 8)
 
 extern "C" {
 
@@ -122,7 +124,8 @@ int fb_raster_forward_bin(const fb_camera* c, const fb_gaussians* g, void* geom,
                           void* stream_) {
     (void)scratch; (void)scratch_bytes;
     cudaStream_t st = (cudaStream_t)stream_;
-    if (!c || !num_rendered_host || c->image_width <= 0 || c->image_height <= 0) return FB_E_INVALID;
+    if (!c || !num_rendered_host || c->image_width <= 0 || c->image_height <= 0 || c->image_width > 4080 ||
+        c->image_height > 4080) return FB_E_INVALID;   // tile coordinates are packed in 8 bits
     int rc = check_gauss(g);
     if (rc) return rc;
     *num_rendered_host = 0;
@@ -171,10 +174,11 @@ int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* ge
         FB_LAUNCH_CHECK();
         static bool attr_set = false;
         if (!attr_set) {
-            FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_KEYS * 8));
+            FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
             attr_set = true;
         }
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_BYTES, st>>>(
+            b, (u64*)((char*)inst + align_up((size_t)num_rendered * 8, 256)), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);

@@ -3,14 +3,14 @@
 
 namespace fb {
 
-__global__ void k_debug_geom(int P, Cam cam, const GRec* recs, const int* radii_or_null, const uint32_t* vis_list,
+__global__ void k_debug_geom(int P, Cam cam, const GRec* recs, const int* radii_or_null, const uint4* vis_list,
                              uint32_t nvis_cap, const uint32_t* vis_count, uint32_t* tiles_touched, float* depths,
                              float* means2D, float* conic_opacity) {
     // Gaussians that are not visible keep zeros (outputs are pre-zeroed by the host wrapper).
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     (void)radii_or_null; (void)nvis_cap;
     if (i >= vis_count[0]) return;
-    unsigned gid = vis_list[i];
+    unsigned gid = vis_list[i].x;
     if ((int)gid >= P) return;
     GRec r = recs[gid];
     int x0, y0, x1, y1;
@@ -49,14 +49,14 @@ __global__ void k_fill(float* p, size_t n, float v) {
 
 struct ScoreLayout {
     size_t recs, recsB, vis_list, vis_count, tile_count, tile_range, totals, partial, final_T, n_contrib, color, depth,
-        dpix, keys, total;
+        dpix, keys, keys_alt, total;
 };
 static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
     ScoreLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1), Vv = (size_t)(V > 0 ? V : 1);
     size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y), HW = (size_t)W * H;
     L.recs = o;       o = align_up(o + Vv * Pp * sizeof(GRec), 256);
     L.recsB = o;      o = align_up(o + Vv * Pp * 64, 256);
-    L.vis_list = o;   o = align_up(o + Vv * Pp * 4, 256);
+    L.vis_list = o;   o = align_up(o + Vv * Pp * 16, 256);
     L.vis_count = o;  o = align_up(o + Vv * 4, 256);
     L.tile_count = o; o = align_up(o + Vv * tiles * 4, 256);
     L.tile_range = o; o = align_up(o + Vv * tiles * 8, 256);
@@ -68,13 +68,14 @@ static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
     L.depth = o;      o = align_up(o + HW * 4, 256);
     L.dpix = o;       o = align_up(o + HW * 12, 256);
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.total = o;
     return L;
 }
 static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& cam, long long cap) {
     Bins b;
     b.recs = (GRec*)(ws + L.recs); b.recsB = (float4*)(ws + L.recsB);
-    b.vis_list = (uint32_t*)(ws + L.vis_list); b.vis_count = (uint32_t*)(ws + L.vis_count);
+    b.vis_list = (uint4*)(ws + L.vis_list); b.vis_count = (uint32_t*)(ws + L.vis_count);
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.total = (uint32_t*)(ws + L.totals); b.keys = (u64*)(ws + L.keys);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
@@ -87,8 +88,6 @@ static GaussIn map_in(const fb_map* m) {
     return i;
 }
 
-#define FB_SCORE_SMEM_KEYS 4096
-static size_t score_smem_bytes() { return (size_t)FB_SCORE_SMEM_KEYS * 8 + sizeof(ScoreBatch) + 8 * 4 + 16; }
 
 }  // namespace fb
 
@@ -129,6 +128,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
                         int views_per_chunk, long long inst_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
+        c->image_width > 4080 || c->image_height > 4080 ||
         inst_capacity <= 0 || !status_dev) return FB_E_INVALID;
     if (K == 0) return FB_OK;
     const int P = map->P;
@@ -141,7 +141,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
     char* ws = (char*)workspace;
     static bool attr_set = false;
     if (!attr_set) {
-        FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes()));
+        FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         attr_set = true;
     }
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
@@ -163,8 +163,9 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, score_smem_bytes(), st>>>(b, cam, grad_scale, FB_SCORE_SMEM_KEYS,
-                                                                                (float*)(ws + L.partial)); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
+        FB_LAUNCH_CHECK();
+        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, 0, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0); }
         FB_LAUNCH_CHECK();
@@ -188,7 +189,7 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     char* ws = (char*)workspace;
     static bool attr_set = false;
     if (!attr_set) {
-        FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_KEYS * 8));
+        FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         attr_set = true;
     }
     const size_t HW = (size_t)cam.W * cam.H;
@@ -211,7 +212,7 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
         k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_KEYS * 8, st>>>(b, FB_SORT_SMEM_KEYS); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_RENDER); k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
                                                    (float*)(ws + L.color), (float*)(ws + L.depth)); }

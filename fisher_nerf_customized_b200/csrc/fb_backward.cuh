@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
                                                  float* __restrict__ mom, float* __restrict__ H_out) {
     const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= bins.vis_count[0]) return;
-    const unsigned idx = bins.vis_list[i];
+    const unsigned idx = bins.vis_list[i].x;
     float acc[FB_NACC];
     float4* row = reinterpret_cast<float4*>(mom + (size_t)idx * FB_NACC);
 #pragma unroll

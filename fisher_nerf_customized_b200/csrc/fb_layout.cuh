@@ -3,7 +3,10 @@
 // (DGR/cuda_rasterizer/rasterizer_impl.h:30-70); those layouts are opaque to its callers
 // (only round-tripped to backward), so this one is free to be B200-shaped:
 //   * one 32-byte record per visible Gaussian (exactly one DRAM sector): {px,py,depth,opacity |
-//     conic a,b,c, radius}
+//     conic a,b,c, radius} on the drop-in path, {px,py,hx,hy | conic a,b,c, opacity} on the scoring
+//     path (hx,hy = half extents of the alpha >= 1/255 footprint, used for warp-level culling)
+//   * one 16-byte entry per visible Gaussian in a compact list {id, depth bits, packed tile rect}
+//     that the key scatter reads coalesced
 //   * instances are 8-byte keys (depth_bits<<32 | gaussian_id) binned per tile, so a tile's
 //     whole work list is one contiguous segment that a CTA can pull into shared memory.
 #pragma once
@@ -23,7 +26,7 @@ struct __align__(16) GRec {
 struct Bins {
     GRec*     recs;        // [V][P]
     float4*   recsB;       // [V][P][4]  scoring only: {rgb, coef0 | coef1-4 | coef5-8 | coef9-12}
-    uint32_t* vis_list;    // [V][P]   ids of visible Gaussians, unordered
+    uint4*    vis_list;    // [V][P]   visible Gaussians, unordered: {id, depth bits, x0|y0<<8|x1<<16|y1<<24, 0}
     uint32_t* vis_count;   // [V]
     uint32_t* tile_count;  // [V][tiles]   instances per tile (used as a cursor by the scatter)
     uint2*    tile_range;  // [V][tiles]   [start,end) into keys
@@ -43,7 +46,7 @@ static inline __host__ GeomLayout geom_layout(int P) {
     L.recs = o;      o = align_up(o + Pp * sizeof(GRec), 256);
     L.rgb = o;       o = align_up(o + Pp * 3 * sizeof(float), 256);
     L.clamped = o;   o = align_up(o + Pp * 4, 256);
-    L.vis_list = o;  o = align_up(o + Pp * 4, 256);
+    L.vis_list = o;  o = align_up(o + Pp * 16, 256);
     L.vis_count = o; o = align_up(o + 256, 256);
     L.total = o;
     return L;

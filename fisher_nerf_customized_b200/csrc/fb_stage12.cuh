@@ -127,10 +127,29 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
             base = __shfl_sync(0xffffffffu, base, leader);
             if (vis) {
                 unsigned slot = base + __popc(m & ((1u << lane) - 1u));
-                bins.vis_list[(size_t)v * P + slot] = (unsigned)idx;
+                bins.vis_list[(size_t)v * P + slot] =
+                    make_uint4((unsigned)idx, __float_as_uint(s.depth),
+                               (unsigned)s.x0 | ((unsigned)s.y0 << 8) | ((unsigned)s.x1 << 16) | ((unsigned)s.y1 << 24), 0u);
                 GRec r;
-                r.a = make_float4(s.px, s.py, s.depth, opacity);
-                r.b = make_float4(s.ca, s.cb, s.cc, __int_as_float(s.radius));
+                if (CH > 0) {
+                    // scoring layout: half extents of the region where alpha = o*exp(power) can reach 1/255
+                    // (d^T Q d <= 2 ln(255 o)); a pair outside it is skipped by the reference's own
+                    // alpha < 1/255 test (forward.cu:352, backward.cu:974), so culling with it is exact.
+                    // Margin: 1e-3 relative + 0.05 px, far above the rounding of pair_power / expf.
+                    float hx = -1.f, hy = -1.f;                       // o < 1/255: never contributes
+                    if (opacity >= 1.0f / 255.0f) {
+                        const float tau2 = 2.0f * logf(255.0f * opacity) + 1e-3f;
+                        const float dq = s.ca * s.cc - s.cb * s.cb;
+                        hx = sqrtf(tau2 * s.cc / dq) * 1.001f + 0.05f;
+                        hy = sqrtf(tau2 * s.ca / dq) * 1.001f + 0.05f;
+                        if (!(dq > 0.f) || !(hx == hx) || !(hy == hy)) { hx = 3.0e38f; hy = 3.0e38f; }   // never cull
+                    }
+                    r.a = make_float4(s.px, s.py, hx, hy);
+                    r.b = make_float4(s.ca, s.cb, s.cc, opacity);
+                } else {
+                    r.a = make_float4(s.px, s.py, s.depth, opacity);
+                    r.b = make_float4(s.ca, s.cb, s.cc, __int_as_float(s.radius));
+                }
                 bins.recs[(size_t)v * P + idx] = r;
                 if (CH > 0) {
                     float3 sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
@@ -217,7 +236,8 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
 }
 
 // ---- stage 2b: scatter keys into tile segments ----------------------------------------------
-// One thread per visible Gaussian of a view.  tile_count doubles as the cursor (counted down).
+// One thread per visible Gaussian of a view, reading the compact 16-byte entries stage 1 left
+// (coalesced).  tile_count doubles as the cursor (counted down).
 __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     const int v = blockIdx.y;
     uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles;
@@ -230,11 +250,9 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     const unsigned nvis = bins.vis_count[v];
     const uint2* tr = bins.tile_range + (size_t)v * bins.tiles;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvis; i += gridDim.x * blockDim.x) {
-        unsigned gid = bins.vis_list[(size_t)v * bins.P + i];
-        GRec r = bins.recs[(size_t)v * bins.P + gid];
-        int x0, y0, x1, y1;
-        tile_rect(r.a.x, r.a.y, __float_as_int(r.b.w), cam.tiles_x, cam.tiles_y, x0, y0, x1, y1);
-        u64 key = ((u64)__float_as_uint(r.a.z) << 32) | (u64)gid;
+        const uint4 e = bins.vis_list[(size_t)v * bins.P + i];
+        const int x0 = e.z & 0xff, y0 = (e.z >> 8) & 0xff, x1 = (e.z >> 16) & 0xff, y1 = e.z >> 24;
+        u64 key = ((u64)e.y << 32) | (u64)e.x;
         for (int y = y0; y < y1; ++y)
             for (int x = x0; x < x1; ++x) {
                 int t = y * cam.tiles_x + x;
@@ -245,52 +263,117 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
 }
 
 // ---- stage 2c: in-CTA sort of one tile segment ----------------------------------------------
-// Bitonic network in the all-ascending form (first step of each merge flips the partner inside
-// the block, later steps are plain xor), so indices >= n behave as +inf without being stored:
-// works in place on any n, in shared or global memory.
-__device__ __forceinline__ void cta_sort_u64(u64* a, int n) {
-    if (n < 2) return;
-    int np2 = 1;
-    while (np2 < n) np2 <<= 1;
-    for (int k = 2; k <= np2; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < (np2 >> 1); t += blockDim.x) {
-                int lo, hi;
-                if (j == (k >> 1)) {
-                    int blk = t / j, off = t % j;
-                    lo = blk * k + off;
-                    hi = blk * k + k - 1 - off;
-                } else {
-                    lo = ((t / j) * (j << 1)) + (t % j);
-                    hi = lo + j;
-                }
-                if (hi < n) {
-                    u64 x = a[lo], y = a[hi];
-                    if (x > y) { a[lo] = y; a[hi] = x; }
-                }
-            }
-            __syncthreads();
-        }
+// Stable LSD radix sort of the 8-byte keys (depth_bits<<32 | gaussian_id) on the 32 DEPTH bits only
+// (four 8-bit passes; a pass whose digit is the same for every key is skipped), followed by a
+// fix-up that orders the rare runs of bit-identical depths by Gaussian id.  The result is the total
+// order by (depth, id), i.e. exactly the reference's stable (tile|depth) radix sort of keys emitted
+// in ascending Gaussian index (rasterizer_impl.cu:92-108, :304-309).
+// Each warp owns a contiguous chunk of the segment, so ranking keys with __match_any_sync inside
+// the warp and per-(warp, digit) counters across warps keeps every pass stable without atomics.
+// src/dst may be shared or global memory (tiles longer than the shared capacity ping-pong in L2).
+#define FB_RADIX_WARPS (FB_TILE_PIX / 32)
+
+__device__ __forceinline__ bool radix_pass_u64(const u64* __restrict__ src, u64* __restrict__ dst, int n, int shift,
+                                               unsigned (*hist)[256]) {
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    for (int i = tid; i < FB_RADIX_WARPS * 256; i += FB_TILE_PIX) (&hist[0][0])[i] = 0u;
+    __syncthreads();
+    const int chunk = (((n + FB_RADIX_WARPS - 1) / FB_RADIX_WARPS) + 31) & ~31;
+    const int beg = min(n, w * chunk), end = min(n, beg + chunk);
+    for (int i = beg; i < end; i += 32) {
+        const int k = i + lane;
+        const unsigned d = (k < end) ? (unsigned)((src[k] >> shift) & 255ull) : (256u + lane);
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        if (k < end && (m & lt) == 0u) hist[w][d] += __popc(m);
     }
+    __syncthreads();
+    // exclusive scan over (digit major, warp minor); thread d owns digit d
+    __shared__ unsigned wsum[FB_RADIX_WARPS];
+    __shared__ int same_digit;
+    unsigned tot = 0;
+    {
+        unsigned run = 0;
+#pragma unroll
+        for (int ww = 0; ww < FB_RADIX_WARPS; ++ww) { unsigned c = hist[ww][tid]; hist[ww][tid] = run; run += c; }
+        tot = run;
+    }
+    if (tid == 0) same_digit = 0;
+    __syncthreads();
+    if (tot == (unsigned)n) same_digit = 1;
+    unsigned x = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    if (same_digit) return false;          // every key has the same digit: the pass is the identity
+    unsigned base = x - tot;
+#pragma unroll
+    for (int ww = 0; ww < FB_RADIX_WARPS; ++ww) if (ww < w) base += wsum[ww];
+#pragma unroll
+    for (int ww = 0; ww < FB_RADIX_WARPS; ++ww) hist[ww][tid] += base;
+    __syncthreads();
+    for (int i = beg; i < end; i += 32) {
+        const int k = i + lane;
+        u64 key = 0;
+        unsigned d = 256u + lane;
+        if (k < end) { key = src[k]; d = (unsigned)((key >> shift) & 255ull); }
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        unsigned off = 0;
+        if (k < end) off = hist[w][d];
+        __syncwarp();
+        if (k < end && (m & lt) == 0u) hist[w][d] = off + __popc(m);
+        __syncwarp();
+        if (k < end) dst[off + __popc(m & lt)] = key;
+    }
+    __syncthreads();
+    return true;
 }
 
-// Single-view path: sort every tile segment in place (shared memory when it fits).
-__global__ void __launch_bounds__(256) k_sort_tiles(Bins bins, int smem_keys) {
+// Orders runs of equal depth bits by id (full 64-bit compare).  Runs are disjoint, one thread each.
+__device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
+    for (int k = threadIdx.x; k + 1 < n; k += blockDim.x) {
+        const unsigned d = (unsigned)(a[k] >> 32);
+        if ((unsigned)(a[k + 1] >> 32) != d) continue;
+        if (k > 0 && (unsigned)(a[k - 1] >> 32) == d) continue;   // not the start of the run
+        int e = k + 1;
+        while (e < n && (unsigned)(a[e] >> 32) == d) ++e;
+        for (int i = k + 1; i < e; ++i) {                          // insertion sort (runs are short)
+            const u64 x = a[i];
+            int j = i - 1;
+            while (j >= k && a[j] > x) { a[j + 1] = a[j]; --j; }
+            a[j + 1] = x;
+        }
+    }
+    __syncthreads();
+}
+
+// Sort every tile segment of every view of the chunk.  Dynamic shared memory: 2 * smem_keys keys.
+__global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __restrict__ keys_alt, int smem_keys) {
     extern __shared__ u64 s_keys[];
+    __shared__ unsigned hist[FB_RADIX_WARPS][256];
     const int v = blockIdx.y, t = blockIdx.x;
     if (bins.total[1]) return;
-    uint2 r = bins.tile_range[(size_t)v * bins.tiles + t];
-    int n = (int)(r.y - r.x);
+    const uint2 r = bins.tile_range[(size_t)v * bins.tiles + t];
+    const int n = (int)(r.y - r.x);
     if (n < 2) return;
     u64* seg = bins.keys + r.x;
-    if (n <= smem_keys) {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) s_keys[i] = seg[i];
+    u64 *a, *b;
+    const bool in_smem = n <= smem_keys;
+    if (in_smem) {
+        a = s_keys; b = s_keys + smem_keys;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) a[i] = seg[i];
         __syncthreads();
-        cta_sort_u64(s_keys, n);
-        for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = s_keys[i];
     } else {
-        __syncthreads();
-        cta_sort_u64(seg, n);
+        a = seg; b = keys_alt + r.x;
+    }
+#pragma unroll 1
+    for (int pass = 0; pass < 4; ++pass) {
+        if (radix_pass_u64(a, b, n, 32 + 8 * pass, hist)) { u64* tmp = a; a = b; b = tmp; }
+    }
+    fix_equal_depth_runs(a, n);
+    if (a != seg) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = a[i];
     }
 }
 

@@ -99,8 +99,8 @@ class FisherScorer:
 
     def _capacity(self, gmap):
         if self.inst_capacity is None:
-            # a projected Gaussian at 256^2 touches ~1-4 tiles; start generous, grow on overflow
-            self.inst_capacity = max(1 << 20, 2 * gmap.P) * max(1, self.V // 4)
+            # about one (Gaussian, tile) instance per Gaussian and view in indoor maps; grow on overflow
+            self.inst_capacity = max(1 << 20, int(1.5 * gmap.P) * self.V)
         return int(self.inst_capacity)
 
     def _run(self, fn_name, gmap, w2c, extra):
@@ -117,7 +117,7 @@ class FisherScorer:
             _lib.check(rc, fn_name)
             tiles = ((self.cam.image_width + 15) // 16) * ((self.cam.image_height + 15) // 16)
             nchunks = (K + self.V - 1) // self.V if fn_name == "fb_score_candidates" else K
-            self.launches += nchunks * (6 if fn_name == "fb_score_candidates" else 8)
+            self.launches += nchunks * (7 if fn_name == "fb_score_candidates" else 9)
             st = status.tolist()
             self.last_status = st
             self.last_instances = st[3]   # sum of num_rendered over the poses of this call

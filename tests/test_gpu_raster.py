@@ -216,3 +216,25 @@ def test_empty_and_culled_inputs(cuda):
     with pytest.raises(RuntimeError):
         cuda._C.rasterize_gaussians(rs.bg, torch.zeros((4, 2), device="cuda"), z, z, z, z, 1.0, e, rs.viewmatrix,
                                     rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, e, 0, rs.campos, False)
+
+
+def test_long_tile_lists_and_depth_ties(cuda, oracle):
+    """Tile lists longer than the shared-memory sort capacity (4096 keys) and thousands of bit-identical
+    depths: the sorted (key, id) list must still equal the reference order (stable radix sort of keys
+    emitted in ascending Gaussian index)."""
+    import torch
+    W = H = 32
+    P = 9000
+    sc = common.random_view_scene(P, 31, W, H)
+    rng = np.random.default_rng(31)
+    sc["means3D"][:, :2] = rng.uniform(-0.3, 0.3, (P, 2)).astype(np.float32)
+    sc["means3D"][:, 2] = np.round(rng.uniform(1.0, 3.0, P), 1).astype(np.float32)   # 21 distinct depths
+    sc["scales"][:] = 0.02
+    rs = _settings(cuda, torch, W, H)
+    got = _run_cuda(cuda, torch, rs, _to_t(torch, sc), 0, None)
+    ref = _run_oracle(oracle, rs, sc)
+    assert (ref.ranges[:, 1] - ref.ranges[:, 0]).max() > 4096
+    np.testing.assert_array_equal(got["ranges"], ref.ranges)
+    np.testing.assert_array_equal(got["point_keys"], ref.keys)
+    np.testing.assert_array_equal(got["point_list"], ref.point_list)
+    assert (got["n_contrib"] != ref.n_contrib).mean() <= 2e-3

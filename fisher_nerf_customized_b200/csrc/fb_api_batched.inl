@@ -142,6 +142,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
     static bool attr_set = false;
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
         attr_set = true;
     }
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
@@ -165,7 +166,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, 0, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
+        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0); }
         FB_LAUNCH_CHECK();

@@ -20,26 +20,38 @@
 // unchanged; the per-pair arithmetic itself is identical (pair_power / expf as compiled).
 #pragma once
 #include "fb_stage12.cuh"
+#include <cuda_pipeline.h>
 
 namespace fb {
 
 #define FB_WB_X 8      // warp pixel block
 #define FB_WB_Y 4
 
-struct ScoreBatch {
-    float4 a[FB_TILE_PIX];       // px, py, hx, hy
-    float4 b[FB_TILE_PIX];       // conic a, b, c, opacity
-    float4 rb[4][FB_TILE_PIX];   // rgb+coef0 | coef1-4 | coef5-8 | coef9-12   (backward pass only)
+// Warp-autonomous traversal.  There is NO block-wide barrier in the pair loops: each warp walks the
+// tile's sorted list on its own, 32 entries per step (one per lane: key, then the 16-byte {px,py,hx,hy}
+// half of the record, both prefetched one / two steps ahead), culls them against its 8x4 pixel block
+// and appends the survivors, in order, to a 64-entry ring in shared memory that is private to the
+// warp.  The appending lane also starts a cp.async of the rest of the record (conic+opacity, and in the
+// backward pass the 64-byte scoring record) into the ring slot, so by the time 32 survivors have
+// queued up their data has landed; the warp then runs the pair arithmetic for those 32 entries with
+// broadcast shared-memory reads.  Warps of a tile never wait for each other (pixel blocks differ a lot
+// in how many Gaussians touch them), and a warp whose 32 pixels are saturated stops scanning.
+#define FB_WQ 64   // ring entries per warp
+struct WarpQ {
+    float4 a[FB_WQ];       // px, py, list position (as int bits), -
+    float4 b[FB_WQ];       // conic a, b, c, opacity
+    float4 rb[4][FB_WQ];   // rgb+coef0 | coef1-4 | coef5-8 | coef9-12   (backward pass only)
 };
+#define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * (FB_TILE_PIX / 32))
 
 __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, float grad_scale,
                                                            float* __restrict__ partial) {
-    __shared__ ScoreBatch sb;
+    extern __shared__ float4 smem[];
     __shared__ float red[FB_TILE_PIX / 32];
-    __shared__ int s_last;
 
     const int t = blockIdx.x, v = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
     const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
     // warp -> 8x4 pixel block of the tile, lane -> pixel of the block
     const int bx = tx * FB_TILE_X + (warp & 1) * FB_WB_X, by = ty * FB_TILE_Y + (warp >> 1) * FB_WB_Y;
@@ -56,113 +68,144 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
     const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
     const float4* __restrict__ recsB = bins.recsB + (size_t)v * bins.P * 4;
     const u64* __restrict__ sorted = bins.keys + range.x;
+    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[warp];
 
     // (1) transmittance pass (forward.cu:330-379 without colour / depth)
     float T = 1.0f;
     int last = 0;
     bool done = !inside;
-    for (int base = 0; base < n; base += FB_TILE_PIX) {
-        if (__syncthreads_count(done) == FB_TILE_PIX) break;   // also orders reuse of sb
-        const int i = base + tid;
-        if (i < n) {
-            const GRec r = recs[(unsigned)(sorted[i] & 0xffffffffull)];
-            sb.a[tid] = r.a;
-            sb.b[tid] = r.b;
-        }
-        __syncthreads();
-        const int m = min(FB_TILE_PIX, n - base);
-        for (int sub = 0; sub < m; sub += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
-            const int k = sub + lane;
-            bool hit = false;
-            if (k < m) {
-                const float4 a = sb.a[k];
-                hit = (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+    if (!__all_sync(0xffffffffu, done)) {
+        int qn = 0, qh = 0;
+        const int nsteps = (n + 31) >> 5;
+        bool v_nxt = lane < n;
+        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+        for (int step = 0; step <= nsteps; ++step) {
+            unsigned mask = 0u;
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < n;
+                gid_nxt = (unsigned)(key2 & 0xffffffffull);
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+                mask = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(step * 32 + lane), 0.f);
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                }
+                __pipeline_commit();
+                qn += __popc(mask);
             }
-            unsigned mask = __ballot_sync(0xffffffffu, hit);
-            while (mask) {
-                const int j = sub + __ffs(mask) - 1;
-                mask &= mask - 1;
-                if (done) continue;
-                const float4 a = sb.a[j];
-                const float4 co = sb.b[j];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, co.w * expf(power));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-                if (test_T < 0.0001f) { done = true; continue; }
-                T = test_T;
-                last = base + j + 1;
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                for (int h = 0; h < cnt; ++h) {
+                    if (done) continue;
+                    const int slot = (qh + h) & (FB_WQ - 1);
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    if (power > 0.0f) continue;
+                    const float alpha = fminf(0.99f, co.w * expf(power));
+                    if (alpha < 1.0f / 255.0f) continue;
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                    if (test_T < 0.0001f) { done = true; continue; }
+                    T = test_T;
+                    last = __float_as_int(a.z) + 1;
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+                if (__all_sync(0xffffffffu, done)) break;
             }
         }
+        __pipeline_wait_prior(0);
+        __syncwarp();
     }
 
     // (2) back-to-front scoring pass (backward.cu:939-1038)
-    if (tid == 0) s_last = 0;
-    __syncthreads();
     const int warp_last = __reduce_max_sync(0xffffffffu, last);
-    if (lane == 0 && warp_last > 0) atomicMax(&s_last, warp_last);
-    __syncthreads();
-    const int block_last = s_last;
     const float T_final = T;
     const float dpix = inside ? grad_scale : 0.f;
     const float bgdot = (cam.bg[0] + cam.bg[1] + cam.bg[2]) * dpix;
     float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
     float last_alpha = 0.f;
     float score = 0.f;
-    for (int top = block_last; top > 0; top -= FB_TILE_PIX) {
-        const int m = min(FB_TILE_PIX, top);
-        __syncthreads();
-        if (tid < m) {
-            const unsigned gid = (unsigned)(sorted[top - 1 - tid] & 0xffffffffull);
-            const GRec r = recs[gid];
-            sb.a[tid] = r.a;
-            sb.b[tid] = r.b;
-            const float4* rb = recsB + (size_t)gid * 4;
+    if (warp_last > 0) {
+        // step s, lane l looks at list position warp_last-1 - (32 s + l): descending depth order
+        int qn = 0, qh = 0;
+        const int nsteps = (warp_last + 31) >> 5;
+        bool v_nxt = lane < warp_last;
+        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[warp_last - 1 - lane] & 0xffffffffull) : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+        u64 key2 = (32 + lane < warp_last) ? sorted[warp_last - 1 - 32 - lane] : 0ull;
+        for (int step = 0; step <= nsteps; ++step) {
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < warp_last;
+                gid_nxt = (unsigned)(key2 & 0xffffffffull);
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+                key2 = ((step + 2) * 32 + lane < warp_last) ? sorted[warp_last - 1 - (step + 2) * 32 - lane] : 0ull;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+                const unsigned mask = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(warp_last - 1 - (step * 32 + lane)), 0.f);
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                    const float4* rb = recsB + (size_t)gid * 4;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) sb.rb[k][tid] = rb[k];
-        }
-        __syncthreads();
-        // slot j holds list position top-1-j; positions >= warp_last are behind every pixel of this warp
-        for (int sub = max(0, top - warp_last) & ~31; sub < m; sub += 32) {
-            const int k = sub + lane;
-            bool hit = false;
-            if (k < m && top - 1 - k < warp_last) {
-                const float4 a = sb.a[k];
-                hit = (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
-            }
-            unsigned mask = __ballot_sync(0xffffffffu, hit);
-            while (mask) {
-                const int j = sub + __ffs(mask) - 1;
-                mask &= mask - 1;
-                if (top - 1 - j >= last) continue;
-                const float4 a = sb.a[j];
-                const float4 co = sb.b[j];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                if (power > 0.0f) continue;
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, co.w * G);
-                if (alpha < 1.0f / 255.0f) continue;
-                T = T / (1.f - alpha);
-                const float4 r0 = sb.rb[0][j];
-                const float col[3] = {r0.x, r0.y, r0.z};
-                float dL_dalpha = 0.0f;
-#pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                    last_color[ch] = col[ch];
-                    dL_dalpha += (col[ch] - accum_rec[ch]) * dpix;
+                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + k, 16);
                 }
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
-                const float s = G * (co.w * dL_dalpha);
-                const float4 r1 = sb.rb[1][j], r2 = sb.rb[2][j], r3 = sb.rb[3][j];
-                const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-                score += (s * s) * eval_poly13(c, dx, dy);
+                __pipeline_commit();
+                qn += __popc(mask);
+            }
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = (qh + h) & (FB_WQ - 1);
+                    const float4 a = q.a[slot];
+                    if (__float_as_int(a.z) >= last) continue;
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    if (power > 0.0f) continue;
+                    const float G = expf(power);
+                    const float alpha = fminf(0.99f, co.w * G);
+                    if (alpha < 1.0f / 255.0f) continue;
+                    T = T / (1.f - alpha);
+                    const float4 r0 = q.rb[0][slot];
+                    const float col[3] = {r0.x, r0.y, r0.z};
+                    float dL_dalpha = 0.0f;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) {
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = col[ch];
+                        dL_dalpha += (col[ch] - accum_rec[ch]) * dpix;
+                    }
+                    dL_dalpha *= T;
+                    last_alpha = alpha;
+                    dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
+                    const float s = G * (co.w * dL_dalpha);
+                    const float4 r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
+                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
+                    score += (s * s) * eval_poly13(c, dx, dy);
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
             }
         }
     }

@@ -4,7 +4,8 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libfisher_b200.so")
+# FISHER_B200_LIB: developer override used to A/B kernel variants built by scratch/variants.sh
+LIB_PATH = os.environ.get("FISHER_B200_LIB") or os.path.join(_PKG, "libfisher_b200.so")
 
 FB_OK, FB_E_INVALID, FB_E_WORKSPACE, FB_E_CUDA, FB_E_CAPACITY, FB_E_PREFILTERED = 0, -1, -2, -3, -4, -5
 

@@ -109,6 +109,7 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr;
     b.vis_list = (uint4*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
+    b.tile_order = nullptr;
     b.total = (uint32_t*)(ib + IL.totals);
     b.keys = (u64*)inst; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
@@ -139,7 +140,7 @@ int fb_raster_forward_bin(const fb_camera* c, const fb_gaussians* g, void* geom,
     Bins b = single_bins(P, cam, geom, image, nullptr, LLONG_MAX);
     GeomLayout GL = geom_layout(P);
     FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 256, st));
-    FB_CUDA(cudaMemsetAsync(b.tile_count, 0, (size_t)b.tiles * 4, st));
+    FB_CUDA(cudaMemsetAsync(b.tile_count, 0, (size_t)b.tiles * 4 * FB_TC_STRIDE, st));
     FB_CUDA(cudaMemsetAsync(b.total, 0, 256, st));
     { FB_PROF(FB_K_PREPROCESS); k_preprocess<false, 0><<<(P + 255) / 256, 256, 0, st>>>(to_in(g), cam, nullptr, b, radii,
                                                            (float*)((char*)geom + GL.rgb), (bool*)((char*)geom + GL.clamped), nullptr); }

@@ -48,7 +48,7 @@ __global__ void k_fill(float* p, size_t n, float v) {
 }
 
 struct ScoreLayout {
-    size_t recs, recsB, vis_list, vis_count, tile_count, tile_range, totals, partial, final_T, n_contrib, color, depth,
+    size_t recs, recsB, vis_list, vis_count, tile_count, tile_range, tile_order, totals, partial, final_T, n_contrib, color, depth,
         dpix, keys, keys_alt, total;
 };
 static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
@@ -58,10 +58,11 @@ static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
     L.recsB = o;      o = align_up(o + Vv * Pp * 64, 256);
     L.vis_list = o;   o = align_up(o + Vv * Pp * 16, 256);
     L.vis_count = o;  o = align_up(o + Vv * 4, 256);
-    L.tile_count = o; o = align_up(o + Vv * tiles * 4, 256);
+    L.tile_count = o; o = align_up(o + Vv * tiles * 4 * FB_TC_STRIDE, 256);
     L.tile_range = o; o = align_up(o + Vv * tiles * 8, 256);
+    L.tile_order = o; o = align_up(o + Vv * tiles * 4, 256);
     L.totals = o;     o = align_up(o + 256, 256);
-    L.partial = o;    o = align_up(o + Vv * tiles * 4, 256);
+    L.partial = o;    o = align_up(o + Vv * tiles * 4 * FB_TILE_WARPS, 256);
     L.final_T = o;    o = align_up(o + HW * 4, 256);
     L.n_contrib = o;  o = align_up(o + HW * 4, 256);
     L.color = o;      o = align_up(o + HW * 12, 256);
@@ -77,6 +78,7 @@ static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& 
     b.recs = (GRec*)(ws + L.recs); b.recsB = (float4*)(ws + L.recsB);
     b.vis_list = (uint4*)(ws + L.vis_list); b.vis_count = (uint32_t*)(ws + L.vis_count);
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
+    b.tile_order = (uint32_t*)(ws + L.tile_order);
     b.total = (uint32_t*)(ws + L.totals); b.keys = (u64*)(ws + L.keys);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
@@ -146,7 +148,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         attr_set = true;
     }
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
-    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
     GaussIn gi = map_in(map);
     for (int k0 = 0; k0 < K; k0 += V) {
         const int Vc = (K - k0 < V) ? (K - k0) : V;
@@ -166,9 +168,9 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles, Vc), FB_TILE_PIX, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
+        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles, scores + k0); }
+        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }
         FB_LAUNCH_CHECK();
     }
     return FB_OK;
@@ -198,11 +200,12 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     float* dpix = (float*)(ws + L.dpix);
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
     FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
-    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)cam.tiles_x * cam.tiles_y * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
     k_fill<<<(unsigned)((3 * HW + 255) / 256), 256, 0, st>>>(dpix, 3 * HW, grad_scale);
     FB_LAUNCH_CHECK();
     GaussIn gi = map_in(map);
     Bins b = score_bins(L, ws, P, 1, cam, inst_capacity);
+    b.tile_order = nullptr;
     dim3 grid(cam.tiles_x, cam.tiles_y);
     for (int k = 0; k < K; ++k) {
         const float* w2c_k = w2c + (size_t)k * 16;

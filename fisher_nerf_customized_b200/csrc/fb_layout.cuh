@@ -17,6 +17,8 @@ namespace fb {
 static inline __host__ __device__ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // One projected Gaussian of one view: 32 bytes, 32-byte aligned.
+#define FB_TC_STRIDE 32   // uint32 slots per tile counter (128 B)
+
 struct __align__(16) GRec {
     float4 a;  // px, py, depth, opacity
     float4 b;  // conic.x, conic.y, conic.z, __int_as_float(radius)
@@ -28,8 +30,10 @@ struct Bins {
     float4*   recsB;       // [V][P][4]  scoring only: {rgb, coef0 | coef1-4 | coef5-8 | coef9-12}
     uint4*    vis_list;    // [V][P]   visible Gaussians, unordered: {id, depth bits, x0|y0<<8|x1<<16|y1<<24, 0}
     uint32_t* vis_count;   // [V]
-    uint32_t* tile_count;  // [V][tiles]   instances per tile (used as a cursor by the scatter)
+    uint32_t* tile_count;  // [V][tiles][FB_TC_STRIDE]  instances per tile (cursor of the scatter); one counter per
+                           // 128-byte line: atomics on one L2 line serialise, 32 hot counters per line cost 10x
     uint2*    tile_range;  // [V][tiles]   [start,end) into keys
+    uint32_t* tile_order;  // [V*tiles]    scoring only (else null): tile slots by descending instance count
     uint32_t* total;       // [4]: total instances (lo), overflow flag, prefiltered-trap flag, max tile count
     u64*      keys;        // [capacity]
     long long capacity;
@@ -60,7 +64,7 @@ static inline __host__ ImageLayout image_layout(int W, int H) {
     L.final_T = o;    o = align_up(o + HW * 4, 256);
     L.n_contrib = o;  o = align_up(o + HW * 4, 256);
     L.tile_range = o; o = align_up(o + tiles * 8, 256);
-    L.tile_count = o; o = align_up(o + tiles * 4, 256);
+    L.tile_count = o; o = align_up(o + tiles * 4 * FB_TC_STRIDE, 256);
     L.totals = o;     o = align_up(o + 256, 256);
     L.total = o;
     return L;

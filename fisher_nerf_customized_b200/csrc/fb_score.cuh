@@ -5,7 +5,7 @@
 //   (1) front-to-back transmittance pass -> T_final, n_contrib per pixel (registers)      [stage 3]
 //   (2) back-to-front pass: per contributing pair, s = G*o*dL/dalpha and
 //       score += s^2 * poly_g(dx,dy)                                                      [stage 4]
-//   (3) block reduce -> one float per (view, tile); k_score_finalize sums the tiles in fixed order.
+//   (3) warp reduce -> one float per (view, tile, pixel block); k_score_finalize sums them in fixed order.
 // No image, no final_T/n_contrib round trip, no per-Gaussian Hessian tensor, no atomics.
 // Replaces the K-iteration Python loop  models/SLAM/gaussian.py:1362-1370  (+ compute_Hessian
 // :1503-1570) around renderCUDA / renderCUDAFused (forward.cu:261-393, backward.cu:850-1140).
@@ -42,15 +42,41 @@ struct WarpQ {
     float4 b[FB_WQ];       // conic a, b, c, opacity
     float4 rb[4][FB_WQ];   // rgb+coef0 | coef1-4 | coef5-8 | coef9-12   (backward pass only)
 };
-#define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * (FB_TILE_PIX / 32))
+// Warps per CTA.  A warp never talks to another warp, so the CTA is only a launch unit: small CTAs let the
+// SM backfill as soon as a warp's pixel block is finished (with 8-warp CTAs 23 % of all warp samples sat in
+// the final barrier waiting for the slowest block of the tile; profiles/r1_summary_v4.md).
+#ifndef FB_SCORE_WPC
+#define FB_SCORE_WPC 4
+#endif
+#define FB_TILE_WARPS (FB_TILE_PIX / 32)
+// FB_SCORE_FAST (default): the scoring path evaluates exp with MUFU.EX2 (ex2.approx(x*log2e), |x| <= 5.6 here so
+// <= 6 ulp), 1/(1-alpha) with MUFU.RCP, and runs the colour recurrence of backward.cu:997-1008 once on r+g+b
+// (dL/dpix is the same scalar for the three channels in compute_Hessian, gaussian.py:1549, and the recurrence is
+// linear).  These differ from the reference's compiled arithmetic by a few ulp per pair; scores stay far inside the
+// stated rtol 1e-3 (tests/test_gpu_scoring.py).  The drop-in rasteriser kernels keep the as-compiled arithmetic.
+#ifndef FB_SCORE_FAST
+#define FB_SCORE_FAST 1
+#endif
+__device__ __forceinline__ float score_exp(float x) {
+#if FB_SCORE_FAST
+    return __expf(x);
+#else
+    return expf(x);
+#endif
+}
+#define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * FB_SCORE_WPC)
 
-__global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, float grad_scale,
+__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam cam, float grad_scale,
                                                            float* __restrict__ partial) {
     extern __shared__ float4 smem[];
-    __shared__ float red[FB_TILE_PIX / 32];
-
-    const int t = blockIdx.x, v = blockIdx.y;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;      // CTAs per tile
+    // CTAs are dispatched in linear block order; tile_order lists the (view, tile) slots of the chunk by
+    // descending instance count, so the longest lists start first and the grid drains evenly.
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;   // pixel block of the tile, 0..7
     const unsigned lt = (1u << lane) - 1u;
     const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
     // warp -> 8x4 pixel block of the tile, lane -> pixel of the block
@@ -60,15 +86,15 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
     const float pxf = (float)px, pyf = (float)py;
     const float cx = (float)bx + 0.5f * (FB_WB_X - 1), cy = (float)by + 0.5f * (FB_WB_Y - 1);
     const float ex = 0.5f * (FB_WB_X - 1), ey = 0.5f * (FB_WB_Y - 1);
-    const int tile_slot = v * bins.tiles + t;
-    if (bins.total[1]) { if (tid == 0) partial[tile_slot] = 0.f; return; }
+    float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + warp;
+    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
     const uint2 range = bins.tile_range[tile_slot];
     const int n = (int)(range.y - range.x);
-    if (n == 0) { if (tid == 0) partial[tile_slot] = 0.f; return; }
+    if (n == 0) { if (lane == 0) *out = 0.f; return; }
     const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
     const float4* __restrict__ recsB = bins.recsB + (size_t)v * bins.P * 4;
     const u64* __restrict__ sorted = bins.keys + range.x;
-    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[warp];
+    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
 
     // (1) transmittance pass (forward.cu:330-379 without colour / depth)
     float T = 1.0f;
@@ -115,7 +141,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
                     const float dx = a.x - pxf, dy = a.y - pyf;
                     const float power = pair_power(co.x, co.y, co.z, dx, dy);
                     if (power > 0.0f) continue;
-                    const float alpha = fminf(0.99f, co.w * expf(power));
+                    const float alpha = fminf(0.99f, co.w * score_exp(power));
                     if (alpha < 1.0f / 255.0f) continue;
                     const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
                     if (test_T < 0.0001f) { done = true; continue; }
@@ -183,11 +209,21 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
                     const float dx = a.x - pxf, dy = a.y - pyf;
                     const float power = pair_power(co.x, co.y, co.z, dx, dy);
                     if (power > 0.0f) continue;
-                    const float G = expf(power);
+                    const float G = score_exp(power);
                     const float alpha = fminf(0.99f, co.w * G);
                     if (alpha < 1.0f / 255.0f) continue;
-                    T = T / (1.f - alpha);
                     const float4 r0 = q.rb[0][slot];
+#if FB_SCORE_FAST
+                    const float inv1ma = __fdividef(1.f, 1.f - alpha);
+                    T = T * inv1ma;
+                    const float csum = (r0.x + r0.y) + r0.z;
+                    accum_rec[0] = last_alpha * last_color[0] + (1.f - last_alpha) * accum_rec[0];
+                    last_color[0] = csum;
+                    float dL_dalpha = (csum - accum_rec[0]) * dpix * T;
+                    last_alpha = alpha;
+                    if (bgdot != 0.f) dL_dalpha += (-T_final * inv1ma) * bgdot;
+#else
+                    T = T / (1.f - alpha);
                     const float col[3] = {r0.x, r0.y, r0.z};
                     float dL_dalpha = 0.0f;
 #pragma unroll
@@ -198,7 +234,8 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
                     }
                     dL_dalpha *= T;
                     last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
+                    if (bgdot != 0.f) dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;   // exact: x + (-0) == x
+#endif
                     const float s = G * (co.w * dL_dalpha);
                     const float4 r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
                     const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
@@ -210,20 +247,13 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_tile_score(Bins bins, Cam cam, 
         }
     }
 
-    // (3) block reduce
+    // (3) warp reduce; k_score_finalize adds the (tile, block) partials in fixed order
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
-    if (lane == 0) red[warp] = score;
-    __syncthreads();
-    if (tid == 0) {
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < FB_TILE_PIX / 32; ++w) s += red[w];
-        partial[tile_slot] = s;
-    }
+    if (lane == 0) *out = score;
 }
 
-// scores[k0 + v] = sum over tiles of partial[v][t], fixed order (deterministic given partials).
+// scores[k0 + v] = sum over (tile, pixel block) of partial[v][t][w], fixed order (deterministic given partials).
 __global__ void k_score_finalize(const float* __restrict__ partial, int tiles, float* __restrict__ scores) {
     const int v = blockIdx.x;
     float s = 0.f;

@@ -167,9 +167,9 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
                     rb[2] = make_float4(coef[5], coef[6], coef[7], coef[8]);
                     rb[3] = make_float4(coef[9], coef[10], coef[11], coef[12]);
                 }
-                uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles;
+                uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
                 for (int y = s.y0; y < s.y1; ++y)
-                    for (int x = s.x0; x < s.x1; ++x) atomicAdd(&tc[y * cam.tiles_x + x], 1u);
+                    for (int x = s.x0; x < s.x1; ++x) atomicAdd(&tc[(y * cam.tiles_x + x) * FB_TC_STRIDE], 1u);
                 if (!BATCHED && g.colors == nullptr) {
                     bool cl[3];
                     float3 c = sh_to_rgb(cam.sh_degree, cam.sh_coeffs, p, cam.campos,
@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
     unsigned local_max = 0;
     for (int base = 0; base < n; base += blockDim.x) {
         int i = base + threadIdx.x;
-        unsigned c = (i < n) ? bins.tile_count[i] : 0u;
+        unsigned c = (i < n) ? bins.tile_count[(size_t)i * FB_TC_STRIDE] : 0u;
         local_max = max(local_max, c);
         unsigned x = c;
 #pragma unroll
@@ -233,6 +233,41 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
         bins.total[1] = ((long long)carry_s > bins.capacity) ? 1u : 0u;
         bins.total[3] = maxc_s;
     }
+    if (bins.tile_order == nullptr) return;
+    // Work order for the scoring kernel: counting sort of the tile slots by descending instance count
+    // (1024 buckets over [0, max]).  The order inside a bucket is whatever the atomics give; it only decides
+    // when a tile is scheduled, never what it computes.
+    __shared__ unsigned bucket[1024];
+    const unsigned maxc = maxc_s > 0u ? maxc_s : 1u;
+    bucket[threadIdx.x] = 0u;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned c = bins.tile_range[i].y - bins.tile_range[i].x;
+        atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
+    }
+    __syncthreads();
+    {
+        const unsigned c = bucket[threadIdx.x];
+        unsigned x = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_sums[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            unsigned w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        bucket[threadIdx.x] = x - c + (wid > 0 ? warp_sums[wid - 1] : 0u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned c = bins.tile_range[i].y - bins.tile_range[i].x;
+        const unsigned pos = atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
+        bins.tile_order[pos] = (unsigned)i;
+    }
 }
 
 // ---- stage 2b: scatter keys into tile segments ----------------------------------------------
@@ -240,11 +275,11 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
 // (coalesced).  tile_count doubles as the cursor (counted down).
 __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     const int v = blockIdx.y;
-    uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles;
+    uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
     if (bins.total[1]) {
         // capacity exceeded: the caller re-runs with a larger buffer.  Leave the cursors clean.
         if (blockIdx.x == 0)
-            for (int i = threadIdx.x; i < bins.tiles; i += blockDim.x) tc[i] = 0u;
+            for (int i = threadIdx.x; i < bins.tiles; i += blockDim.x) tc[i * FB_TC_STRIDE] = 0u;
         return;
     }
     const unsigned nvis = bins.vis_count[v];
@@ -256,7 +291,7 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
         for (int y = y0; y < y1; ++y)
             for (int x = x0; x < x1; ++x) {
                 int t = y * cam.tiles_x + x;
-                unsigned slot = atomicSub(&tc[t], 1u) - 1u;
+                unsigned slot = atomicSub(&tc[t * FB_TC_STRIDE], 1u) - 1u;
                 bins.keys[tr[t].x + slot] = key;
             }
     }

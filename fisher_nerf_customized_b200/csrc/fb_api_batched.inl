@@ -145,6 +145,8 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<4>)));
+        FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<11>)));
         attr_set = true;
     }
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
@@ -156,9 +158,9 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
         const float* w2c_k = w2c + (size_t)k0 * 16;
         if (C_H == 4)
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 4><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<4><<<(P + FB_PS_THREADS - 1) / FB_PS_THREADS, FB_PS_THREADS, sizeof(PSmem<4>), st>>>(gi, cam, w2c_k, b, weight); }
         else
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 11><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<(P + FB_PS_THREADS - 1) / FB_PS_THREADS, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();

@@ -182,6 +182,137 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
     }
 }
 
+// ---- stage 1, scoring form -------------------------------------------------------------------
+// Same outputs as k_preprocess<true, CH> but split in two phases per group of FB_PS_VG views, because
+// only ~30 % of the (Gaussian, view) pairs are visible and the 13-coefficient build costs ~10x the projection:
+//   phase 1  thread = Gaussian: project into each view, count tiles, append to the view's visible list, write
+//            the 32-byte GRec, and push (local Gaussian, view) onto a queue in shared memory;
+//   phase 2  thread = queue entry: rebuild the conic of that pair from the Gaussian's parameters (kept in
+//            shared memory; same expressions, same bits) and run score_coefs with every lane busy.
+#define FB_PS_VG 16
+#define FB_PS_THREADS 256
+template <int CH> struct PSmem {
+    float p[3][FB_PS_THREADS], cov6[6][FB_PS_THREADS], op[FB_PS_THREADS], sc[3][FB_PS_THREADS], q[4][FB_PS_THREADS],
+        col[3][FB_PS_THREADS], w[CH][FB_PS_THREADS];
+    float w2c[FB_PS_VG * 12];
+    unsigned short queue[FB_PS_THREADS * FB_PS_VG];
+    unsigned qcount;
+};
+
+template <int CH>
+__global__ void __launch_bounds__(FB_PS_THREADS) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
+                                                                    Bins bins, const float* __restrict__ weight) {
+    extern __shared__ __align__(16) unsigned char ps_raw[];
+    PSmem<CH>& S = *reinterpret_cast<PSmem<CH>*>(ps_raw);
+    const int P = bins.P, V = bins.V;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int idx = blockIdx.x * FB_PS_THREADS + tid;
+    const bool live = idx < P;
+    float3 p = make_float3(0.f, 0.f, 0.f);
+    float cov6[6] = {0, 0, 0, 0, 0, 0};
+    float opacity = 0.f;
+    if (live) {
+        p = make_float3(g.means3D[3 * idx], g.means3D[3 * idx + 1], g.means3D[3 * idx + 2]);
+        opacity = g.opacities[idx];
+        const float3 sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
+        const float4 q = *reinterpret_cast<const float4*>(g.rotations + 4 * (size_t)idx);
+        cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov6);
+        S.p[0][tid] = p.x; S.p[1][tid] = p.y; S.p[2][tid] = p.z;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) S.cov6[i][tid] = cov6[i];
+        S.op[tid] = opacity;
+        S.sc[0][tid] = sc.x; S.sc[1][tid] = sc.y; S.sc[2][tid] = sc.z;
+        S.q[0][tid] = q.x; S.q[1][tid] = q.y; S.q[2][tid] = q.z; S.q[3][tid] = q.w;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) S.col[k][tid] = g.colors[3 * idx + k];
+#pragma unroll
+        for (int k = 0; k < CH; ++k) S.w[k][tid] = weight[(size_t)idx * CH + k];
+    }
+    for (int v0 = 0; v0 < V; v0 += FB_PS_VG) {
+        const int nv = min(FB_PS_VG, V - v0);
+        __syncthreads();                                   // previous group's phase 2 is done with w2c / queue
+        for (int i = tid; i < nv * 12; i += FB_PS_THREADS) S.w2c[i] = w2c[(size_t)(v0 + i / 12) * 16 + (i % 12)];
+        if (tid == 0) S.qcount = 0u;
+        __syncthreads();
+        // ---- phase 1
+        for (int vv = 0; vv < nv; ++vv) {
+            const int v = v0 + vv;
+            const float* m = S.w2c + vv * 12;
+            float3 pc;
+            pc.x = fmaf(m[2], p.z, fmaf(m[1], p.y, m[0] * p.x)) + m[3];
+            pc.y = fmaf(m[6], p.z, fmaf(m[5], p.y, m[4] * p.x)) + m[7];
+            pc.z = fmaf(m[10], p.z, fmaf(m[9], p.y, m[8] * p.x)) + m[11];
+            Splat s; int culled = 0; int vis = 0;
+            if (live) vis = project_splat(pc, cov6, cam, s, culled);
+            const unsigned bm = __ballot_sync(0xffffffffu, vis);
+            if (bm == 0u) continue;
+            const int leader = __ffs(bm) - 1;
+            unsigned base = 0, qbase = 0;
+            if (lane == leader) {
+                base = atomicAdd(&bins.vis_count[v], (unsigned)__popc(bm));
+                qbase = atomicAdd(&S.qcount, (unsigned)__popc(bm));
+            }
+            base = __shfl_sync(0xffffffffu, base, leader);
+            qbase = __shfl_sync(0xffffffffu, qbase, leader);
+            if (!vis) continue;
+            const unsigned rank = __popc(bm & ((1u << lane) - 1u));
+            S.queue[qbase + rank] = (unsigned short)(tid | (vv << 8));
+            bins.vis_list[(size_t)v * P + base + rank] =
+                make_uint4((unsigned)idx, __float_as_uint(s.depth),
+                           (unsigned)s.x0 | ((unsigned)s.y0 << 8) | ((unsigned)s.x1 << 16) | ((unsigned)s.y1 << 24), 0u);
+            // half extents of the alpha >= 1/255 footprint (see k_preprocess)
+            float hx = -1.f, hy = -1.f;
+            if (opacity >= 1.0f / 255.0f) {
+                const float tau2 = 2.0f * logf(255.0f * opacity) + 1e-3f;
+                const float dq = s.ca * s.cc - s.cb * s.cb;
+                hx = sqrtf(tau2 * s.cc / dq) * 1.001f + 0.05f;
+                hy = sqrtf(tau2 * s.ca / dq) * 1.001f + 0.05f;
+                if (!(dq > 0.f) || !(hx == hx) || !(hy == hy)) { hx = 3.0e38f; hy = 3.0e38f; }
+            }
+            GRec r;
+            r.a = make_float4(s.px, s.py, hx, hy);
+            r.b = make_float4(s.ca, s.cb, s.cc, opacity);
+            bins.recs[(size_t)v * P + idx] = r;
+            uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
+            for (int y = s.y0; y < s.y1; ++y)
+                for (int x = s.x0; x < s.x1; ++x) atomicAdd(&tc[(y * cam.tiles_x + x) * FB_TC_STRIDE], 1u);
+        }
+        __syncthreads();
+        // ---- phase 2
+        const unsigned qn = S.qcount;
+        for (unsigned i = tid; i < qn; i += FB_PS_THREADS) {
+            const unsigned e = S.queue[i];
+            const int gi = e & 255, vv = e >> 8;
+            const float* m = S.w2c + vv * 12;
+            const float3 pw = make_float3(S.p[0][gi], S.p[1][gi], S.p[2][gi]);
+            float3 pc;
+            pc.x = fmaf(m[2], pw.z, fmaf(m[1], pw.y, m[0] * pw.x)) + m[3];
+            pc.y = fmaf(m[6], pw.z, fmaf(m[5], pw.y, m[4] * pw.x)) + m[7];
+            pc.z = fmaf(m[10], pw.z, fmaf(m[9], pw.y, m[8] * pw.x)) + m[11];
+            float c6[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) c6[k] = S.cov6[k][gi];
+            const GCtx ctx = make_ctx(pc, c6, cam);
+            // conic exactly as project_splat builds it
+            const float det = __fmaf_rn(ctx.c2.a, ctx.c2.c, -__fmul_rn(ctx.c2.b, ctx.c2.b));
+            const float det_inv = 1.f / det;
+            const float ca = __fmul_rn(ctx.c2.c, det_inv), cb = __fmul_rn(-ctx.c2.b, det_inv), cc = __fmul_rn(ctx.c2.a, det_inv);
+            const SRCtx sr = make_sr(make_float3(S.sc[0][gi], S.sc[1][gi], S.sc[2][gi]), cam.scale_modifier,
+                                     make_float4(S.q[0][gi], S.q[1][gi], S.q[2][gi], S.q[3][gi]));
+            float wv[CH];
+#pragma unroll
+            for (int k = 0; k < CH; ++k) wv[k] = S.w[k][gi];
+            float coef[13];
+            score_coefs<CH>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
+            float4* rb = bins.recsB + ((size_t)(v0 + vv) * P + (size_t)blockIdx.x * FB_PS_THREADS + gi) * 4;
+            rb[0] = make_float4(S.col[0][gi], S.col[1][gi], S.col[2][gi], coef[0]);
+            rb[1] = make_float4(coef[1], coef[2], coef[3], coef[4]);
+            rb[2] = make_float4(coef[5], coef[6], coef[7], coef[8]);
+            rb[3] = make_float4(coef[9], coef[10], coef[11], coef[12]);
+        }
+    }
+}
+
 // ---- stage 2a: counts -> segment offsets (one CTA, V*tiles entries) -------------------------
 // Empty tiles get range (0,0) as in the reference (cudaMemset + identifyTileRanges,
 // rasterizer_impl.cu:311-319).  total[0] = instance count, total[1] = overflow flag,

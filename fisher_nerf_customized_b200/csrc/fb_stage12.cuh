@@ -515,31 +515,140 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
 }
 
 // Sort every tile segment of every view of the chunk.  Dynamic shared memory: 2 * smem_keys keys.
+//
+// The required order is the total order of the 64-bit key (depth_bits << 32 | gaussian_id), so ANY complete
+// sort of the full key reproduces the reference's stable radix sort; stability is not needed.  Segments that
+// fit in shared memory use a histogram-equalised bucket sort (5 light passes, no per-digit passes):
+//   A  stage keys, min/max of the depth bits                 B  256 coarse buckets (linear in the depth bits)
+//   C  each coarse bucket gets fine buckets in proportion to its population (<= 2048 in total), so the
+//      monotone piecewise-linear map depth -> fine bucket leaves ~1 key per bucket even when the tile's
+//      depths cluster on a few surfaces; fine histogram + scan
+//   D  scatter into bucket order (arrival order inside a bucket)
+//   E  every key counts the smaller keys of its own bucket and is written to its final place.
+// Segments longer than the shared capacity, or with a pathologically full bucket, take the LSD radix path.
+#define FB_SORT_COARSE 256
+#define FB_SORT_FINE 2048
+#define FB_SORT_MAX_BUCKET 64
+
+__device__ __forceinline__ unsigned block_excl_scan_256(unsigned x, unsigned* warp_sums, unsigned* total) {
+    // exclusive scan of one value per thread over a 256-thread block (all threads call; contains barriers)
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    unsigned inc = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+    __syncthreads();                       // warp_sums may still be read from a previous call
+    if (lane == 31) warp_sums[w] = inc;
+    __syncthreads();
+    unsigned base = 0, tot = 0;
+#pragma unroll
+    for (int ww = 0; ww < FB_RADIX_WARPS; ++ww) { const unsigned v = warp_sums[ww]; if (ww < w) base += v; tot += v; }
+    if (total) *total = tot;
+    return base + inc - x;
+}
+
 __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __restrict__ keys_alt, int smem_keys) {
     extern __shared__ u64 s_keys[];
-    __shared__ unsigned hist[FB_RADIX_WARPS][256];
-    const int v = blockIdx.y, t = blockIdx.x;
+    __shared__ unsigned work[FB_RADIX_WARPS * 256];      // fine-bucket cursors, or the radix histograms
+    __shared__ unsigned c_cnt[FB_SORT_COARSE], c_base[FB_SORT_COARSE], c_nf[FB_SORT_COARSE];
+    __shared__ unsigned wsums[FB_RADIX_WARPS];
+    __shared__ unsigned s_lo, s_hi, s_maxb;
+    const int tid = threadIdx.x;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const unsigned slot = bins.tile_order ? bins.tile_order[lin] : lin;    // heaviest segments first
     if (bins.total[1]) return;
-    const uint2 r = bins.tile_range[(size_t)v * bins.tiles + t];
+    const uint2 r = bins.tile_range[slot];
     const int n = (int)(r.y - r.x);
     if (n < 2) return;
     u64* seg = bins.keys + r.x;
-    u64 *a, *b;
-    const bool in_smem = n <= smem_keys;
-    if (in_smem) {
-        a = s_keys; b = s_keys + smem_keys;
-        for (int i = threadIdx.x; i < n; i += blockDim.x) a[i] = seg[i];
+    bool radix = n > smem_keys;
+    if (!radix) {
+        u64* s_in = s_keys;
+        u64* s_out = s_keys + smem_keys;
+        // A
+        if (tid == 0) { s_lo = 0xffffffffu; s_hi = 0u; s_maxb = 0u; }
+        c_cnt[tid] = 0u;
         __syncthreads();
-    } else {
-        a = seg; b = keys_alt + r.x;
+        unsigned lo = 0xffffffffu, hi = 0u;
+        for (int i = tid; i < n; i += FB_TILE_PIX) {
+            const u64 k = seg[i];
+            s_in[i] = k;
+            const unsigned d = (unsigned)(k >> 32);
+            lo = min(lo, d); hi = max(hi, d);
+        }
+        lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((tid & 31) == 0) { atomicMin(&s_lo, lo); atomicMax(&s_hi, hi); }
+        __syncthreads();
+        lo = s_lo;
+        const unsigned range = s_hi - lo;
+        const int nb = 32 - __clz(range | 1u);                 // bits needed for (d - lo)
+        const int shc = nb > 8 ? nb - 8 : 0;                   // coarse bucket = (d - lo) >> shc  (< 256)
+        const unsigned wmask = (1u << shc) - 1u;
+        // B
+        for (int i = tid; i < n; i += FB_TILE_PIX)
+            atomicAdd(&c_cnt[((unsigned)(s_in[i] >> 32) - lo) >> shc], 1u);
+        __syncthreads();
+        // C: fine buckets per coarse bucket, proportional to its population
+        {
+            const unsigned cnt = c_cnt[tid];
+            const unsigned nf = (unsigned)(((u64)cnt * (FB_SORT_FINE - FB_SORT_COARSE) + (unsigned)n - 1u) / (unsigned)n);
+            c_nf[tid] = nf;
+            c_base[tid] = block_excl_scan_256(nf, wsums, nullptr);
+        }
+        for (int i = tid; i < FB_SORT_FINE; i += FB_TILE_PIX) work[i] = 0u;
+        __syncthreads();
+#define FB_FINE_BUCKET(d) ({ const unsigned x_ = (d) - lo; const unsigned c_ = x_ >> shc; \
+                             c_base[c_] + (unsigned)(((u64)(x_ & wmask) * c_nf[c_]) >> shc); })
+        for (int i = tid; i < n; i += FB_TILE_PIX) atomicAdd(&work[FB_FINE_BUCKET((unsigned)(s_in[i] >> 32))], 1u);
+        __syncthreads();
+        {
+            // exclusive scan of the 2048 fine counts: 8 consecutive buckets per thread
+            unsigned c[8], sum = 0, mx = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { c[k] = work[tid * 8 + k]; sum += c[k]; mx = max(mx, c[k]); }
+            mx = __reduce_max_sync(0xffffffffu, mx);
+            if ((tid & 31) == 0) atomicMax(&s_maxb, mx);
+            unsigned run = block_excl_scan_256(sum, wsums, nullptr);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { work[tid * 8 + k] = run; run += c[k]; }
+        }
+        __syncthreads();
+        if (s_maxb > FB_SORT_MAX_BUCKET) {
+            radix = true;                                      // uniform: s_maxb is block-wide
+        } else {
+            // D
+            for (int i = tid; i < n; i += FB_TILE_PIX) {
+                const u64 k = s_in[i];
+                const unsigned pos = atomicAdd(&work[FB_FINE_BUCKET((unsigned)(k >> 32))], 1u);
+                s_out[pos] = k;
+            }
+            __syncthreads();
+            // E: work[f] is now the END of bucket f, i.e. the start of bucket f + 1
+            for (int i = tid; i < n; i += FB_TILE_PIX) {
+                const u64 k = s_out[i];
+                const unsigned f = FB_FINE_BUCKET((unsigned)(k >> 32));
+                const unsigned e = work[f], b0 = f ? work[f - 1] : 0u;
+                unsigned rank = 0;
+                for (unsigned j = b0; j < e; ++j) rank += (s_out[j] < k) ? 1u : 0u;
+                seg[b0 + rank] = k;
+            }
+            return;
+        }
+#undef FB_FINE_BUCKET
+        __syncthreads();
     }
+    // LSD radix on the depth bits through global memory (L2-resident ping-pong), then the equal-depth fix-up
+    {
+        unsigned (*hist)[256] = reinterpret_cast<unsigned (*)[256]>(work);
+        u64* a = seg;
+        u64* b = keys_alt + r.x;
 #pragma unroll 1
-    for (int pass = 0; pass < 4; ++pass) {
-        if (radix_pass_u64(a, b, n, 32 + 8 * pass, hist)) { u64* tmp = a; a = b; b = tmp; }
-    }
-    fix_equal_depth_runs(a, n);
-    if (a != seg) {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) seg[i] = a[i];
+        for (int pass = 0; pass < 4; ++pass) {
+            if (radix_pass_u64(a, b, n, 32 + 8 * pass, hist)) { u64* tmp = a; a = b; b = tmp; }
+        }
+        fix_equal_depth_runs(a, n);
+        if (a != seg) {
+            for (int i = tid; i < n; i += blockDim.x) seg[i] = a[i];
+        }
     }
 }
 

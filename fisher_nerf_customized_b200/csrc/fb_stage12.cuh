@@ -182,6 +182,42 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
     }
 }
 
+// Warp-aggregated update of per-tile counters.  Every lane brings a tile rectangle (empty if x0 >= x1).  When the
+// union of the warp's rectangles is small (a spatially ordered map: the 32 Gaussians of a warp land on a few
+// tiles) the warp walks the union, one ballot per tile, and the first participating lane issues ONE atomic for
+// all of them; otherwise every lane walks its own rectangle.  f(t, n, leader) performs the atomic on the leader
+// and returns its result to every lane; the callback g(t, value, rank) runs on the participating lanes.
+#define FB_AGG_MAX_UNION 24
+template <class Atomic, class Each>
+__device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int tiles_x, Atomic atom, Each each) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const bool any = x0 < x1 && y0 < y1;
+    const int ux0 = __reduce_min_sync(full, any ? x0 : 0x7fffffff), uy0 = __reduce_min_sync(full, any ? y0 : 0x7fffffff);
+    const int ux1 = __reduce_max_sync(full, any ? x1 : -1), uy1 = __reduce_max_sync(full, any ? y1 : -1);
+    if (ux1 <= ux0) return;                                   // nobody has a tile
+    if ((ux1 - ux0) * (uy1 - uy0) <= FB_AGG_MAX_UNION) {
+        for (int y = uy0; y < uy1; ++y)
+            for (int x = ux0; x < ux1; ++x) {
+                const bool in = any && x >= x0 && x < x1 && y >= y0 && y < y1;
+                const unsigned m = __ballot_sync(full, in);
+                if (m == 0u) continue;
+                const int leader = __ffs(m) - 1;
+                const int t = y * tiles_x + x;
+                unsigned r = 0;
+                if (lane == leader) r = atom(t, (unsigned)__popc(m));
+                r = __shfl_sync(full, r, leader);
+                if (in) each(t, r, (unsigned)__popc(m & ((1u << lane) - 1u)));
+            }
+    } else if (any) {
+        for (int y = y0; y < y1; ++y)
+            for (int x = x0; x < x1; ++x) {
+                const int t = y * tiles_x + x;
+                each(t, atom(t, 1u), 0u);
+            }
+    }
+}
+
 // ---- stage 1, scoring form -------------------------------------------------------------------
 // Same outputs as k_preprocess<true, CH> but split in two phases per group of FB_PS_VG views, because
 // only ~30 % of the (Gaussian, view) pairs are visible and the 13-coefficient build costs ~10x the projection:
@@ -246,6 +282,12 @@ __global__ void __launch_bounds__(FB_PS_THREADS) k_preprocess_score(GaussIn g, C
             if (live) vis = project_splat(pc, cov6, cam, s, culled);
             const unsigned bm = __ballot_sync(0xffffffffu, vis);
             if (bm == 0u) continue;
+            {
+                uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
+                warp_tiles(vis ? s.x0 : 0, vis ? s.y0 : 0, vis ? s.x1 : 0, vis ? s.y1 : 0, cam.tiles_x,
+                           [&](int t, unsigned n) { atomicAdd(&tc[t * FB_TC_STRIDE], n); return 0u; },
+                           [&](int, unsigned, unsigned) {});
+            }
             const int leader = __ffs(bm) - 1;
             unsigned base = 0, qbase = 0;
             if (lane == leader) {
@@ -273,9 +315,6 @@ __global__ void __launch_bounds__(FB_PS_THREADS) k_preprocess_score(GaussIn g, C
             r.a = make_float4(s.px, s.py, hx, hy);
             r.b = make_float4(s.ca, s.cb, s.cc, opacity);
             bins.recs[(size_t)v * P + idx] = r;
-            uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
-            for (int y = s.y0; y < s.y1; ++y)
-                for (int x = s.x0; x < s.x1; ++x) atomicAdd(&tc[(y * cam.tiles_x + x) * FB_TC_STRIDE], 1u);
         }
         __syncthreads();
         // ---- phase 2
@@ -415,16 +454,16 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     }
     const unsigned nvis = bins.vis_count[v];
     const uint2* tr = bins.tile_range + (size_t)v * bins.tiles;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvis; i += gridDim.x * blockDim.x) {
-        const uint4 e = bins.vis_list[(size_t)v * bins.P + i];
+    // warp-uniform trip count: every lane of a warp stays in the loop while any lane has an entry
+    for (unsigned i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; i0 < nvis; i0 += gridDim.x * blockDim.x) {
+        const unsigned i = i0 + (threadIdx.x & 31);
+        uint4 e = make_uint4(0u, 0u, 0u, 0u);
+        if (i < nvis) e = bins.vis_list[(size_t)v * bins.P + i];
         const int x0 = e.z & 0xff, y0 = (e.z >> 8) & 0xff, x1 = (e.z >> 16) & 0xff, y1 = e.z >> 24;
-        u64 key = ((u64)e.y << 32) | (u64)e.x;
-        for (int y = y0; y < y1; ++y)
-            for (int x = x0; x < x1; ++x) {
-                int t = y * cam.tiles_x + x;
-                unsigned slot = atomicSub(&tc[t * FB_TC_STRIDE], 1u) - 1u;
-                bins.keys[tr[t].x + slot] = key;
-            }
+        const u64 key = ((u64)e.y << 32) | (u64)e.x;
+        warp_tiles(x0, y0, x1, y1, cam.tiles_x,
+                   [&](int t, unsigned n) { return atomicSub(&tc[t * FB_TC_STRIDE], n); },
+                   [&](int t, unsigned old, unsigned rank) { bins.keys[tr[t].x + old - 1u - rank] = key; });
     }
 }
 

@@ -34,26 +34,65 @@ def setup_camera(w, h, k, w2c, near=0.01, far=100, device="cuda"):
         viewmatrix=w2c_t, projmatrix=full_proj, sh_degree=0, campos=cam_center, prefiltered=False)
 
 
+def morton_order(means3D, bits=10):
+    """Permutation that sorts points by the 3*bits-bit Morton code of their position in the map's bounding
+    box (device-side torch ops, no host sync): Gaussians that are close in space become close in memory, so
+    the 32 Gaussians of a warp land in a handful of tiles (warp-aggregated counters) and a tile's list
+    gathers neighbouring records."""
+    lo = means3D.amin(dim=0, keepdim=True)
+    ext = (means3D.amax(dim=0, keepdim=True) - lo).clamp_min(1e-12)
+    q = ((means3D - lo) / ext * (2 ** bits - 1)).to(torch.int64).clamp_(0, 2 ** bits - 1)
+    code = torch.zeros((means3D.shape[0],), dtype=torch.int64, device=means3D.device)
+    for b in range(bits):
+        for axis in range(3):
+            code |= ((q[:, axis] >> b) & 1) << (3 * b + axis)
+    return torch.argsort(code, stable=True)
+
+
 class GaussianMap:
     """The resident map in the activated form compute_Hessian feeds the rasteriser
-    (gaussian.py:1523-1543): world-frame means, normalised rotations, sigmoid opacities, exp scales, rgb."""
+    (gaussian.py:1523-1543): world-frame means, normalised rotations, sigmoid opacities, exp scales, rgb.
 
-    def __init__(self, means3D, rgb_colors, rotations, opacities, scales):
+    HBM layout: with `spatial_order=True` (default) the replica is stored in Morton order of the means
+    (`perm[i]` = caller's index of the Gaussian stored at row i).  Everything that crosses the API in per-Gaussian
+    form (H_train, H_train_inv, compute_Hessian) stays in the CALLER's order; FisherScorer permutes at the
+    boundary (one 4*C_H*P-byte gather per call).  Scores are sums over Gaussians and do not depend on the order."""
+
+    def __init__(self, means3D, rgb_colors, rotations, opacities, scales, spatial_order=True):
+        scales = scales if scales.shape[-1] == 3 else scales.repeat(1, 3)   # isotropic: gaussian.py:1532-1533
+        self.perm = None
+        if spatial_order and means3D.shape[0] > 1:
+            with torch.no_grad():
+                self.perm = morton_order(means3D.detach().float())
+            pick = lambda t: t.detach().index_select(0, self.perm)
+            means3D, rgb_colors, rotations = pick(means3D), pick(rgb_colors), pick(rotations)
+            opacities, scales = pick(opacities.reshape(-1)), pick(scales)
         self.means3D = _f32c(means3D)
         self.colors = _f32c(rgb_colors)
         self.rotations = _f32c(rotations)
         self.opacities = _f32c(opacities.reshape(-1))
-        scales = scales if scales.shape[-1] == 3 else scales.repeat(1, 3)   # isotropic: gaussian.py:1532-1533
         self.scales = _f32c(scales)
         self.P = self.means3D.shape[0]
 
+    def to_map_order(self, per_gaussian):
+        """[P, ...] tensor in the caller's order -> the resident (Morton) order."""
+        return per_gaussian if self.perm is None else per_gaussian.index_select(0, self.perm)
+
+    def to_caller_order(self, per_gaussian):
+        if self.perm is None:
+            return per_gaussian
+        out = torch.empty_like(per_gaussian)
+        out.index_copy_(0, self.perm, per_gaussian)
+        return out
+
     @classmethod
-    def from_params(cls, params):
+    def from_params(cls, params, spatial_order=True):
         """From the reference's raw parameter dict (gaussian.py:156-168)."""
         with torch.no_grad():
             return cls(params["means3D"], params["rgb_colors"],
                        torch.nn.functional.normalize(params["unnorm_rotations"]),
-                       torch.sigmoid(params["logit_opacities"]), torch.exp(params["log_scales"]))
+                       torch.sigmoid(params["logit_opacities"]), torch.exp(params["log_scales"]),
+                       spatial_order=spatial_order)
 
     def c_struct(self):
         m = _lib.fb_map()
@@ -134,7 +173,7 @@ class FisherScorer:
         """scores[k] = sum(H_k * H_train_inv), H_k the Fisher diagonal of pose k (gaussian.py:1362-1370).
         w2c: [K,4,4] world-to-camera (already inverted).  Returns a CUDA float tensor [K]."""
         K = w2c.reshape(-1, 4, 4).shape[0]
-        weight = _f32c(H_train_inv.reshape(gmap.P, self.C_H))
+        weight = _f32c(gmap.to_map_order(H_train_inv.reshape(gmap.P, self.C_H)))
         scores = torch.zeros((K,), dtype=torch.float32, device=gmap.means3D.device)
 
         def call(L, cam, m, w2c_t, K_, status, ws, cap):
@@ -147,18 +186,18 @@ class FisherScorer:
     @torch.no_grad()
     def compute_H_train(self, gmap: GaussianMap, keyframe_w2c, out=None):
         """H_train[P,C_H] = sum over keyframes of the per-view Fisher diagonal (gaussian.py:1338-1348)."""
-        H = out if out is not None else torch.zeros((gmap.P, self.C_H), dtype=torch.float32, device=gmap.means3D.device)
-        H0 = H.clone() if out is not None else None
+        H = torch.zeros((gmap.P, self.C_H), dtype=torch.float32, device=gmap.means3D.device)   # map order
 
         def call(L, cam, m, w2c_t, K_, status, ws, cap):
-            if H0 is not None:
-                H.copy_(H0)
-            else:
-                H.zero_()
+            H.zero_()
             return L.fb_accumulate_hessian(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, self.C_H, self.grad_scale,
                                            H.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), self.V, cap,
                                            _stream())
         self._run("fb_accumulate_hessian", gmap, keyframe_w2c, call)
+        H = gmap.to_caller_order(H)
+        if out is not None:
+            out += H
+            return out
         return H
 
     @torch.no_grad()

@@ -168,3 +168,29 @@ def test_full_size_properties(cuda):
         Hk = a.compute_Hessian(gmap, w2c[k])
         torch.testing.assert_close(s_all[k], Hk.double().sum().float(), rtol=1e-3, atol=0)
     assert torch.isfinite(s1).all() and (s1 > 0).all()
+
+
+def test_spatial_order_is_a_layout_not_a_result(cuda):
+    """The Morton-ordered replica (GaussianMap(spatial_order=True), the default) must give the scores and the
+    per-Gaussian H_train (in the CALLER's order) of the replica kept in the caller's order."""
+    import torch
+    W = H = 128
+    P, K, NKF = 30000, 8, 2
+    sc = common.small_scene(P, seed=11)
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    poses = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(K + NKF, seed=5, box=(6.0, 3.0, 6.0)))).cuda()
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    args = (t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"])
+    g_sorted, g_plain = cuda.GaussianMap(*args), cuda.GaussianMap(*args, spatial_order=False)
+    assert g_sorted.perm is not None and g_plain.perm is None
+    assert sorted(g_sorted.perm.tolist()) == list(range(P))
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4)
+    H_a = scorer.compute_H_train(g_sorted, poses[:NKF])
+    H_b = scorer.compute_H_train(g_plain, poses[:NKF])
+    scale = H_b.abs().amax(dim=0, keepdim=True)
+    assert bool(((H_a - H_b).abs() <= 1e-4 * H_b.abs() + 1e-6 * scale).float().mean() > 0.999)
+    H_inv = torch.reciprocal(H_b + 0.1)
+    s_a = scorer.score_candidates(g_sorted, poses[NKF:], H_inv).cpu().numpy()
+    s_b = scorer.score_candidates(g_plain, poses[NKF:], H_inv).cpu().numpy()
+    np.testing.assert_allclose(s_a, s_b, rtol=1e-4)
+    assert int(np.argmax(s_a)) == int(np.argmax(s_b))

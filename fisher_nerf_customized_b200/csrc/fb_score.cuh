@@ -59,10 +59,17 @@ struct WarpQ {
 #endif
 __device__ __forceinline__ float score_exp(float x) {
 #if FB_SCORE_FAST
-    return __expf(x);
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));   // FMUL + MUFU.EX2
+    return r;
 #else
     return expf(x);
 #endif
+}
+__device__ __forceinline__ float score_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));                          // MUFU.RCP
+    return r;
 }
 #define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * FB_SCORE_WPC)
 
@@ -133,6 +140,26 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
                 const int cnt = min(qn, 32);
                 __pipeline_wait_prior(0);
                 __syncwarp();
+#if FB_SCORE_FAST
+                // branch-free: nearly every entry of the ring has a contributing lane, so the skips of
+                // forward.cu:343-358 become predicates and selects instead of divergent branches
+#pragma unroll 4
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = (qh + h) & (FB_WQ - 1);
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    const float alpha = fminf(0.99f, co.w * score_exp(power));
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                    const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    const bool term = ok && test_T < 0.0001f;
+                    done = done || term;
+                    const bool upd = ok && !term;
+                    T = upd ? test_T : T;
+                    last = upd ? __float_as_int(a.z) + 1 : last;
+                }
+#else
                 for (int h = 0; h < cnt; ++h) {
                     if (done) continue;
                     const int slot = (qh + h) & (FB_WQ - 1);
@@ -148,6 +175,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
                     T = test_T;
                     last = __float_as_int(a.z) + 1;
                 }
+#endif
                 __syncwarp();
                 qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
                 if (__all_sync(0xffffffffu, done)) break;
@@ -201,6 +229,33 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
                 const int cnt = min(qn, 32);
                 __pipeline_wait_prior(0);
                 __syncwarp();
+#if FB_SCORE_FAST
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = (qh + h) & (FB_WQ - 1);
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    const float G = score_exp(power);
+                    const float alpha = fminf(0.99f, co.w * G);
+                    const bool ok = __float_as_int(a.z) < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (!__any_sync(0xffffffffu, ok)) continue;          // a quarter of the entries: nobody contributes
+                    const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
+                    const float inv1ma = score_rcp(1.f - alpha);
+                    const float Tn = T * inv1ma;
+                    const float csum = (r0.x + r0.y) + r0.z;
+                    const float ar = last_alpha * last_color[0] + (1.f - last_alpha) * accum_rec[0];
+                    float dL_dalpha = (csum - ar) * dpix * Tn;
+                    if (bgdot != 0.f) dL_dalpha += (-T_final * inv1ma) * bgdot;
+                    const float sv = ok ? G * (co.w * dL_dalpha) : 0.f;
+                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
+                    score += (sv * sv) * eval_poly13(c, dx, dy);
+                    T = ok ? Tn : T;
+                    accum_rec[0] = ok ? ar : accum_rec[0];
+                    last_color[0] = ok ? csum : last_color[0];
+                    last_alpha = ok ? alpha : last_alpha;
+                }
+#else
                 for (int h = 0; h < cnt; ++h) {
                     const int slot = (qh + h) & (FB_WQ - 1);
                     const float4 a = q.a[slot];
@@ -213,16 +268,6 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
                     const float alpha = fminf(0.99f, co.w * G);
                     if (alpha < 1.0f / 255.0f) continue;
                     const float4 r0 = q.rb[0][slot];
-#if FB_SCORE_FAST
-                    const float inv1ma = __fdividef(1.f, 1.f - alpha);
-                    T = T * inv1ma;
-                    const float csum = (r0.x + r0.y) + r0.z;
-                    accum_rec[0] = last_alpha * last_color[0] + (1.f - last_alpha) * accum_rec[0];
-                    last_color[0] = csum;
-                    float dL_dalpha = (csum - accum_rec[0]) * dpix * T;
-                    last_alpha = alpha;
-                    if (bgdot != 0.f) dL_dalpha += (-T_final * inv1ma) * bgdot;
-#else
                     T = T / (1.f - alpha);
                     const float col[3] = {r0.x, r0.y, r0.z};
                     float dL_dalpha = 0.0f;
@@ -235,12 +280,12 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
                     dL_dalpha *= T;
                     last_alpha = alpha;
                     if (bgdot != 0.f) dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;   // exact: x + (-0) == x
-#endif
                     const float s = G * (co.w * dL_dalpha);
                     const float4 r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
                     const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
                     score += (s * s) * eval_poly13(c, dx, dy);
                 }
+#endif
                 __syncwarp();
                 qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
             }

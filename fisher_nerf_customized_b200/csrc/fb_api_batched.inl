@@ -1,6 +1,12 @@
 // fb_api_batched.inl -- debug export, batched scoring / H_train entry points, stage 5 entry points.
 // Included by fb_api.cu.
 
+#if FB_SCORE_SINGLE_PASS
+#define FB_SCORE_KERNEL k_tile_score1
+#else
+#define FB_SCORE_KERNEL k_tile_score
+#endif
+
 namespace fb {
 
 __global__ void k_debug_geom(int P, Cam cam, const GRec* recs, const int* radii_or_null, const uint4* vis_list,
@@ -144,7 +150,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
     static bool attr_set = false;
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
-        FB_CUDA(cudaFuncSetAttribute(k_tile_score, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(FB_SCORE_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<4>)));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<11>)));
         attr_set = true;
@@ -170,7 +176,7 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_TILE_SCORE); k_tile_score<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
+        { FB_PROF(FB_K_TILE_SCORE); FB_SCORE_KERNEL<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }
         FB_LAUNCH_CHECK();

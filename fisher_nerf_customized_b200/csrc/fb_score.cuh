@@ -57,6 +57,10 @@ struct WarpQ {
 #ifndef FB_SCORE_FAST
 #define FB_SCORE_FAST 1
 #endif
+// FB_SCORE_SINGLE_PASS (default): k_tile_score1 below; 0 selects the two-sweep kernel k_tile_score.
+#ifndef FB_SCORE_SINGLE_PASS
+#define FB_SCORE_SINGLE_PASS 1
+#endif
 __device__ __forceinline__ float score_exp(float x) {
 #if FB_SCORE_FAST
     float r;
@@ -293,6 +297,131 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
     }
 
     // (3) warp reduce; k_score_finalize adds the (tile, block) partials in fixed order
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
+    if (lane == 0) *out = score;
+}
+
+// ---- single-pass form -------------------------------------------------------------------------
+// The reference needs two sweeps of a pixel's list: forward for T_final / n_contrib, then backward for
+//   dL/dalpha_i = T_i (c_i - S_i) - T_final bg / (1 - alpha_i),   S_i = colour accumulated BEHIND Gaussian i
+// (backward.cu:978-1017).  With C = sum_j c_j alpha_j T_j the colour of the pixel and Cp_i the same sum over j <= i,
+//   S_i = (C - Cp_i) / (T_i (1 - alpha_i))   =>   dL/dalpha_i = A_i - (C + T_final bg) B_i,
+//   A_i = T_i c_i + Cp_i / (1 - alpha_i),   B_i = 1 / (1 - alpha_i),
+// and A_i, B_i are known when Gaussian i is visited FRONT TO BACK; only the scalar C' = C + T_final bg is not.  The
+// score of the pixel, sum_i (G_i o_i dL/dalpha_i)^2 poly_i, is a quadratic in C':
+//   Q_AA - 2 C' Q_AB + C'^2 Q_BB,   Q_XY = sum_i g_i X_i Y_i,   g_i = (G_i o_i)^2 poly_i >= 0,
+// so one front-to-back sweep with three accumulators per pixel replaces both sweeps: the list is scanned and
+// culled once, alpha is evaluated once per pair, T is the forward product T (1 - alpha) itself (no T / (1 - alpha)
+// reconstruction), and n_contrib never exists.  c is r+g+b because dL/dpix is one scalar for the three channels
+// (gaussian.py:1549).  The blend rules (skips, 0.99 clamp, stop BEFORE the Gaussian that would take T below 1e-4)
+// are those of forward.cu:343-358, which are also the set backward.cu:962-975 revisits.
+// Rounding: the three sums are of non-negative terms and the cancellation happens once per pixel; measured
+// against the reference extension the scores agree to ~1e-5 (tests/test_gpu_scoring.py, rtol 1e-3 required).
+__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Cam cam, float grad_scale,
+                                                                   float* __restrict__ partial) {
+    extern __shared__ float4 smem[];
+    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;
+    const unsigned lt = (1u << lane) - 1u;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * FB_WB_X, by = ty * FB_TILE_Y + (warp >> 1) * FB_WB_Y;
+    const int px = bx + (lane & 7), py = by + (lane >> 3);
+    const bool inside = px < cam.W && py < cam.H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float cx = (float)bx + 0.5f * (FB_WB_X - 1), cy = (float)by + 0.5f * (FB_WB_Y - 1);
+    const float ex = 0.5f * (FB_WB_X - 1), ey = 0.5f * (FB_WB_Y - 1);
+    float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + warp;
+    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
+    const uint2 range = bins.tile_range[tile_slot];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) { if (lane == 0) *out = 0.f; return; }
+    const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
+    const float4* __restrict__ recsB = bins.recsB + (size_t)v * bins.P * 4;
+    const u64* __restrict__ sorted = bins.keys + range.x;
+    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
+
+    float T = 1.0f, Cp = 0.f, Qaa = 0.f, Qab = 0.f, Qbb = 0.f;
+    bool done = !inside;
+    if (!__all_sync(0xffffffffu, done)) {
+        int qn = 0, qh = 0;
+        const int nsteps = (n + 31) >> 5;
+        bool v_nxt = lane < n;
+        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+        for (int step = 0; step <= nsteps; ++step) {
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < n;
+                gid_nxt = (unsigned)(key2 & 0xffffffffull);
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+                const unsigned mask = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = a;
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                    const float4* rb = recsB + (size_t)gid * 4;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + k, 16);
+                }
+                __pipeline_commit();
+                qn += __popc(mask);
+            }
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = (qh + h) & (FB_WQ - 1);
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    const float G = score_exp(power);
+                    const float alpha = fminf(0.99f, co.w * G);
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                    const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    const bool term = ok && test_T < 0.0001f;
+                    done = done || term;
+                    const bool upd = ok && !term;
+                    if (!__any_sync(0xffffffffu, upd)) continue;
+                    const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
+                    const float inv = score_rcp(1.f - alpha);
+                    const float csum = (r0.x + r0.y) + r0.z;
+                    const float Cn = fmaf(csum, alpha * T, Cp);
+                    const float A = fmaf(T, csum, Cn * inv);
+                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
+                    const float go = G * co.w;
+                    const float g = upd ? (go * go) * eval_poly13(c, dx, dy) : 0.f;
+                    const float gA = g * A, gB = g * inv;
+                    Qaa = fmaf(gA, A, Qaa);
+                    Qab = fmaf(gA, inv, Qab);
+                    Qbb = fmaf(gB, inv, Qbb);
+                    Cp = upd ? Cn : Cp;
+                    T = upd ? test_T : T;
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+                if (__all_sync(0xffffffffu, done)) break;
+            }
+        }
+        __pipeline_wait_prior(0);
+        __syncwarp();
+    }
+    const float dpix = inside ? grad_scale : 0.f;
+    const float Cf = fmaf(T, (cam.bg[0] + cam.bg[1]) + cam.bg[2], Cp);     // C + T_final * bg
+    float score = (dpix * dpix) * fmaf(Cf, fmaf(Cf, Qbb, -2.f * Qab), Qaa);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
     if (lane == 0) *out = score;

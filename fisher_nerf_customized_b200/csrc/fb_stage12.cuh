@@ -188,8 +188,9 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
 // all of them; otherwise every lane walks its own rectangle.  f(t, n, leader) performs the atomic on the leader
 // and returns its result to every lane; the callback g(t, value, rank) runs on the participating lanes.
 #define FB_AGG_MAX_UNION 24
-template <class Atomic, class Each>
-__device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int tiles_x, Atomic atom, Each each) {
+#define FB_AGG_BIG_RECT 8
+template <bool COOP, class Atomic, class Each>
+__device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int tiles_x, u64 payload, Atomic atom, Each each) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const bool any = x0 < x1 && y0 < y1;
@@ -207,14 +208,34 @@ __device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int t
                 unsigned r = 0;
                 if (lane == leader) r = atom(t, (unsigned)__popc(m));
                 r = __shfl_sync(full, r, leader);
-                if (in) each(t, r, (unsigned)__popc(m & ((1u << lane) - 1u)));
+                if (in) each(t, r, (unsigned)__popc(m & ((1u << lane) - 1u)), payload);
             }
-    } else if (any) {
+        return;
+    }
+    // scattered warp: small rectangles stay with their lane; a large one (a Gaussian close to the camera can
+    // cover every tile) is spread over the 32 lanes so that no single thread walks hundreds of tiles
+    // (COOP: only where the atomic returns a value the thread waits for; fire-and-forget counters do not stall)
+    const bool big = COOP && any && (x1 - x0) * (y1 - y0) > FB_AGG_BIG_RECT;
+    if (any && !big) {
         for (int y = y0; y < y1; ++y)
             for (int x = x0; x < x1; ++x) {
                 const int t = y * tiles_x + x;
-                each(t, atom(t, 1u), 0u);
+                each(t, atom(t, 1u), 0u, payload);
             }
+    }
+    unsigned bm = COOP ? __ballot_sync(full, big) : 0u;
+    while (bm) {
+        const int src = __ffs(bm) - 1;
+        bm &= bm - 1u;
+        const int sx0 = __shfl_sync(full, x0, src), sy0 = __shfl_sync(full, y0, src);
+        const int sx1 = __shfl_sync(full, x1, src), sy1 = __shfl_sync(full, y1, src);
+        const u64 pl = ((u64)__shfl_sync(full, (unsigned)(payload >> 32), src) << 32) |
+                       (u64)__shfl_sync(full, (unsigned)payload, src);
+        const int w = sx1 - sx0, cnt = w * (sy1 - sy0);
+        for (int j = lane; j < cnt; j += 32) {
+            const int t = (sy0 + j / w) * tiles_x + sx0 + j % w;
+            each(t, atom(t, 1u), 0u, pl);
+        }
     }
 }
 
@@ -284,9 +305,9 @@ __global__ void __launch_bounds__(FB_PS_THREADS) k_preprocess_score(GaussIn g, C
             if (bm == 0u) continue;
             {
                 uint32_t* tc = bins.tile_count + (size_t)v * bins.tiles * FB_TC_STRIDE;
-                warp_tiles(vis ? s.x0 : 0, vis ? s.y0 : 0, vis ? s.x1 : 0, vis ? s.y1 : 0, cam.tiles_x,
+                warp_tiles<false>(vis ? s.x0 : 0, vis ? s.y0 : 0, vis ? s.x1 : 0, vis ? s.y1 : 0, cam.tiles_x, 0ull,
                            [&](int t, unsigned n) { atomicAdd(&tc[t * FB_TC_STRIDE], n); return 0u; },
-                           [&](int, unsigned, unsigned) {});
+                           [&](int, unsigned, unsigned, u64) {});
             }
             const int leader = __ffs(bm) - 1;
             unsigned base = 0, qbase = 0;
@@ -461,9 +482,9 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
         if (i < nvis) e = bins.vis_list[(size_t)v * bins.P + i];
         const int x0 = e.z & 0xff, y0 = (e.z >> 8) & 0xff, x1 = (e.z >> 16) & 0xff, y1 = e.z >> 24;
         const u64 key = ((u64)e.y << 32) | (u64)e.x;
-        warp_tiles(x0, y0, x1, y1, cam.tiles_x,
+        warp_tiles<true>(x0, y0, x1, y1, cam.tiles_x, key,
                    [&](int t, unsigned n) { return atomicSub(&tc[t * FB_TC_STRIDE], n); },
-                   [&](int t, unsigned old, unsigned rank) { bins.keys[tr[t].x + old - 1u - rank] = key; });
+                   [&](int t, unsigned old, unsigned rank, u64 k) { bins.keys[tr[t].x + old - 1u - rank] = k; });
     }
 }
 

@@ -116,7 +116,7 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
 }
 
 #define FB_SORT_SMEM_KEYS 4096
-#define FB_SORT_SMEM_BYTES (2 * FB_SORT_SMEM_KEYS * 8)
+#define FB_SORT_SMEM_BYTES ((FB_SORT_STAGE ? 2 : 1) * FB_SORT_SMEM_KEYS * 8)
 
 extern "C" {
 

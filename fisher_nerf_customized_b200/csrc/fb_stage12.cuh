@@ -574,7 +574,7 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
     __syncthreads();
 }
 
-// Sort every tile segment of every view of the chunk.  Dynamic shared memory: 2 * smem_keys keys.
+// Sort every tile segment of every view of the chunk.  Dynamic shared memory: smem_keys keys (x2 if FB_SORT_STAGE).
 //
 // The required order is the total order of the 64-bit key (depth_bits << 32 | gaussian_id), so ANY complete
 // sort of the full key reproduces the reference's stable radix sort; stability is not needed.  Segments that
@@ -586,6 +586,9 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
 //   D  scatter into bucket order (arrival order inside a bucket)
 //   E  every key counts the smaller keys of its own bucket and is written to its final place.
 // Segments longer than the shared capacity, or with a pathologically full bucket, take the LSD radix path.
+#ifndef FB_SORT_STAGE
+#define FB_SORT_STAGE 1
+#endif
 #define FB_SORT_COARSE 256
 #define FB_SORT_FINE 2048
 #define FB_SORT_MAX_BUCKET 64
@@ -620,18 +623,27 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
     const int n = (int)(r.y - r.x);
     if (n < 2) return;
     u64* seg = bins.keys + r.x;
-    bool radix = n > smem_keys;
-    if (!radix) {
-        u64* s_in = s_keys;
-        u64* s_out = s_keys + smem_keys;
+    bool radix = false;
+    {
+        // Segments that fit: keys staged and scattered in shared memory, 2048 fine buckets in `work`.
+        // Longer segments (a view close to a wall puts > 10k instances on a tile): same algorithm with the keys
+        // in global memory (seg -> keys_alt -> seg, L2-resident) and the dynamic shared memory used as the
+        // bucket array instead (16 KB per 4096 entries), so the buckets stay short.
+        const bool big = n > smem_keys;
+        const u64* s_in = big ? seg : s_keys;
+        u64* s_out = big ? keys_alt + r.x : s_keys + smem_keys;
+        unsigned* fine = big ? reinterpret_cast<unsigned*>(s_keys) : work;
+        const int NF = big ? min(smem_keys * 4, 32768) : FB_SORT_FINE;      // u32 entries available; multiple of 256
+        const int per = NF / FB_TILE_PIX;                                   // fine buckets scanned per thread
         // A
         if (tid == 0) { s_lo = 0xffffffffu; s_hi = 0u; s_maxb = 0u; }
         c_cnt[tid] = 0u;
         __syncthreads();
         unsigned lo = 0xffffffffu, hi = 0u;
+#pragma unroll 4
         for (int i = tid; i < n; i += FB_TILE_PIX) {
             const u64 k = seg[i];
-            s_in[i] = k;
+            if (!big) s_keys[i] = k;
             const unsigned d = (unsigned)(k >> 32);
             lo = min(lo, d); hi = max(hi, d);
         }
@@ -644,49 +656,51 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
         const int shc = nb > 8 ? nb - 8 : 0;                   // coarse bucket = (d - lo) >> shc  (< 256)
         const unsigned wmask = (1u << shc) - 1u;
         // B
+#pragma unroll 4
         for (int i = tid; i < n; i += FB_TILE_PIX)
             atomicAdd(&c_cnt[((unsigned)(s_in[i] >> 32) - lo) >> shc], 1u);
         __syncthreads();
         // C: fine buckets per coarse bucket, proportional to its population
         {
             const unsigned cnt = c_cnt[tid];
-            const unsigned nf = (unsigned)(((u64)cnt * (FB_SORT_FINE - FB_SORT_COARSE) + (unsigned)n - 1u) / (unsigned)n);
+            const unsigned nf = (unsigned)(((u64)cnt * (unsigned)(NF - FB_SORT_COARSE) + (unsigned)n - 1u) / (unsigned)n);
             c_nf[tid] = nf;
             c_base[tid] = block_excl_scan_256(nf, wsums, nullptr);
         }
-        for (int i = tid; i < FB_SORT_FINE; i += FB_TILE_PIX) work[i] = 0u;
+        for (int i = tid; i < NF; i += FB_TILE_PIX) fine[i] = 0u;
         __syncthreads();
 #define FB_FINE_BUCKET(d) ({ const unsigned x_ = (d) - lo; const unsigned c_ = x_ >> shc; \
                              c_base[c_] + (unsigned)(((u64)(x_ & wmask) * c_nf[c_]) >> shc); })
-        for (int i = tid; i < n; i += FB_TILE_PIX) atomicAdd(&work[FB_FINE_BUCKET((unsigned)(s_in[i] >> 32))], 1u);
+#pragma unroll 4
+        for (int i = tid; i < n; i += FB_TILE_PIX) atomicAdd(&fine[FB_FINE_BUCKET((unsigned)(s_in[i] >> 32))], 1u);
         __syncthreads();
         {
-            // exclusive scan of the 2048 fine counts: 8 consecutive buckets per thread
-            unsigned c[8], sum = 0, mx = 0;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { c[k] = work[tid * 8 + k]; sum += c[k]; mx = max(mx, c[k]); }
+            // exclusive scan of the fine counts: `per` consecutive buckets per thread
+            unsigned sum = 0, mx = 0;
+            for (int k = 0; k < per; ++k) { const unsigned c = fine[tid * per + k]; sum += c; mx = max(mx, c); }
             mx = __reduce_max_sync(0xffffffffu, mx);
             if ((tid & 31) == 0) atomicMax(&s_maxb, mx);
             unsigned run = block_excl_scan_256(sum, wsums, nullptr);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { work[tid * 8 + k] = run; run += c[k]; }
+            for (int k = 0; k < per; ++k) { const unsigned c = fine[tid * per + k]; fine[tid * per + k] = run; run += c; }
         }
         __syncthreads();
         if (s_maxb > FB_SORT_MAX_BUCKET) {
             radix = true;                                      // uniform: s_maxb is block-wide
         } else {
             // D
-            for (int i = tid; i < n; i += FB_TILE_PIX) {
+    #pragma unroll 4
+        for (int i = tid; i < n; i += FB_TILE_PIX) {
                 const u64 k = s_in[i];
-                const unsigned pos = atomicAdd(&work[FB_FINE_BUCKET((unsigned)(k >> 32))], 1u);
+                const unsigned pos = atomicAdd(&fine[FB_FINE_BUCKET((unsigned)(k >> 32))], 1u);
                 s_out[pos] = k;
             }
-            __syncthreads();
-            // E: work[f] is now the END of bucket f, i.e. the start of bucket f + 1
-            for (int i = tid; i < n; i += FB_TILE_PIX) {
+            __syncthreads();                                   // (global writes of this block are visible to it)
+            // E: fine[f] is now the END of bucket f, i.e. the start of bucket f + 1
+    #pragma unroll 4
+        for (int i = tid; i < n; i += FB_TILE_PIX) {
                 const u64 k = s_out[i];
                 const unsigned f = FB_FINE_BUCKET((unsigned)(k >> 32));
-                const unsigned e = work[f], b0 = f ? work[f - 1] : 0u;
+                const unsigned e = fine[f], b0 = f ? fine[f - 1] : 0u;
                 unsigned rank = 0;
                 for (unsigned j = b0; j < e; ++j) rank += (s_out[j] < k) ? 1u : 0u;
                 seg[b0 + rank] = k;

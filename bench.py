@@ -31,7 +31,7 @@ if ROOT not in sys.path:
 
 P_GAUSS = 500_000
 K_CAND = 256
-N_KEYFRAMES = 8
+N_KEYFRAMES = 32
 W = H = 256
 C_H = 4
 LAMBDA = 0.1
@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--views-per-chunk", type=int, default=16)
+    ap.add_argument("--views-per-chunk", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -127,6 +127,19 @@ def max_over_ranks(x, world):
     t = torch.tensor([x], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def ncu_traffic(kernel, views_per_chunk):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full`
+    capture of this same command (profiles/ncu_traffic.json); None if no capture matches the chunk size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+        if int(t.get("views_per_chunk", -1)) != int(views_per_chunk):
+            return None
+        return t["dram_bytes_per_launch"].get(kernel)
+    except Exception:
+        return None
 
 
 def peaks():
@@ -256,7 +269,7 @@ def run_b200(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "cfg3: EIG scoring, 500k Gaussians x 256 candidate poses per GPU per step at 256x256, "
-                               "C_H=4, lambda=0.1, H_train from 8 keyframes", "P": P_GAUSS, "K_per_gpu": K_CAND,
+                               f"C_H=4, lambda=0.1, H_train from {N_KEYFRAMES} keyframes", "P": P_GAUSS, "K_per_gpu": K_CAND,
                    "views_per_chunk": args.views_per_chunk, "scene": "shell seed 1234",
                    "l2": "256 MiB fill between steps, outside the timed events",
                    "instances_per_view": R_step / K_CAND, "visible_per_view": vis_step / K_CAND},
@@ -264,7 +277,7 @@ def run_b200(args):
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": ncu_traffic(dom, args.views_per_chunk), "peak_source": peak_src,
                      "kernel_share_of_step": dom_ms / tot_prof, "kernel_ms_per_launch": dom_ms / dom_n,
                      "algorithmic_bytes_per_launch": bytes_per_launch,
                      "whole_path": {"B_view": B_view, "achieved": value / world * B_view / 1e9,

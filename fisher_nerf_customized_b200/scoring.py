@@ -108,7 +108,7 @@ class GaussianMap:
 class FisherScorer:
     """Scores candidate poses by expected information gain, sum(H_candidate * 1/(H_train + lambda))."""
 
-    def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=16,
+    def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=32,
                  inst_capacity=None):
         assert C_H in (4, 11)
         self.cam, self.C_H, self.grad_scale = cam, C_H, float(grad_scale)

@@ -288,6 +288,7 @@ def run_b200(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(sc, c2w_np, H_inv.cpu().numpy(), scores_resident)
+        line["count_visible"] = visibility_baseline(dev)
     print(json.dumps(line))
 
 
@@ -306,6 +307,36 @@ def cpu_baseline(sc, c2w_np, H_inv, scores_gpu, max_views=3):
     return {"value": max_views / dt, "unit": UNIT, "cores": 1, "kind": "port",
             "sample": f"first {max_views} of the 256 candidate poses, same 500k-Gaussian map, {dt:.1f} s",
             "max_rel_diff_vs_gpu": rel}
+
+
+def visibility_baseline(dev, N=1_000_000, K=64):
+    """The path's one CPU function in the reference, numpy count_visible_points (tester_navigator.py:147-180, restated
+    operation by operation in oracle.count_visible_points), timed on the host cores beside fb_count_visible
+    (BASELINE config 1: 1M points x 64 poses, 256x256).  The counts must be equal."""
+    import torch
+    import fisher_nerf_customized_b200 as fb
+    from fisher_nerf_customized_b200 import synth
+    from oracle import oracle as O
+    pts = synth.make_points(N)
+    c2w = synth.make_poses(K).astype(np.float64)
+    intr = synth.intrinsics(W, H).astype(np.float32)
+    dpts = torch.from_numpy(pts).to(dev)
+    for _ in range(3):
+        got = fb.count_visible_batch(dpts, c2w, intr, W)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    got = fb.count_visible_batch(dpts, c2w, intr, W)
+    b.record(); b.synchronize()
+    t0 = time.perf_counter()
+    want = np.array([len(O.count_visible_points(pts, c2w[k], intr, W)) for k in range(K)])
+    dt = time.perf_counter() - t0
+    try:
+        ncores = len(os.sched_getaffinity(0))
+    except Exception:
+        ncores = os.cpu_count()
+    return {"workload": f"{N} points x {K} poses, {W}x{H}", "unit": "point-poses/s",
+            "b200": N * K / (a.elapsed_time(b) * 1e-3), "cpu_numpy": N * K / dt, "cpu_s": dt, "cores": ncores,
+            "counts_equal": bool((got.cpu().numpy() == want).all())}
 
 
 def run_reference(args):

@@ -257,7 +257,10 @@ template <int CH> struct PSmem {
 };
 
 template <int CH>
-__global__ void __launch_bounds__(FB_PS_THREADS) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
+#ifndef FB_PS_MINB
+#define FB_PS_MINB 3
+#endif
+__global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
                                                                     Bins bins, const float* __restrict__ weight) {
     extern __shared__ __align__(16) unsigned char ps_raw[];
     PSmem<CH>& S = *reinterpret_cast<PSmem<CH>*>(ps_raw);
@@ -590,7 +593,9 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
 #define FB_SORT_STAGE 1
 #endif
 #define FB_SORT_COARSE 256
+#ifndef FB_SORT_FINE
 #define FB_SORT_FINE 2048
+#endif
 #define FB_SORT_MAX_BUCKET 64
 
 __device__ __forceinline__ unsigned block_excl_scan_256(unsigned x, unsigned* warp_sums, unsigned* total) {
@@ -611,7 +616,7 @@ __device__ __forceinline__ unsigned block_excl_scan_256(unsigned x, unsigned* wa
 
 __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __restrict__ keys_alt, int smem_keys) {
     extern __shared__ u64 s_keys[];
-    __shared__ unsigned work[FB_RADIX_WARPS * 256];      // fine-bucket cursors, or the radix histograms
+    __shared__ unsigned work[FB_SORT_FINE > FB_RADIX_WARPS * 256 ? FB_SORT_FINE : FB_RADIX_WARPS * 256];   // fine-bucket cursors, or the radix histograms
     __shared__ unsigned c_cnt[FB_SORT_COARSE], c_base[FB_SORT_COARSE], c_nf[FB_SORT_COARSE];
     __shared__ unsigned wsums[FB_RADIX_WARPS];
     __shared__ unsigned s_lo, s_hi, s_maxb;
@@ -633,8 +638,8 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
         const u64* s_in = big ? seg : s_keys;
         u64* s_out = big ? keys_alt + r.x : s_keys + smem_keys;
         unsigned* fine = big ? reinterpret_cast<unsigned*>(s_keys) : work;
-        const int NF = big ? min(smem_keys * 4, 32768) : FB_SORT_FINE;      // u32 entries available; multiple of 256
-        const int per = NF / FB_TILE_PIX;                                   // fine buckets scanned per thread
+#define FB_FIDX(f) (f)
+        const int NF = big ? min(smem_keys * 4, 32768) & ~255 : FB_SORT_FINE;   // u32 entries available; multiple of 256
         // A
         if (tid == 0) { s_lo = 0xffffffffu; s_hi = 0u; s_maxb = 0u; }
         c_cnt[tid] = 0u;
@@ -672,16 +677,30 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
 #define FB_FINE_BUCKET(d) ({ const unsigned x_ = (d) - lo; const unsigned c_ = x_ >> shc; \
                              c_base[c_] + (unsigned)(((u64)(x_ & wmask) * c_nf[c_]) >> shc); })
 #pragma unroll 4
-        for (int i = tid; i < n; i += FB_TILE_PIX) atomicAdd(&fine[FB_FINE_BUCKET((unsigned)(s_in[i] >> 32))], 1u);
+        for (int i = tid; i < n; i += FB_TILE_PIX) atomicAdd(&fine[FB_FIDX(FB_FINE_BUCKET((unsigned)(s_in[i] >> 32)))], 1u);
         __syncthreads();
         {
-            // exclusive scan of the fine counts: `per` consecutive buckets per thread
+            // exclusive scan of the fine counts.  Warp w owns the contiguous range [w, w+1) * NF/8 and walks it 32
+            // buckets at a time (lane-contiguous: no bank conflicts, whatever NF is): totals first, then the scan.
+            const int lane = tid & 31, w = tid >> 5;
+            const int wlen = NF / FB_RADIX_WARPS, wbeg = w * wlen;
             unsigned sum = 0, mx = 0;
-            for (int k = 0; k < per; ++k) { const unsigned c = fine[tid * per + k]; sum += c; mx = max(mx, c); }
+            for (int j = lane; j < wlen; j += 32) { const unsigned c = fine[wbeg + j]; sum += c; mx = max(mx, c); }
+            sum = __reduce_add_sync(0xffffffffu, sum);
             mx = __reduce_max_sync(0xffffffffu, mx);
-            if ((tid & 31) == 0) atomicMax(&s_maxb, mx);
-            unsigned run = block_excl_scan_256(sum, wsums, nullptr);
-            for (int k = 0; k < per; ++k) { const unsigned c = fine[tid * per + k]; fine[tid * per + k] = run; run += c; }
+            if (lane == 0) { wsums[w] = sum; atomicMax(&s_maxb, mx); }
+            __syncthreads();
+            unsigned carry = 0;
+#pragma unroll
+            for (int ww = 0; ww < FB_RADIX_WARPS; ++ww) if (ww < w) carry += wsums[ww];
+            for (int j = lane; j < wlen; j += 32) {
+                const unsigned c = fine[wbeg + j];
+                unsigned inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+                fine[wbeg + j] = carry + inc - c;
+                carry += __shfl_sync(0xffffffffu, inc, 31);
+            }
         }
         __syncthreads();
         if (s_maxb > FB_SORT_MAX_BUCKET) {
@@ -691,7 +710,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
     #pragma unroll 4
         for (int i = tid; i < n; i += FB_TILE_PIX) {
                 const u64 k = s_in[i];
-                const unsigned pos = atomicAdd(&fine[FB_FINE_BUCKET((unsigned)(k >> 32))], 1u);
+                const unsigned pos = atomicAdd(&fine[FB_FIDX(FB_FINE_BUCKET((unsigned)(k >> 32)))], 1u);
                 s_out[pos] = k;
             }
             __syncthreads();                                   // (global writes of this block are visible to it)
@@ -700,7 +719,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
         for (int i = tid; i < n; i += FB_TILE_PIX) {
                 const u64 k = s_out[i];
                 const unsigned f = FB_FINE_BUCKET((unsigned)(k >> 32));
-                const unsigned e = fine[f], b0 = f ? fine[f - 1] : 0u;
+                const unsigned e = fine[FB_FIDX(f)], b0 = f ? fine[FB_FIDX(f - 1)] : 0u;
                 unsigned rank = 0;
                 for (unsigned j = b0; j < e; ++j) rank += (s_out[j] < k) ? 1u : 0u;
                 seg[b0 + rank] = k;

@@ -382,8 +382,8 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                 const int cnt = min(qn, 32);
                 __pipeline_wait_prior(0);
                 __syncwarp();
-                for (int h = 0; h < cnt; ++h) {
-                    const int slot = (qh + h) & (FB_WQ - 1);
+                // batches are 32 entries except the last one, so qh is 0 or 32 and qh + h never wraps
+                auto hit = [&](int slot) {
                     const float4 a = q.a[slot];
                     const float4 co = q.b[slot];
                     const float dx = a.x - pxf, dy = a.y - pyf;
@@ -395,21 +395,27 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                     const bool term = ok && test_T < 0.0001f;
                     done = done || term;
                     const bool upd = ok && !term;
-                    if (!__any_sync(0xffffffffu, upd)) continue;
+                    if (!__any_sync(0xffffffffu, upd)) return;           // ~30 % of the entries: nobody contributes
                     const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
                     const float inv = score_rcp(1.f - alpha);
                     const float csum = (r0.x + r0.y) + r0.z;
                     const float Cn = fmaf(csum, alpha * T, Cp);
                     const float A = fmaf(T, csum, Cn * inv);
                     const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-                    const float go = G * co.w;
-                    const float g = upd ? (go * go) * eval_poly13(c, dx, dy) : 0.f;
+                    const float go = upd ? G * co.w : 0.f;               // select BEFORE the polynomial: no branch around it
+                    const float g = (go * go) * eval_poly13(c, dx, dy);
                     const float gA = g * A, gB = g * inv;
                     Qaa = fmaf(gA, A, Qaa);
                     Qab = fmaf(gA, inv, Qab);
                     Qbb = fmaf(gB, inv, Qbb);
                     Cp = upd ? Cn : Cp;
                     T = upd ? test_T : T;
+                };
+                if (cnt == 32) {
+#pragma unroll 4
+                    for (int h = 0; h < 32; ++h) hit(qh + h);
+                } else {
+                    for (int h = 0; h < cnt; ++h) hit(qh + h);
                 }
                 __syncwarp();
                 qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);

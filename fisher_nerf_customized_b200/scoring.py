@@ -206,6 +206,38 @@ class FisherScorer:
         return self.compute_H_train(gmap, rel_w2c.reshape(1, 4, 4))
 
     @torch.no_grad()
+    def path_point_eig(self, gmap: GaussianMap, path_w2c, H_train, H_reg_lambda=0.1, acc_H_train_every=5):
+        """Point-EIG terms along ONE candidate path, with the running Hessian of path_evaluation
+        (tester_gaussians_navigation.py:1886-1975): for step i = 1..L (pose path_w2c[i-1])
+            point_EIG_i = log sum(cur_H_i * 1/(H_path + lambda))      (0 if nothing is visible, :1933-1935)
+            if (i + 1) % acc_H_train_every == 0:  total += point_EIG_i;  H_path += cur_H_i            (:1944-1946)
+        Returns (point_EIG [L] CUDA tensor, total, H_path).  The weights only change at the accumulation steps, so
+        every run of steps between two of them is ONE batched fb_score_candidates call and only the accumulation
+        poses go through fb_accumulate_hessian: L/acc Hessians instead of L, no [P,C_H] tensor for the other poses.
+        (The customised reference overwrites point_EIG with 0 after computing it, :1929/:1936, and adds a pose term
+        log det(pose_H) from compute_Hessian(return_pose=True); this is the upstream FisherRF point term)"""
+        path_w2c = path_w2c.reshape(-1, 4, 4)
+        L = path_w2c.shape[0]
+        acc = int(acc_H_train_every)
+        H_path = H_train.clone()
+        out = torch.zeros((L,), dtype=torch.float32, device=gmap.means3D.device)
+        total = torch.zeros((), dtype=torch.float32, device=gmap.means3D.device)
+        start = 0
+        while start < L:
+            b = start
+            while b < L and (b + 2) % acc != 0:        # 0-based step b is an accumulation step iff (b + 2) % acc == 0
+                b += 1
+            last = min(b, L - 1)
+            s = self.score_candidates(gmap, path_w2c[start:last + 1], torch.reciprocal(H_path + H_reg_lambda))
+            e = torch.where(s > 0, torch.log(s.clamp_min(1e-45)), torch.zeros_like(s))
+            out[start:last + 1] = e
+            if b < L:
+                total = total + e[-1]
+                H_path = H_path + self.compute_Hessian(gmap, path_w2c[b])
+            start = last + 1
+        return out, total, H_path
+
+    @torch.no_grad()
     def pose_eval(self, gmap: GaussianMap, poses_c2w, keyframe_w2c, H_reg_lambda=0.1):
         """Reference pose_eval: returns (scores [K] CPU tensor, poses)."""
         H_train = self.compute_H_train(gmap, keyframe_w2c)

@@ -194,3 +194,34 @@ def test_spatial_order_is_a_layout_not_a_result(cuda):
     s_b = scorer.score_candidates(g_plain, poses[NKF:], H_inv).cpu().numpy()
     np.testing.assert_allclose(s_a, s_b, rtol=1e-4)
     assert int(np.argmax(s_a)) == int(np.argmax(s_b))
+
+
+def test_path_point_eig_equals_step_by_step_loop(cuda):
+    """the batched path evaluation equals the reference's sequential loop
+    (tester_gaussians_navigation.py:1919-1946) run one pose at a time through compute_Hessian."""
+    import torch
+    W = H = 64
+    P, L, acc = 5000, 13, 5
+    sc = common.small_scene(P, seed=21)
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    poses = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(L + 2, seed=8, box=(6.0, 3.0, 6.0)))).cuda()
+    gmap = _gmap(cuda, torch, sc)
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4)
+    H_train = scorer.compute_H_train(gmap, poses[:2])
+    path = poses[2:]
+    got, total, H_end = scorer.path_point_eig(gmap, path, H_train, 0.1, acc)
+    # the reference's loop
+    H_path = H_train.clone()
+    want, tot = [], 0.0
+    for i in range(1, L + 1):
+        cur_H = scorer.compute_Hessian(gmap, path[i - 1])
+        s = float(torch.sum(cur_H * torch.reciprocal(H_path + 0.1)))
+        e = float(np.log(s)) if s > 0 else 0.0
+        want.append(e)
+        if (i + 1) % acc == 0:
+            tot += e
+            H_path = H_path + cur_H
+    np.testing.assert_allclose(got.cpu().numpy(), np.array(want), rtol=1e-3, atol=1e-4)
+    assert abs(float(total) - tot) <= 1e-3 * abs(tot) + 1e-4
+    scale = H_path.abs().amax(dim=0, keepdim=True)
+    assert bool(((H_end - H_path).abs() <= 1e-4 * H_path.abs() + 1e-6 * scale).all())

@@ -34,6 +34,19 @@ def setup_camera(w, h, k, w2c, near=0.01, far=100, device="cuda"):
         viewmatrix=w2c_t, projmatrix=full_proj, sh_degree=0, campos=cam_center, prefiltered=False)
 
 
+def read_npz_params(path, device="cuda"):
+    """The raw parameter dict of a reference checkpoint, `params.npz` / `params{t}.npz` as written by save_params /
+    save_params_ckpt (models/SLAM/utils/common_utils.py:30-59; loaded by tester_gaussians_navigation.py:2745-2762).
+    Camera tracks and the extras stored beside the parameters are ignored."""
+    import numpy as np
+    keys = ("means3D", "rgb_colors", "unnorm_rotations", "logit_opacities", "log_scales")
+    with np.load(path, allow_pickle=True) as z:
+        missing = [k for k in keys if k not in z.files]
+        if missing:
+            raise KeyError(f"{path}: not a reference parameter checkpoint, missing {missing}")
+        return {k: torch.as_tensor(np.asarray(z[k]), dtype=torch.float32, device=device) for k in keys}
+
+
 def morton_order(means3D, bits=10):
     """Permutation that sorts points by the 3*bits-bit Morton code of their position in the map's bounding
     box (device-side torch ops, no host sync): Gaussians that are close in space become close in memory, so
@@ -93,6 +106,11 @@ class GaussianMap:
                        torch.nn.functional.normalize(params["unnorm_rotations"]),
                        torch.sigmoid(params["logit_opacities"]), torch.exp(params["log_scales"]),
                        spatial_order=spatial_order)
+
+    @classmethod
+    def from_npz(cls, path, device="cuda", spatial_order=True):
+        """From a reference checkpoint (see read_npz_params)."""
+        return cls.from_params(read_npz_params(path, device), spatial_order=spatial_order)
 
     def c_struct(self):
         m = _lib.fb_map()

@@ -225,3 +225,27 @@ def test_path_point_eig_equals_step_by_step_loop(cuda):
     assert abs(float(total) - tot) <= 1e-3 * abs(tot) + 1e-4
     scale = H_path.abs().amax(dim=0, keepdim=True)
     assert bool(((H_end - H_path).abs() <= 1e-4 * H_path.abs() + 1e-6 * scale).all())
+
+
+def test_map_from_reference_checkpoint(cuda, tmp_path):
+    """GaussianMap.from_npz (reference params{t}.npz) == GaussianMap from the same activated tensors; isotropic
+    checkpoints (one log-scale per Gaussian, gaussian.py:1532-1533) are broadcast to three."""
+    import torch
+    raw = synth.make_scene(3000, seed=5, box=(6.0, 3.0, 6.0), focal=32.0, mean_depth=2.0)
+    path = tmp_path / "params3.npz"
+    np.savez(path, **raw, timestep=np.zeros(3000, np.float32))
+    g = cuda.GaussianMap.from_npz(str(path))
+    act = synth.activate(raw)
+    np.testing.assert_array_equal(g.to_caller_order(g.means3D).cpu().numpy(), act["means3D"])
+    np.testing.assert_allclose(g.to_caller_order(g.opacities).cpu().numpy(), act["opacities"].reshape(-1), rtol=1e-6)
+    np.testing.assert_allclose(g.to_caller_order(g.rotations).cpu().numpy(), act["rotations"], rtol=1e-5, atol=1e-7)
+    rs = cuda.setup_camera(64, 64, common.K_for(64, 64), np.eye(4, dtype=np.float32))
+    w2c = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(3, seed=2, box=(6.0, 3.0, 6.0)))).cuda()
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4)
+    w = torch.ones((3000, 4), device="cuda")
+    s_a = scorer.score_candidates(g, w2c, w).cpu().numpy()
+    s_b = scorer.score_candidates(_gmap(cuda, torch, act), w2c, w).cpu().numpy()
+    np.testing.assert_allclose(s_a, s_b, rtol=1e-4)
+    iso = dict(raw); iso["log_scales"] = raw["log_scales"][:, :1]
+    gi = cuda.GaussianMap.from_params({k: torch.from_numpy(np.asarray(v, np.float32)).cuda() for k, v in iso.items()})
+    assert tuple(gi.scales.shape) == (3000, 3) and bool((gi.scales[:, 0] == gi.scales[:, 2]).all())

@@ -69,10 +69,10 @@ static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
     L.tile_order = o; o = align_up(o + Vv * tiles * 4, 256);
     L.totals = o;     o = align_up(o + 256, 256);
     L.partial = o;    o = align_up(o + Vv * tiles * 4 * FB_TILE_WARPS, 256);
-    L.final_T = o;    o = align_up(o + HW * 4, 256);
-    L.n_contrib = o;  o = align_up(o + HW * 4, 256);
-    L.color = o;      o = align_up(o + HW * 12, 256);
-    L.depth = o;      o = align_up(o + HW * 4, 256);
+    L.final_T = o;    o = align_up(o + Vv * HW * 4, 256);      // per view: the H_train path batches views too
+    L.n_contrib = o;  o = align_up(o + Vv * HW * 4, 256);
+    L.color = o;      o = align_up(o + Vv * HW * 12, 256);
+    L.depth = o;      o = align_up(o + Vv * HW * 4, 256);
     L.dpix = o;       o = align_up(o + HW * 12, 256);
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
@@ -188,7 +188,8 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
                           float* H_out, int* status_dev, void* workspace, size_t workspace_bytes, int views_per_chunk,
                           long long inst_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
-    if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || inst_capacity <= 0 || !status_dev)
+    if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
+        inst_capacity <= 0 || !status_dev)
         return FB_E_INVALID;
     if (K == 0) return FB_OK;
     const int P = map->P;
@@ -204,27 +205,30 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
         attr_set = true;
     }
     const size_t HW = (size_t)cam.W * cam.H;
-    float* mom = (float*)(ws + L.recsB);   // P x 16 floats == one view's worth of the scoring-record region
+    const int V = views_per_chunk;
+    float* mom = (float*)(ws + L.recsB);   // [V][P][16] floats: exactly the scoring-record region
     float* dpix = (float*)(ws + L.dpix);
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
-    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
-    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
+    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)V * P * FB_NACC * 4, st));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
     k_fill<<<(unsigned)((3 * HW + 255) / 256), 256, 0, st>>>(dpix, 3 * HW, grad_scale);
     FB_LAUNCH_CHECK();
     GaussIn gi = map_in(map);
-    Bins b = score_bins(L, ws, P, 1, cam, inst_capacity);
-    b.tile_order = nullptr;
-    dim3 grid(cam.tiles_x, cam.tiles_y);
-    for (int k = 0; k < K; ++k) {
-        const float* w2c_k = w2c + (size_t)k * 16;
-        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, 4, st));
-        { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<(P + 255) / 256, 256, 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
+    // V keyframes per launch sequence: a single 256x256 view is 256 CTAs, less than two per SM
+    for (int k0 = 0; k0 < K; k0 += V) {
+        const int Vc = (K - k0 < V) ? (K - k0) : V;
+        Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
+        b.tile_order = nullptr;
+        const float* w2c_k = w2c + (size_t)k0 * 16;
+        const dim3 grid(cam.tiles_x, cam.tiles_y, Vc);
+        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
+        { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
         k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
-        int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
-        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
+        int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
+        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_RENDER); k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
                                                    (float*)(ws + L.color), (float*)(ws + L.depth)); }

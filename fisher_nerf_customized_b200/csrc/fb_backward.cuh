@@ -23,7 +23,15 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_bwd_tiles(Bins bins, Cam cam, c
                                                           const uint32_t* __restrict__ n_contrib,
                                                           const float* __restrict__ dL_dpix, float* __restrict__ mom) {
     __shared__ BwdSmem sm;
-    const int tx = blockIdx.x, ty = blockIdx.y;
+    // blockIdx.z = view of a batch: per-view records, ranges, pixel state and moment rows; dL_dpix is shared
+    const int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    {
+        const size_t HWv = (size_t)cam.W * cam.H * v;
+        final_T += HWv; n_contrib += HWv;
+        bins.recs += (size_t)v * bins.P;
+        bins.tile_range += (size_t)v * bins.tiles;
+        mom += (size_t)v * bins.P * FB_NACC;
+    }
     const int px = tx * FB_TILE_X + threadIdx.x % FB_TILE_X, py = ty * FB_TILE_Y + threadIdx.x / FB_TILE_X;
     const bool inside = px < cam.W && py < cam.H;
     const int pix_id = cam.W * py + px;
@@ -149,61 +157,86 @@ __global__ void __launch_bounds__(128) k_expand_grads(int P, GaussIn g, Cam cam,
     }
 }
 
-// H_out[g, 0..CH) += Fisher diagonal of one view (compute_H_train, models/SLAM/gaussian.py:1338-1348).
-// One thread per visible Gaussian of the view; the moment row is cleared after use so the
-// buffer is all-zero again for the next view.  w2c: row-major 4x4 of this view.
+// H_out[g, 0..CH) += sum over the V views of a batch of the view's Fisher diagonal (compute_H_train,
+// models/SLAM/gaussian.py:1338-1348).  One thread per Gaussian walks the views in order (deterministic, no atomics
+// on H); a view in which the Gaussian collected nothing has an all-zero moment row and is skipped.  Rows are cleared
+// after use so the buffer is all-zero again for the next batch.  w2c: V row-major 4x4 matrices.
 template <int CH>
-__global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam, const float* __restrict__ w2c,
-                                                 float* __restrict__ mom, float* __restrict__ H_out) {
-    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= bins.vis_count[0]) return;
-    const unsigned idx = bins.vis_list[i].x;
-    float acc[FB_NACC];
-    float4* row = reinterpret_cast<float4*>(mom + (size_t)idx * FB_NACC);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { *reinterpret_cast<float4*>(acc + 4 * k) = row[k]; row[k] = make_float4(0.f, 0.f, 0.f, 0.f); }
-    const GRec r = bins.recs[idx];
-    const float3 p = make_float3(g.means3D[3 * idx], g.means3D[3 * idx + 1], g.means3D[3 * idx + 2]);
-    float3 pc;
-    pc.x = fmaf(w2c[2], p.z, fmaf(w2c[1], p.y, w2c[0] * p.x)) + w2c[3];
-    pc.y = fmaf(w2c[6], p.z, fmaf(w2c[5], p.y, w2c[4] * p.x)) + w2c[7];
-    pc.z = fmaf(w2c[10], p.z, fmaf(w2c[9], p.y, w2c[8] * p.x)) + w2c[11];
-    float3 sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
-    float4 q = *reinterpret_cast<const float4*>(g.rotations + 4 * (size_t)idx);
-    float cov6[6];
-    cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov6);
-    SRCtx sr = make_sr(sc, cam.scale_modifier, q);
-    const GCtx ctx = make_ctx(pc, cov6, cam);
+__global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam, const float* __restrict__ w2c_all,
+                                                 float* __restrict__ mom_all, float* __restrict__ H_out) {
+    const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (unsigned)bins.P) return;
     constexpr int NOUT = (CH == 11) ? 10 : 3;
-    float col[5][NOUT];
-    const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
+    double Hk[NOUT];
+    double Hop = 0.0;
 #pragma unroll
-    for (int b = 0; b < 5; ++b) {
-        float e[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-        e[b] = 1.f;
-        float u[5];
-        phi_to_u(e, r.b.x, r.b.y, r.b.z, halfW, halfH, u);
-        ChainOut co = chain_geom(ctx, cam, u[0], u[1], u[2], u[3], u[4]);
-        col[b][0] = co.mean[0]; col[b][1] = co.mean[1]; col[b][2] = co.mean[2];
-        if (CH == 11) {
-            float ds[3], dr[4];
-            chain_scale_rot(sr, co.cov3D, ds, dr);
-            col[b][3] = ds[0]; col[b][4] = ds[1]; col[b][5] = ds[2];
-            col[b][6] = dr[0]; col[b][7] = dr[1]; col[b][8] = dr[2]; col[b][9] = dr[3];
+    for (int k = 0; k < NOUT; ++k) Hk[k] = 0.0;
+    bool any = false;
+    float3 p, sc; float4 q; float cov6[6]; SRCtx sr;
+    for (int v = 0; v < bins.V; ++v) {
+        float acc[FB_NACC];
+        float4* row = reinterpret_cast<float4*>(mom_all + ((size_t)v * bins.P + idx) * FB_NACC);
+        bool nz = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float4 r4 = row[k];
+            *reinterpret_cast<float4*>(acc + 4 * k) = r4;
+            nz = nz || r4.x != 0.f || r4.y != 0.f || r4.z != 0.f || r4.w != 0.f;
         }
+        if (!nz) continue;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) row[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!any) {
+            any = true;
+            p = make_float3(g.means3D[3 * idx], g.means3D[3 * idx + 1], g.means3D[3 * idx + 2]);
+            sc = make_float3(g.scales[3 * idx], g.scales[3 * idx + 1], g.scales[3 * idx + 2]);
+            q = *reinterpret_cast<const float4*>(g.rotations + 4 * (size_t)idx);
+            cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov6);
+            sr = make_sr(sc, cam.scale_modifier, q);
+        }
+        const float* w2c = w2c_all + 16 * v;
+        const GRec r = bins.recs[(size_t)v * bins.P + idx];
+        float3 pc;
+        pc.x = fmaf(w2c[2], p.z, fmaf(w2c[1], p.y, w2c[0] * p.x)) + w2c[3];
+        pc.y = fmaf(w2c[6], p.z, fmaf(w2c[5], p.y, w2c[4] * p.x)) + w2c[7];
+        pc.z = fmaf(w2c[10], p.z, fmaf(w2c[9], p.y, w2c[8] * p.x)) + w2c[11];
+        const GCtx ctx = make_ctx(pc, cov6, cam);
+        float col[5][NOUT];
+        const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
+#pragma unroll
+        for (int b = 0; b < 5; ++b) {
+            float e[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+            e[b] = 1.f;
+            float u[5];
+            phi_to_u(e, r.b.x, r.b.y, r.b.z, halfW, halfH, u);
+            ChainOut co = chain_geom(ctx, cam, u[0], u[1], u[2], u[3], u[4]);
+            col[b][0] = co.mean[0]; col[b][1] = co.mean[1]; col[b][2] = co.mean[2];
+            if (CH == 11) {
+                float ds[3], dr[4];
+                chain_scale_rot(sr, co.cov3D, ds, dr);
+                col[b][3] = ds[0]; col[b][4] = ds[1]; col[b][5] = ds[2];
+                col[b][6] = dr[0]; col[b][7] = dr[1]; col[b][8] = dr[2]; col[b][9] = dr[3];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NOUT; ++k) {
+            double sum = 0.0;
+#pragma unroll
+            for (int a = 0; a < 5; ++a)
+#pragma unroll
+                for (int b = 0; b < 5; ++b) sum += (double)col[a][k] * (double)col[b][k] * (double)moment_phi(acc, a, b);
+            Hk[k] += (double)(float)sum;          // each view's term is rounded to float as the per-view tensor is
+        }
+        Hop += (double)(acc[0] / (r.a.w * r.a.w));
     }
+    if (!any) return;
     float* H = H_out + (size_t)idx * CH;
 #pragma unroll
     for (int k = 0; k < NOUT; ++k) {
-        double sum = 0.0;
-#pragma unroll
-        for (int a = 0; a < 5; ++a)
-#pragma unroll
-            for (int b = 0; b < 5; ++b) sum += (double)col[a][k] * (double)col[b][k] * (double)moment_phi(acc, a, b);
         const int c = (k < 3) ? k : k + 1;
-        H[c] += (float)sum;
+        H[c] += (float)Hk[k];
     }
-    H[3] += acc[0] / (r.a.w * r.a.w);
+    H[3] += (float)Hop;
 }
 
 }  // namespace fb

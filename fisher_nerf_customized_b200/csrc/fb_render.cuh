@@ -20,7 +20,14 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_render_fwd(Bins bins, Cam cam, 
                                                            float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                                                            float* __restrict__ out_color, float* __restrict__ out_depth) {
     __shared__ TileBatch sb;
-    const int tx = blockIdx.x, ty = blockIdx.y;
+    // blockIdx.z = view of a batch (per-view strides P, HW); the single-view drop-in launches with gridDim.z = 1
+    const int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    {
+        const size_t HWv = (size_t)cam.W * cam.H * v;
+        final_T += HWv; n_contrib += HWv; out_color += 3 * HWv; out_depth += HWv;
+        bins.recs += (size_t)v * bins.P;
+        bins.tile_range += (size_t)v * bins.tiles;
+    }
     const int lx = threadIdx.x % FB_TILE_X, ly = threadIdx.x / FB_TILE_X;
     const int px = tx * FB_TILE_X + lx, py = ty * FB_TILE_Y + ly;
     const int W = cam.W, H = cam.H;

@@ -173,8 +173,8 @@ class FisherScorer:
             rc = extra(L, cam, m, w2c, K, status, ws, cap)
             _lib.check(rc, fn_name)
             tiles = ((self.cam.image_width + 15) // 16) * ((self.cam.image_height + 15) // 16)
-            nchunks = (K + self.V - 1) // self.V if fn_name == "fb_score_candidates" else K
-            self.launches += nchunks * (7 if fn_name == "fb_score_candidates" else 9)
+            nchunks = (K + self.V - 1) // self.V
+            self.launches += nchunks * 7 if fn_name == "fb_score_candidates" else nchunks * 8 + 1
             st = status.tolist()
             self.last_status = st
             self.last_instances = st[3]   # sum of num_rendered over the poses of this call

@@ -218,7 +218,6 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     for (int k0 = 0; k0 < K; k0 += V) {
         const int Vc = (K - k0 < V) ? (K - k0) : V;
         Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
-        b.tile_order = nullptr;
         const float* w2c_k = w2c + (size_t)k0 * 16;
         const dim3 grid(cam.tiles_x, cam.tiles_y, Vc);
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));

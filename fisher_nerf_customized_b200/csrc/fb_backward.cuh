@@ -24,7 +24,13 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_bwd_tiles(Bins bins, Cam cam, c
                                                           const float* __restrict__ dL_dpix, float* __restrict__ mom) {
     __shared__ BwdSmem sm;
     // blockIdx.z = view of a batch: per-view records, ranges, pixel state and moment rows; dL_dpix is shared
-    const int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    if (bins.tile_order) {            // batched: heaviest (view, tile) slots first
+        const unsigned slot = bins.tile_order[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x];
+        v = (int)(slot / (unsigned)bins.tiles);
+        const int t = (int)(slot % (unsigned)bins.tiles);
+        tx = t % cam.tiles_x; ty = t / cam.tiles_x;
+    }
     {
         const size_t HWv = (size_t)cam.W * cam.H * v;
         final_T += HWv; n_contrib += HWv;

@@ -21,7 +21,13 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_render_fwd(Bins bins, Cam cam, 
                                                            float* __restrict__ out_color, float* __restrict__ out_depth) {
     __shared__ TileBatch sb;
     // blockIdx.z = view of a batch (per-view strides P, HW); the single-view drop-in launches with gridDim.z = 1
-    const int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
+    if (bins.tile_order) {            // batched: heaviest (view, tile) slots first
+        const unsigned slot = bins.tile_order[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x];
+        v = (int)(slot / (unsigned)bins.tiles);
+        const int t = (int)(slot % (unsigned)bins.tiles);
+        tx = t % cam.tiles_x; ty = t / cam.tiles_x;
+    }
     {
         const size_t HWv = (size_t)cam.W * cam.H * v;
         final_T += HWv; n_contrib += HWv; out_color += 3 * HWv; out_depth += HWv;

@@ -15,3 +15,11 @@ for V in (1, 8, 16, 32):
     for _ in range(3): H = s.compute_H_train(gmap, kf)
     torch.cuda.synchronize(); dt=(time.perf_counter()-t0)/3
     print(f"V={V}: {dt*1e3:.1f} ms for 32 keyframes = {32/dt:.0f} keyframes/s; sum(H)={float(H.double().sum()):.6e}")
+from fisher_nerf_customized_b200 import _lib
+s = fb.FisherScorer(rs, C_H=4, views_per_chunk=32)
+s.compute_H_train(gmap, kf)
+_lib.profile_enable(True); _lib.profile_read()
+s.compute_H_train(gmap, kf)
+prof = _lib.profile_read(); _lib.profile_enable(False)
+for k,v in prof.items():
+    if v[1]: print(f"  {k:18s} {v[0]*1e3/v[1]:9.1f} us/launch x{v[1]}")

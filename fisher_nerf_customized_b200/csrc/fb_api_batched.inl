@@ -202,24 +202,20 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     static bool attr_set = false;
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(k_tile_hessian, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
         attr_set = true;
     }
-    const size_t HW = (size_t)cam.W * cam.H;
     const int V = views_per_chunk;
     float* mom = (float*)(ws + L.recsB);   // [V][P][16] floats: exactly the scoring-record region
-    float* dpix = (float*)(ws + L.dpix);
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
     FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)V * P * FB_NACC * 4, st));
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
-    k_fill<<<(unsigned)((3 * HW + 255) / 256), 256, 0, st>>>(dpix, 3 * HW, grad_scale);
-    FB_LAUNCH_CHECK();
     GaussIn gi = map_in(map);
     // V keyframes per launch sequence: a single 256x256 view is 256 CTAs, less than two per SM
     for (int k0 = 0; k0 < K; k0 += V) {
         const int Vc = (K - k0 < V) ? (K - k0) : V;
         Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
         const float* w2c_k = w2c + (size_t)k0 * 16;
-        const dim3 grid(cam.tiles_x, cam.tiles_y, Vc);
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
         { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
         FB_LAUNCH_CHECK();
@@ -229,10 +225,8 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_RENDER); k_render_fwd<<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (float*)(ws + L.final_T), (uint32_t*)(ws + L.n_contrib),
-                                                   (float*)(ws + L.color), (float*)(ws + L.depth)); }
-        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, false><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, map->colors, (const float*)(ws + L.final_T),
-                                                              (const uint32_t*)(ws + L.n_contrib), dpix, mom); }
+        { FB_PROF(FB_K_BWD_TILES); k_tile_hessian<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
+              b, cam, map->colors, grad_scale, mom); }
         FB_LAUNCH_CHECK();
         if (C_H == 4) { FB_PROF(FB_K_EXPAND); k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }
         else { FB_PROF(FB_K_EXPAND); k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }

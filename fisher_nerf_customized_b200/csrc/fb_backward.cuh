@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
                 for (int b = 0; b < 5; ++b) sum += (double)col[a][k] * (double)col[b][k] * (double)moment_phi(acc, a, b);
             Hk[k] += (double)(float)sum;          // each view's term is rounded to float as the per-view tensor is
         }
-        Hop += (double)(acc[0] / (r.a.w * r.a.w));
+        Hop += (double)(acc[0] / (r.b.w * r.b.w));          // batched record layout: opacity in b.w
     }
     if (!any) return;
     float* H = H_out + (size_t)idx * CH;

@@ -433,6 +433,193 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     if (lane == 0) *out = score;
 }
 
+// ---- per-Gaussian Hessian moments (compute_H_train), warp-autonomous form ----------------------------------
+// Same traversal as k_tile_score (two sweeps, the reference's arithmetic: expf, IEEE division, the recurrences of
+// backward.cu:978-1017 with r+g+b as the one colour channel), but what a contributing pair produces is the 13
+// monomial moments  s^2 * dx^i dy^j  of fb_fisher_tile.cuh (power = 2).  They are summed over the 32 pixels of the
+// block with the halving butterfly (16 SHFL), four neighbouring sums are gathered into one lane and added to the
+// Gaussian's 16-float row with ONE red.global.add.v4.f32 per quad: 4 vector atomics per (Gaussian, pixel block).
+// k_expand_H turns the rows into H columns.  Replaces k_render_fwd + k_bwd_tiles on the batched H_train path (every
+// pixel tests every instance, block barriers per 256 instances): 170 -> ~60 us per keyframe at 500k Gaussians.
+__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, Cam cam, const float* __restrict__ colors,
+                                                                    float grad_scale, float* __restrict__ mom_all) {
+    extern __shared__ float4 smem[];
+    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;
+    const unsigned lt = (1u << lane) - 1u;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * FB_WB_X, by = ty * FB_TILE_Y + (warp >> 1) * FB_WB_Y;
+    const int px = bx + (lane & 7), py = by + (lane >> 3);
+    const bool inside = px < cam.W && py < cam.H;
+    const float pxf = (float)px, pyf = (float)py;
+    const float cx = (float)bx + 0.5f * (FB_WB_X - 1), cy = (float)by + 0.5f * (FB_WB_Y - 1);
+    const float ex = 0.5f * (FB_WB_X - 1), ey = 0.5f * (FB_WB_Y - 1);
+    if (bins.total[1]) return;
+    const uint2 range = bins.tile_range[tile_slot];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) return;
+    const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
+    float* __restrict__ mom = mom_all + (size_t)v * bins.P * FB_NACC;
+    const u64* __restrict__ sorted = bins.keys + range.x;
+    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
+
+    // (1) transmittance sweep (forward.cu:330-379 without colour / depth)
+    float T = 1.0f;
+    int last = 0;
+    bool done = !inside;
+    if (!__all_sync(0xffffffffu, done)) {
+        int qn = 0, qh = 0;
+        const int nsteps = (n + 31) >> 5;
+        bool v_nxt = lane < n;
+        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+        for (int step = 0; step <= nsteps; ++step) {
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < n;
+                gid_nxt = (unsigned)(key2 & 0xffffffffull);
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+                const unsigned mask = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(step * 32 + lane), 0.f);
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                }
+                __pipeline_commit();
+                qn += __popc(mask);
+            }
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = qh + h;
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    const float alpha = fminf(0.99f, co.w * expf(power));
+                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                    const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    const bool term = ok && test_T < 0.0001f;
+                    done = done || term;
+                    const bool upd = ok && !term;
+                    T = upd ? test_T : T;
+                    last = upd ? __float_as_int(a.z) + 1 : last;
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+                if (__all_sync(0xffffffffu, done)) break;
+            }
+        }
+        __pipeline_wait_prior(0);
+        __syncwarp();
+    }
+
+    // (2) back-to-front sweep (backward.cu:939-1038), moments instead of gradients
+    const int warp_last = __reduce_max_sync(0xffffffffu, last);
+    if (warp_last == 0) return;
+    const float T_final = T;
+    const float dpix = inside ? grad_scale : 0.f;
+    const float bgdot = ((cam.bg[0] + cam.bg[1]) + cam.bg[2]) * dpix;
+    float accum_rec = 0.f, last_color = 0.f, last_alpha = 0.f;
+    const int rslot = reduce16_slot(lane);
+    {
+        int qn = 0, qh = 0;
+        const int nsteps = (warp_last + 31) >> 5;
+        bool v_nxt = lane < warp_last;
+        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[warp_last - 1 - lane] & 0xffffffffull) : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+        u64 key2 = (32 + lane < warp_last) ? sorted[warp_last - 1 - 32 - lane] : 0ull;
+        for (int step = 0; step <= nsteps; ++step) {
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < warp_last;
+                gid_nxt = (unsigned)(key2 & 0xffffffffull);
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+                key2 = ((step + 2) * 32 + lane < warp_last) ? sorted[warp_last - 1 - (step + 2) * 32 - lane] : 0ull;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
+                const unsigned mask = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(warp_last - 1 - (step * 32 + lane)), __uint_as_float(gid));
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                    const float* c = colors + 3 * (size_t)gid;
+                    float* dst = reinterpret_cast<float*>(&q.rb[0][slot]);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst + k, c + k, 4);
+                }
+                __pipeline_commit();
+                qn += __popc(mask);
+            }
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                for (int h = 0; h < cnt; ++h) {
+                    const int slot = qh + h;
+                    const float4 a = q.a[slot];
+                    const float4 co = q.b[slot];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
+                    const float G = expf(power);
+                    const float alpha = fminf(0.99f, co.w * G);
+                    const bool ok = __float_as_int(a.z) < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+                    if (!__any_sync(0xffffffffu, ok)) continue;
+                    const float4 c3 = q.rb[0][slot];
+                    const float Tn = T / (1.f - alpha);
+                    const float csum = (c3.x + c3.y) + c3.z;
+                    const float ar = last_alpha * last_color + (1.f - last_alpha) * accum_rec;
+                    float dL_dalpha = (csum - ar) * dpix * Tn;
+                    if (bgdot != 0.f) dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
+                    const float sv = ok ? G * (co.w * dL_dalpha) : 0.f;
+                    T = ok ? Tn : T;
+                    accum_rec = ok ? ar : accum_rec;
+                    last_color = ok ? csum : last_color;
+                    last_alpha = ok ? alpha : last_alpha;
+                    float m[FB_NACC];
+                    {
+                        const float qq = sv * sv;
+                        const float qx = qq * dx, qy = qq * dy;
+                        const float m20 = qx * dx, m11 = qx * dy, m02 = qy * dy;
+                        const float m30 = m20 * dx, m21 = m20 * dy, m12 = m02 * dx, m03 = m02 * dy;
+                        m[0] = qq; m[1] = m20; m[2] = m11; m[3] = m02;
+                        m[4] = m30; m[5] = m21; m[6] = m12; m[7] = m03;
+                        m[8] = m30 * dx; m[9] = m30 * dy; m[10] = m21 * dy; m[11] = m03 * dx; m[12] = m03 * dy;
+                        m[13] = 0.f; m[14] = 0.f; m[15] = 0.f;
+                    }
+                    const float tot = warp_reduce16(m, lane);        // even lane L holds the block sum of moment rslot
+                    // quad k = moments 4k..4k+3 sits on lanes 8k, 8k+2, 8k+4, 8k+6: gather it on lane 8k
+                    float4 quad;
+                    quad.x = tot;
+                    quad.y = __shfl_down_sync(0xffffffffu, tot, 2);
+                    quad.z = __shfl_down_sync(0xffffffffu, tot, 4);
+                    quad.w = __shfl_down_sync(0xffffffffu, tot, 6);
+                    if ((lane & 7) == 0 && (quad.x != 0.f || quad.y != 0.f || quad.z != 0.f || quad.w != 0.f))
+                        atomicAdd(reinterpret_cast<float4*>(mom + (size_t)__float_as_uint(a.w) * FB_NACC) + (rslot >> 2), quad);
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+            }
+        }
+    }
+}
+
 // scores[k0 + v] = sum over (tile, pixel block) of partial[v][t][w], fixed order (deterministic given partials).
 __global__ void k_score_finalize(const float* __restrict__ partial, int tiles, float* __restrict__ scores) {
     const int v = blockIdx.x;

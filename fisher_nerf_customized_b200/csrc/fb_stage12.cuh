@@ -131,8 +131,8 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
                     make_uint4((unsigned)idx, __float_as_uint(s.depth),
                                (unsigned)s.x0 | ((unsigned)s.y0 << 8) | ((unsigned)s.x1 << 16) | ((unsigned)s.y1 << 24), 0u);
                 GRec r;
-                if (CH > 0) {
-                    // scoring layout: half extents of the region where alpha = o*exp(power) can reach 1/255
+                if (CH > 0 || BATCHED) {
+                    // scoring / batched-Hessian layout: half extents of the region where alpha = o*exp(power) can reach 1/255
                     // (d^T Q d <= 2 ln(255 o)); a pair outside it is skipped by the reference's own
                     // alpha < 1/255 test (forward.cu:352, backward.cu:974), so culling with it is exact.
                     // Margin: 1e-3 relative + 0.05 px, far above the rounding of pair_power / expf.

@@ -174,7 +174,7 @@ class FisherScorer:
             _lib.check(rc, fn_name)
             tiles = ((self.cam.image_width + 15) // 16) * ((self.cam.image_height + 15) // 16)
             nchunks = (K + self.V - 1) // self.V
-            self.launches += nchunks * 7 if fn_name == "fb_score_candidates" else nchunks * 8 + 1
+            self.launches += nchunks * 7 if fn_name == "fb_score_candidates" else nchunks * 7
             st = status.tolist()
             self.last_status = st
             self.last_instances = st[3]   # sum of num_rendered over the poses of this call

@@ -1,5 +1,11 @@
 // fb_api.cu -- the C ABI (include/fisher_b200.h) over the sm_100a kernels.  No torch types here.
 #include "fb_score.cuh"
+#include "fb_render_warp.cuh"
+// FB_DROPIN_WARP (default): the single-view drop-in renders with k_render_warp / k_bwd_warp; 0 selects the
+// block-synchronous kernels k_render_fwd / k_bwd_tiles (same results, kept for A/B runs).
+#ifndef FB_DROPIN_WARP
+#define FB_DROPIN_WARP 1
+#endif
 #include "fb_backward.cuh"
 #include "fb_stage5.cuh"
 #include <limits.h>
@@ -109,7 +115,7 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr;
     b.vis_list = (uint4*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
-    b.tile_order = nullptr;
+    b.tile_order = (uint32_t*)(ib + IL.tile_order);
     b.total = (uint32_t*)(ib + IL.totals);
     b.keys = (u64*)inst; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
@@ -188,8 +194,14 @@ int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* ge
         FB_LAUNCH_CHECK();
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);
+#if FB_DROPIN_WARP
+    { FB_PROF(FB_K_RENDER); k_render_warp<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
+        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
+#else
+    b.tile_order = nullptr;
     { FB_PROF(FB_K_RENDER); k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
         b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
+#endif
     FB_LAUNCH_CHECK();
     return FB_OK;
 }
@@ -219,14 +231,27 @@ int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* rad
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((const char*)geom + GL.rgb);
     const float* fT = (const float*)((const char*)image + IL.final_T);
     const uint32_t* nc = (const uint32_t*)((const char*)image + IL.n_contrib);
+#if FB_DROPIN_WARP
+    dim3 grid(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1);
+#else
+    b.tile_order = nullptr;
     dim3 grid(cam.tiles_x, cam.tiles_y);
+#endif
     GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations};
     if (power == 2) {
+#if FB_DROPIN_WARP
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<true><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+#else
         { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+#endif
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_EXPAND); k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     } else {
+#if FB_DROPIN_WARP
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+#else
         { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+#endif
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_EXPAND); k_expand_grads<false><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     }

@@ -19,8 +19,9 @@ __global__ void k_debug_geom(int P, Cam cam, const GRec* recs, const int* radii_
     unsigned gid = vis_list[i].x;
     if ((int)gid >= P) return;
     GRec r = recs[gid];
-    int x0, y0, x1, y1;
-    tile_rect(r.a.x, r.a.y, __float_as_int(r.b.w), cam.tiles_x, cam.tiles_y, x0, y0, x1, y1);
+    const unsigned rect = vis_list[i].z;          // x0 | y0 << 8 | x1 << 16 | y1 << 24, as stage 1 computed it
+    const int x0 = rect & 0xff, y0 = (rect >> 8) & 0xff, x1 = (rect >> 16) & 0xff, y1 = rect >> 24;
+    (void)cam;
     if (tiles_touched) tiles_touched[gid] = (uint32_t)((x1 - x0) * (y1 - y0));
     if (depths) depths[gid] = r.a.z;
     if (means2D) { means2D[2 * gid] = r.a.x; means2D[2 * gid + 1] = r.a.y; }

@@ -21,7 +21,7 @@ static inline __host__ __device__ size_t align_up(size_t x, size_t a) { return (
 
 struct __align__(16) GRec {
     float4 a;  // px, py, depth, opacity
-    float4 b;  // conic.x, conic.y, conic.z, __int_as_float(radius)
+    float4 b;  // conic.x, conic.y, conic.z, footprint half extents as half2 (single view) / opacity (batched: a = px,py,hx,hy)
 };
 
 // View-batched binning state.  All arrays are [V][...] with the given strides.
@@ -56,7 +56,7 @@ static inline __host__ GeomLayout geom_layout(int P) {
     return L;
 }
 struct ImageLayout {
-    size_t final_T, n_contrib, tile_range, tile_count, totals, total;
+    size_t final_T, n_contrib, tile_range, tile_count, tile_order, totals, total;
 };
 static inline __host__ ImageLayout image_layout(int W, int H) {
     ImageLayout L; size_t o = 0; size_t HW = (size_t)W * H;
@@ -65,6 +65,7 @@ static inline __host__ ImageLayout image_layout(int W, int H) {
     L.n_contrib = o;  o = align_up(o + HW * 4, 256);
     L.tile_range = o; o = align_up(o + tiles * 8, 256);
     L.tile_count = o; o = align_up(o + tiles * 4 * FB_TC_STRIDE, 256);
+    L.tile_order = o; o = align_up(o + tiles * 4, 256);
     L.totals = o;     o = align_up(o + 256, 256);
     L.total = o;
     return L;

@@ -17,8 +17,20 @@
 #pragma once
 #include "fb_layout.cuh"
 #include "fb_fisher.cuh"
+#include <cuda_fp16.h>
 
 namespace fb {
+
+// footprint half extents of the single-view record: two halves (rounded up) in GRec.b.w
+__device__ __forceinline__ float pack_extents(float hx, float hy) {
+    const __half2 h = __halves2half2(__float2half_ru(hx), __float2half_ru(hy));
+    return __uint_as_float(*reinterpret_cast<const unsigned*>(&h));
+}
+__device__ __forceinline__ float2 unpack_extents(float w) {
+    const unsigned u = __float_as_uint(w);
+    return __half22float2(*reinterpret_cast<const __half2*>(&u));
+}
+
 
 // ---- SH -> RGB (forward.cu:20-71); coefficients are the standard real SH constants -------------
 __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float3& pos, const float* campos,
@@ -147,8 +159,18 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
                     r.a = make_float4(s.px, s.py, hx, hy);
                     r.b = make_float4(s.ca, s.cb, s.cc, opacity);
                 } else {
+                    // single-view layout: depth and opacity stay in the record (forward needs both), the footprint
+                    // half extents (as above) travel as two halves rounded up
+                    float hx = -1.f, hy = -1.f;
+                    if (opacity >= 1.0f / 255.0f) {
+                        const float tau2 = 2.0f * logf(255.0f * opacity) + 1e-3f;
+                        const float dq = s.ca * s.cc - s.cb * s.cb;
+                        hx = sqrtf(tau2 * s.cc / dq) * 1.001f + 0.05f;
+                        hy = sqrtf(tau2 * s.ca / dq) * 1.001f + 0.05f;
+                        if (!(dq > 0.f) || !(hx == hx) || !(hy == hy)) { hx = 3.0e38f; hy = 3.0e38f; }   // never cull
+                    }
                     r.a = make_float4(s.px, s.py, s.depth, opacity);
-                    r.b = make_float4(s.ca, s.cb, s.cc, __int_as_float(s.radius));
+                    r.b = make_float4(s.ca, s.cb, s.cc, pack_extents(hx, hy));
                 }
                 bins.recs[(size_t)v * P + idx] = r;
                 if (CH > 0) {

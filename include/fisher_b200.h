@@ -187,8 +187,10 @@ typedef struct fb_map {
     const float* colors;     /* [P,3] */
 } fb_map;
 
-/* Workspace for scoring `views_per_chunk` poses at a time with room for
- * `inst_capacity` (Gaussian,tile) instances per chunk. */
+/* Workspace for scoring `views_per_chunk` (1..64) poses at a time with room for
+ * `inst_capacity` (Gaussian,tile) instances per chunk.  The map may be given in any order; a spatially
+ * coherent order (the Python GaussianMap stores it Morton-sorted) lets the kernels aggregate their tile
+ * counters per warp and is ~20 % faster, with the same results. */
 size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk,
                                 long long inst_capacity);
 
@@ -214,7 +216,9 @@ int fb_score_candidates(const fb_camera* cam, const fb_map* map,
                         void* stream);
 
 /* H_out[g,c] += sum_k H_k[g,c]   (compute_H_train, gaussian.py:1338-1348).
- * H_out is [P,C_H], caller-initialised.  Same status convention. */
+ * H_out is [P,C_H], caller-initialised.  Keyframes are processed views_per_chunk (<= 64) per launch
+ * sequence; the per-Gaussian sum over the views of a chunk is formed in a fixed order (no atomics on H_out).
+ * Same workspace (fb_score_workspace_bytes) and status convention as fb_score_candidates. */
 int fb_accumulate_hessian(const fb_camera* cam, const fb_map* map,
                           const float* w2c, int K,
                           int C_H, float grad_scale,

@@ -263,3 +263,76 @@ class FisherScorer:
         poses_c2w = torch.as_tensor(poses_c2w, dtype=torch.float32, device=gmap.means3D.device).reshape(-1, 4, 4)
         w2c = torch.linalg.inv(poses_c2w)
         return self.score_candidates(gmap, w2c, H_train_inv).cpu(), poses_c2w
+
+    # ---- POp-GS variants (gaussian_object.py:1545-1658, 2046-2109): Hutchinson probes through the same operator ----
+    @torch.no_grad()
+    def estimate_diag_JtJ(self, gmap: GaussianMap, w2c, K=4, probes=None, generator=None):
+        """estimate_diag_JtJ_simple (gaussian_object.py:2046-2109): one forward at the pose, K backward passes of the
+        power-2 operator with probe images z_k ([3,H,W], standard normal unless `probes` gives them), and
+            diag = 1/K * sum_k g_k * g_k,   g_k = cat(d means3D [3P], d opacities [P], d rotations [4P], d scales [3P]).
+        The forward is shared by the K probes (the reference keeps the graph, :2092); no autograd graph is built here.
+        Returns (diag [11P] in the CALLER's Gaussian order, number of Gaussians with radius > 0)."""
+        from .rasterizer import _C
+        rs, dev = self.cam, gmap.means3D.device
+        w2c = torch.as_tensor(w2c, dtype=torch.float32, device=dev).reshape(4, 4)
+        pts4 = torch.cat([gmap.means3D, torch.ones((gmap.P, 1), dtype=torch.float32, device=dev)], dim=1)
+        pts = (w2c @ pts4.T).T[:, :3].contiguous()                       # camera frame, :2062-2064
+        e = torch.Tensor([])
+        opac = gmap.opacities.reshape(-1, 1)
+        R, im, radii, geom, inst, img, _ = _C.rasterize_gaussians(
+            rs.bg, pts, gmap.colors, opac, gmap.scales, gmap.rotations, rs.scale_modifier, e, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, e, rs.sh_degree, rs.campos,
+            rs.prefiltered)
+        acc = torch.zeros((gmap.P, 11), dtype=torch.float32, device=dev)
+        for k in range(int(K)):
+            z = probes[k] if probes is not None else torch.randn(im.shape, generator=generator, device=dev)
+            _, _, g_op, g_mean, _, _, g_sc, g_rot = _C.rasterize_gaussians_backward(
+                rs.bg, pts, radii, gmap.colors, gmap.scales, gmap.rotations, rs.scale_modifier, e, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, z, e, rs.sh_degree, rs.campos, geom, R, inst, img, 2)
+            g = torch.cat([g_mean, g_op, g_rot, g_sc], dim=1)
+            acc.addcmul_(g, g)
+            self.launches += 1
+        acc = gmap.to_caller_order(acc / float(K))
+        diag = torch.cat([acc[:, 0:3].reshape(-1), acc[:, 3].reshape(-1), acc[:, 4:8].reshape(-1),
+                          acc[:, 8:11].reshape(-1)])                      # the reference's concatenation order, :2099
+        return diag, int((radii > 0).sum().item())
+
+    @staticmethod
+    def topt_score_from_diags(H_train_diag, JtJ_diag, lam=1e-6):
+        """T-optimality, to maximise: -sum 1/(H_train + JtJ + lam)   (gaussian_object.py:1705-1710)."""
+        return -torch.sum(1.0 / torch.clamp(H_train_diag + JtJ_diag + lam, min=1e-12))
+
+    @staticmethod
+    def dopt_score_from_diags(H_train_diag, JtJ_diag, lam=1e-6):
+        """D-optimality, to maximise: sum log(H_train + JtJ + lam) - sum log(H_train + lam)   (:1712-1718)."""
+        Hm = H_train_diag + lam
+        return torch.sum(torch.log(torch.clamp(Hm + JtJ_diag, min=1e-12))) - torch.sum(torch.log(torch.clamp(Hm, min=1e-12)))
+
+    @torch.no_grad()
+    def compute_H_train_popgs(self, gmap: GaussianMap, keyframe_w2c, K=4, generator=None):
+        """Sum of the Hutchinson diagonals over the keyframes (gaussian_object.py:1545-1570)."""
+        keyframe_w2c = torch.as_tensor(keyframe_w2c, dtype=torch.float32).reshape(-1, 4, 4)
+        if keyframe_w2c.shape[0] == 0:
+            raise RuntimeError("No keyframes available for POP-GS prior.")            # :1569
+        H = None
+        for w2c in keyframe_w2c:
+            d, _ = self.estimate_diag_JtJ(gmap, w2c, K=K, generator=generator)
+            H = d if H is None else H + d
+        return H
+
+    @torch.no_grad()
+    def pose_eval_popgs(self, gmap: GaussianMap, poses_c2w, keyframe_w2c, criterion="topt", K=4, lam=1e-6,
+                        generator=None):
+        """pose_eval_popgs (gaussian_object.py:1619-1658): returns (scores [n] CPU tensor, poses)."""
+        crit = criterion.lower()
+        if crit not in ("topt", "dopt"):
+            raise ValueError("criterion must be 'topt' or 'dopt'")                    # :1648
+        score_fn = self.topt_score_from_diags if crit == "topt" else self.dopt_score_from_diags
+        dev = gmap.means3D.device
+        H_train = self.compute_H_train_popgs(gmap, keyframe_w2c, K=K, generator=generator)
+        poses_c2w = torch.as_tensor(poses_c2w, dtype=torch.float32, device=dev).reshape(-1, 4, 4)
+        scores = []
+        for c2w in poses_c2w:
+            cur, _ = self.estimate_diag_JtJ(gmap, torch.linalg.inv(c2w), K=K, generator=generator)
+            scores.append(score_fn(H_train, cur, lam=lam))
+        return torch.stack(scores).cpu(), poses_c2w

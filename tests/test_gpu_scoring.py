@@ -249,3 +249,50 @@ def test_map_from_reference_checkpoint(cuda, tmp_path):
     iso = dict(raw); iso["log_scales"] = raw["log_scales"][:, :1]
     gi = cuda.GaussianMap.from_params({k: torch.from_numpy(np.asarray(v, np.float32)).cuda() for k, v in iso.items()})
     assert tuple(gi.scales.shape) == (3000, 3) and bool((gi.scales[:, 0] == gi.scales[:, 2]).all())
+
+
+def test_batched_edge_cases(cuda):
+    """No candidates; an image that is not a multiple of the tile size; a workspace too small for the instance list
+    (the driver grows it and re-runs); tile lists of thousands of entries with only 21 distinct depths (the sort's
+    equal-key fallback) -- each against the reference caller's loop through the drop-in operator."""
+    import torch
+    # (1) K = 0
+    W, H = 100, 70
+    sc = common.random_view_scene(6000, 51, W, H)
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    gmap = _gmap(cuda, torch, sc)
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4)
+    Hinv = torch.ones((6000, 4), device="cuda")
+    assert scorer.score_candidates(gmap, torch.zeros((0, 4, 4), device="cuda"), Hinv).shape == (0,)
+    assert not scorer.compute_H_train(gmap, torch.zeros((0, 4, 4), device="cuda")).any()
+    # (2) ragged image, K not a multiple of the chunk, (3) capacity far too small at first
+    eye = np.eye(4, dtype=np.float32)
+    poses = np.stack([eye] + [common.look_at_w2c((0.2 * i, 0.1 * i, -0.3 * i), (0.0, 0.0, 2.0)) for i in range(1, 6)]).astype(np.float32)
+    want = torch.stack([(_caller_loop_H(cuda, torch, rs, sc, w, 4) * Hinv).sum() for w in poses]).cpu().numpy()
+    got = scorer.score_candidates(gmap, torch.from_numpy(poses).cuda(), Hinv).cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=RTOL)
+    small = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4, inst_capacity=256)
+    got2 = small.score_candidates(gmap, torch.from_numpy(poses).cuda(), Hinv).cpu().numpy()
+    assert small.inst_capacity > 256
+    np.testing.assert_array_equal(got2, got)
+    # (4) depth ties and long lists; caller's order kept so that ties break as in the reference
+    W = H = 32
+    P = 9000
+    sc = common.random_view_scene(P, 31, W, H)
+    rng = np.random.default_rng(31)
+    sc["means3D"][:, :2] = rng.uniform(-0.3, 0.3, (P, 2)).astype(np.float32)
+    sc["means3D"][:, 2] = np.round(rng.uniform(1.0, 3.0, P), 1).astype(np.float32)
+    sc["scales"][:] = 0.02
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), eye)
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    gmap = cuda.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"], spatial_order=False)
+    for C_H in (4, 11):
+        scorer = cuda.FisherScorer(rs, C_H=C_H, views_per_chunk=2)
+        H_want = _caller_loop_H(cuda, torch, rs, sc, eye, C_H)
+        H_got = scorer.compute_Hessian(gmap, torch.from_numpy(eye).cuda())
+        scale = H_want.abs().amax(dim=0, keepdim=True)
+        bad = (H_got - H_want).abs() > RTOL * H_want.abs() + RTOL * 1e-3 * scale
+        assert bad.float().mean().item() < 2e-3
+        Hinv = torch.reciprocal(H_want + 0.1)
+        s = scorer.score_candidates(gmap, torch.from_numpy(np.stack([eye, eye])).cuda(), Hinv).cpu().numpy()
+        np.testing.assert_allclose(s, np.full(2, float((H_want * Hinv).sum())), rtol=RTOL)

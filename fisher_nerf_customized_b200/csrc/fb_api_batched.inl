@@ -164,10 +164,11 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
         const float* w2c_k = w2c + (size_t)k0 * 16;
+        const dim3 ps_grid((P + FB_PS_THREADS - 1) / FB_PS_THREADS, min(FB_PS_SPLIT, (Vc + FB_PS_VG - 1) / FB_PS_VG));
         if (C_H == 4)
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<4><<<(P + FB_PS_THREADS - 1) / FB_PS_THREADS, FB_PS_THREADS, sizeof(PSmem<4>), st>>>(gi, cam, w2c_k, b, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<4><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<4>), st>>>(gi, cam, w2c_k, b, weight); }
         else
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<(P + FB_PS_THREADS - 1) / FB_PS_THREADS, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();
@@ -218,7 +219,7 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
         Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
         const float* w2c_k = w2c + (size_t)k0 * 16;
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
-        { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<(P + 255) / 256, 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
+        { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<dim3((P + 255) / 256, min(FB_PS_SPLIT, Vc)), 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
         k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
             cov3d_from_scale_rot(sc, cam.scale_modifier, q, cov6);
         }
     }
-    for (int v = 0; v < V; ++v) {
+    for (int v = blockIdx.y; v < V; v += gridDim.y) {      // batched launches deal the views over grid.y (shorter blocks)
         float3 pc = p;
         if (BATCHED) {
             const float* m = s_w2c + v * 12;
@@ -268,8 +268,13 @@ __device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int t
 //            the 32-byte GRec, and push (local Gaussian, view) onto a queue in shared memory;
 //   phase 2  thread = queue entry: rebuild the conic of that pair from the Gaussian's parameters (kept in
 //            shared memory; same expressions, same bits) and run score_coefs with every lane busy.
+#ifndef FB_PS_VG
 #define FB_PS_VG 16
+#endif
 #define FB_PS_THREADS 256
+#ifndef FB_PS_SPLIT
+#define FB_PS_SPLIT 4          // view groups of one Gaussian group go to up to this many blocks (grid.y)
+#endif
 template <int CH> struct PSmem {
     float p[3][FB_PS_THREADS], cov6[6][FB_PS_THREADS], op[FB_PS_THREADS], sc[3][FB_PS_THREADS], q[4][FB_PS_THREADS],
         col[3][FB_PS_THREADS], w[CH][FB_PS_THREADS];
@@ -310,7 +315,9 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
 #pragma unroll
         for (int k = 0; k < CH; ++k) S.w[k][tid] = weight[(size_t)idx * CH + k];
     }
-    for (int v0 = 0; v0 < V; v0 += FB_PS_VG) {
+    // gridDim.y blocks share a Gaussian group and deal its view groups round-robin: 4x more, 4x shorter blocks,
+    // so the last wave of the grid is a small fraction of the kernel
+    for (int v0 = blockIdx.y * FB_PS_VG; v0 < V; v0 += gridDim.y * FB_PS_VG) {
         const int nv = min(FB_PS_VG, V - v0);
         __syncthreads();                                   // previous group's phase 2 is done with w2c / queue
         for (int i = tid; i < nv * 12; i += FB_PS_THREADS) S.w2c[i] = w2c[(size_t)(v0 + i / 12) * 16 + (i % 12)];

@@ -226,12 +226,65 @@ __device__ __forceinline__ int reduce16_slot(int lane) { return ((lane >> 4) & 1
 // moment row (1, dx2, dxdy, dy2, dx3, dx2dy, dxdy2, dy3, dx4, dx3dy, dx2dy2, dxdy3, dy4).
 // H column order: means3D(3), opacity(1) [C_H=4, gaussian.py:1554-1560] + scales(3), rotations(4)
 // [C_H=11, gaussian_object.py:2024-2032].
+// C_H = 4 only needs dL/dmeans3D = M (s*phi); M (3x5) written out as a product of the chain's small matrices
+// instead of five passes through chain_geom with unit vectors (the compiler may not fold x*0, so each pass costs the
+// whole chain): K = d(cov2D a,b,c)/d(conic) with the -1/2 of phi_to_u folded in, D = d(t)/d(a,b,c) through
+// T = W J (backward.cu:333-407), the view rotation, and the projection path for the two mean2D columns (:566-574).
+__device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam, float A, float B, float C,
+                                                  float halfW, float halfH, float M[3][5]) {
+    const float a = g.c2.a, b = g.c2.b, c = g.c2.c, denom = g.denom;
+    const M3& T = g.c2.T;
+    const float h = -0.5f * g.d2i, dmac = denom - a * c;
+    float K[3][3];                                   // rows (da, db, dc), columns (phi0, phi1, phi2)
+    K[0][0] = h * (-c * c);        K[0][1] = h * (2.f * b * c);                 K[0][2] = h * dmac;
+    K[1][0] = 2.f * h * (b * c);   K[1][1] = -2.f * h * (denom + 2.f * b * b);  K[1][2] = 2.f * h * (a * b);
+    K[2][0] = h * dmac;            K[2][1] = h * (2.f * a * b);                 K[2][2] = h * (-a * a);
+    const float V00 = g.V[0], V01 = g.V[1], V02 = g.V[2], V11 = g.V[3], V12 = g.V[4], V22 = g.V[5];
+    const float r0[3] = {T.c[0][0] * V00 + T.c[0][1] * V01 + T.c[0][2] * V02, T.c[0][0] * V01 + T.c[0][1] * V11 + T.c[0][2] * V12,
+                         T.c[0][0] * V02 + T.c[0][1] * V12 + T.c[0][2] * V22};
+    const float r1[3] = {T.c[1][0] * V00 + T.c[1][1] * V01 + T.c[1][2] * V02, T.c[1][0] * V01 + T.c[1][1] * V11 + T.c[1][2] * V12,
+                         T.c[1][0] * V02 + T.c[1][1] * V12 + T.c[1][2] * V22};
+    const float* vw = cam.view;
+    const float p00 = vw[0] * r0[0] + vw[4] * r0[1] + vw[8] * r0[2], p01 = vw[0] * r1[0] + vw[4] * r1[1] + vw[8] * r1[2];
+    const float p10 = vw[1] * r0[0] + vw[5] * r0[1] + vw[9] * r0[2], p11 = vw[1] * r1[0] + vw[5] * r1[1] + vw[9] * r1[2];
+    const float p20 = vw[2] * r0[0] + vw[6] * r0[1] + vw[10] * r0[2], p21 = vw[2] * r1[0] + vw[6] * r1[1] + vw[10] * r1[2];
+    const float3 t = g.c2.t;
+    const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float fx2 = -cam.focal_x * tz2, fy2 = -cam.focal_y * tz2;
+    const float kx = g.xmul * fx2, ky = g.ymul * fy2;
+    const float cx3 = 2.f * cam.focal_x * t.x * tz3, cy3 = 2.f * cam.focal_y * t.y * tz3;
+    float D[3][3];                                   // rows (dtx, dty, dtz), columns (da, db, dc)
+    D[0][0] = 2.f * kx * p20;                D[0][1] = kx * p21;                                      D[0][2] = 0.f;
+    D[1][0] = 0.f;                           D[1][1] = ky * p20;                                      D[1][2] = 2.f * ky * p21;
+    D[2][0] = 2.f * (fx2 * p00 + cx3 * p20); D[2][1] = fx2 * p01 + fy2 * p10 + cx3 * p21 + cy3 * p20; D[2][2] = 2.f * (fy2 * p11 + cy3 * p21);
+    float E[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) E[i][j] = D[i][0] * K[0][j] + D[i][1] * K[1][j] + D[i][2] * K[2][j];
+    const float* pr = cam.proj;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) M[i][j] = vw[4 * i] * E[0][j] + vw[4 * i + 1] * E[1][j] + vw[4 * i + 2] * E[2][j];
+        const float px = pr[4 * i] * g.m_w - pr[4 * i + 3] * g.mul1, py = pr[4 * i + 1] * g.m_w - pr[4 * i + 3] * g.mul2;
+        M[i][3] = -(px * (A * halfW) + py * (B * halfH));
+        M[i][4] = -(px * (B * halfW) + py * (C * halfH));
+    }
+}
+
 template <int CH>
 __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, const SRCtx& sr, float A, float B, float C,
                                             float op, const float* __restrict__ w, float* coef) {
     constexpr int NOUT = (CH == 11) ? 10 : 3;
     float col[5][NOUT];
     const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
+    if (CH == 4) {
+        float M[3][5];
+        mean_chain_matrix(ctx, cam, A, B, C, halfW, halfH, M);
+#pragma unroll
+        for (int i = 0; i < 5; ++i) { col[i][0] = M[0][i]; col[i][1] = M[1][i]; col[i][2] = M[2][i]; }
+    } else
 #pragma unroll
     for (int i = 0; i < 5; ++i) {
         float e[5] = {0.f, 0.f, 0.f, 0.f, 0.f};

@@ -57,6 +57,9 @@ SIGNATURES = {
     "fb_knn_workspace_bytes": (sz, [ci]),
     "fb_dist2_knn3": (ci, [ci, vp, vp, vp, sz, vp]),
     "fb_count_visible": (ci, [ci, vp, ci, vp, vp, ci, ci, vp, vp, vp]),
+    "fb_block_outer_accumulate": (ci, [ci, vp, vp, vp, vp, vp, cf, vp, vp]),
+    "fb_block_opt_partials": (ci, [ci]),
+    "fb_block_opt": (ci, [ci, ci, vp, vp, vp, vp, cf, ci, vp, vp, vp]),
 }
 
 _lib = None

@@ -294,4 +294,38 @@ int fb_count_visible(int N, const float* points, int K, const double* w2c, const
     return FB_OK;
 }
 
+int fb_block_outer_accumulate(int Nv, const long long* rows, const float* g_mean, const float* g_op, const float* g_rot,
+                              const float* g_scale, float divide_by, float* H_blocks, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (Nv < 0) return FB_E_INVALID;
+    if (Nv == 0) return FB_OK;
+    if (!rows || !g_mean || !H_blocks) return FB_E_INVALID;
+    const int d = 3 + (g_op ? 1 : 0) + (g_rot ? 4 : 0) + (g_scale ? 3 : 0);
+    const long long n = (long long)Nv * d * d;
+    long long blocks = (n + 255) / 256; if (blocks > 148 * 16) blocks = 148 * 16;
+    BlockCols g{g_mean, g_op, g_rot, g_scale};
+    { FB_PROF(FB_K_BLOCKS); k_block_outer<<<(int)blocks, 256, 0, st>>>(n, d, rows, g, divide_by, H_blocks); }
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
+int fb_block_opt_partials(int n_blocks) { return (n_blocks + FB_BLOCK_OPT_THREADS - 1) / FB_BLOCK_OPT_THREADS; }
+
+int fb_block_opt(int n_blocks, int d, const float* Hm_blocks, const long long* idx_m, const float* J_blocks,
+                 const long long* idx_j, float lam, int criterion, double* partial, float* per_block, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (n_blocks < 0 || d < 1 || d > 11 || (criterion != 0 && criterion != 1)) return FB_E_INVALID;
+    if (n_blocks == 0) return FB_OK;
+    if (!Hm_blocks || !J_blocks || !partial) return FB_E_INVALID;
+    const int grid = fb_block_opt_partials(n_blocks);
+    const size_t smem = (size_t)(d * d + d) * FB_BLOCK_OPT_THREADS * sizeof(double);
+    FB_PROF(FB_K_BLOCKS);
+    if (criterion == 0) k_block_opt<false><<<grid, FB_BLOCK_OPT_THREADS, smem, st>>>(n_blocks, d, Hm_blocks, idx_m, J_blocks, idx_j, lam, partial, per_block);
+    else                k_block_opt<true><<<grid, FB_BLOCK_OPT_THREADS, smem, st>>>(n_blocks, d, Hm_blocks, idx_m, J_blocks, idx_j, lam, partial, per_block);
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
 }  // extern "C"

@@ -336,3 +336,134 @@ class FisherScorer:
             cur, _ = self.estimate_diag_JtJ(gmap, torch.linalg.inv(c2w), K=K, generator=generator)
             scores.append(score_fn(H_train, cur, lam=lam))
         return torch.stack(scores).cpu(), poses_c2w
+
+    # ---- POp-GS block form (gaussian_object.py:1572-1586, 1660-1703, 1720-1732, 2112-2176) ----
+    @torch.no_grad()
+    def estimate_block_JtJ(self, gmap: GaussianMap, w2c, K=2, use_rot=True, use_scale=True, use_opacity=True,
+                           probes=None, generator=None):
+        """estimate_block_JtJ (gaussian_object.py:2112-2176): d x d blocks 1/K * sum_k g_k g_k^T of the Gaussians with
+        radius > 0, g_k = [d means3D | d opacity | d rotations | d scales] under probe z_k through the power-2 operator.
+        One forward, K backward launches, the outer products accumulated on device by `fb_block_outer_accumulate`
+        (the block array is the only per-probe read-modify-write; no [N,d] concatenation, no autograd graph).
+        Returns (H_blocks [Nv,d,d], vis_idx [Nv] int64 ascending, in the CALLER's Gaussian order)."""
+        from .rasterizer import _C
+        L = _lib.lib()
+        rs, dev = self.cam, gmap.means3D.device
+        w2c = torch.as_tensor(w2c, dtype=torch.float32, device=dev).reshape(4, 4)
+        pts4 = torch.cat([gmap.means3D, torch.ones((gmap.P, 1), dtype=torch.float32, device=dev)], dim=1)
+        pts = (w2c @ pts4.T).T[:, :3].contiguous()                       # camera frame, :2125-2127
+        e = torch.Tensor([])
+        opac = gmap.opacities.reshape(-1, 1)
+        R, im, radii, geom, inst, img, _ = _C.rasterize_gaussians(
+            rs.bg, pts, gmap.colors, opac, gmap.scales, gmap.rotations, rs.scale_modifier, e, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, e, rs.sh_degree, rs.campos,
+            rs.prefiltered)
+        vis_idx = torch.where(gmap.to_caller_order(radii) > 0)[0]         # :2147, caller's indices, ascending
+        if gmap.perm is None:
+            rows = vis_idx
+        else:                                                             # resident row of each visible Gaussian
+            inv_perm = torch.empty_like(gmap.perm)
+            inv_perm[gmap.perm] = torch.arange(gmap.P, device=dev)
+            rows = inv_perm.index_select(0, vis_idx)
+        rows = rows.contiguous()
+        Nv = int(vis_idx.numel())
+        d = 3 + (1 if use_opacity else 0) + (4 if use_rot else 0) + (3 if use_scale else 0)
+        H_blocks = torch.zeros((Nv, d, d), dtype=torch.float32, device=dev)
+        K = int(K)
+        for k in range(K):
+            z = probes[k] if probes is not None else torch.randn(im.shape, generator=generator, device=dev)
+            _, _, g_op, g_mean, _, _, g_sc, g_rot = _C.rasterize_gaussians_backward(
+                rs.bg, pts, radii, gmap.colors, gmap.scales, gmap.rotations, rs.scale_modifier, e, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, z, e, rs.sh_degree, rs.campos, geom, R, inst, img, 2)
+            rc = L.fb_block_outer_accumulate(
+                Nv, rows.data_ptr(), g_mean.data_ptr(), g_op.data_ptr() if use_opacity else None,
+                g_rot.data_ptr() if use_rot else None, g_sc.data_ptr() if use_scale else None,
+                float(K) if k == K - 1 else 0.0, H_blocks.data_ptr(), _stream())
+            _lib.check(rc, "fb_block_outer_accumulate")
+            self.launches += 2
+        return H_blocks, vis_idx
+
+    @torch.no_grad()
+    def compute_H_train_blocks(self, gmap: GaussianMap, keyframe_w2c, K=2, generator=None, **kw):
+        """compute_H_train_blocks (gaussian_object.py:1572-1586), including its alignment rule: the running sum and
+        its index list are truncated to the smaller visible count, position by position."""
+        keyframe_w2c = torch.as_tensor(keyframe_w2c, dtype=torch.float32).reshape(-1, 4, 4)
+        Hm, vis_ref = None, None
+        for w2c in keyframe_w2c:
+            Hb, vis_idx = self.estimate_block_JtJ(gmap, w2c, K=K, generator=generator, **kw)
+            if Hm is None:
+                Hm, vis_ref = Hb, vis_idx
+            else:
+                Nv = min(Hm.shape[0], Hb.shape[0])
+                Hm = Hm[:Nv] + Hb[:Nv]
+                vis_ref = vis_ref[:Nv]
+        if Hm is None:
+            raise RuntimeError("No keyframes available for POP-GS prior (blocks).")   # :1585
+        return Hm, vis_ref
+
+    def _block_opt(self, Hm_blocks, J_blocks, lam, criterion, idx_m=None, idx_j=None, per_block=False):
+        L = _lib.lib()
+        Hm_blocks, J_blocks = _f32c(Hm_blocks), _f32c(J_blocks)
+        d = int(Hm_blocks.shape[-1])
+        if J_blocks.shape[-1] != d or Hm_blocks.shape[-2] != d:
+            raise ValueError("block shapes differ")
+        n = int(idx_m.numel()) if idx_m is not None else int(Hm_blocks.shape[0])
+        if idx_m is None and J_blocks.shape[0] != n:
+            raise ValueError("Hm_blocks and J_blocks differ in length")
+        dev = Hm_blocks.device
+        partial = torch.zeros((max(1, L.fb_block_opt_partials(n)),), dtype=torch.float64, device=dev)
+        terms = torch.empty((n,), dtype=torch.float32, device=dev) if per_block else None
+        ptr = lambda t: None if t is None else t.contiguous().data_ptr()
+        rc = L.fb_block_opt(n, d, Hm_blocks.data_ptr(), ptr(idx_m), J_blocks.data_ptr(), ptr(idx_j), float(lam),
+                            criterion, partial.data_ptr(), ptr(terms), _stream())
+        _lib.check(rc, "fb_block_opt")
+        self.launches += 1
+        total = partial.sum().to(torch.float32)
+        return (total, terms) if per_block else total
+
+    def t_opt_blocks(self, Hm_blocks, J_blocks, lam=1e-6):
+        """T-optimality over blocks, to maximise: -sum_b trace((Hm_b + J_b + lam I)^-1)   (gaussian_object.py:1720-1724)."""
+        return self._block_opt(Hm_blocks, J_blocks, lam, 0)
+
+    def d_opt_blocks(self, Hm_blocks, J_blocks, lam=1e-6):
+        """D-optimality over blocks: sum_b logdet(Hm_b + lam I + J_b) - logdet(Hm_b + lam I)   (:1726-1732)."""
+        return self._block_opt(Hm_blocks, J_blocks, lam, 1)
+
+    @torch.no_grad()
+    def pose_eval_popgs_blocks(self, gmap: GaussianMap, poses_c2w, keyframe_w2c, criterion="topt", K=6, lam=1e-6,
+                               use_rot=True, use_scale=True, use_opacity=True, generator=None):
+        """pose_eval_popgs_blocks (gaussian_object.py:1660-1703): the blocks of the Gaussians visible both in the
+        prior and from the candidate are paired by index (`np.intersect1d(..., return_indices=True)`, done here with a
+        device-side searchsorted: both lists are ascending and unique) and gathered inside `fb_block_opt`.
+        A candidate that shares no Gaussian with the prior scores -inf (:1682-1685).  Returns (scores CPU, poses)."""
+        crit = criterion.lower()
+        if crit not in ("topt", "dopt"):
+            raise ValueError("criterion must be 'topt' or 'dopt'")                    # :1694
+        kw = dict(use_rot=use_rot, use_scale=use_scale, use_opacity=use_opacity)
+        dev = gmap.means3D.device
+        Hm_blocks, train_vis_idx = self.compute_H_train_blocks(gmap, keyframe_w2c, K=K, generator=generator, **kw)
+        poses_c2w = torch.as_tensor(poses_c2w, dtype=torch.float32, device=dev).reshape(-1, 4, 4)
+        scores = []
+        for c2w in poses_c2w:
+            Jb, cur_vis_idx = self.estimate_block_JtJ(gmap, torch.linalg.inv(c2w), K=K, generator=generator, **kw)
+            scores.append(self.score_blocks(Hm_blocks, train_vis_idx, Jb, cur_vis_idx, crit, lam))
+        return torch.stack(scores).cpu(), poses_c2w
+
+    def score_blocks(self, Hm_blocks, train_vis_idx, J_blocks, cur_vis_idx, criterion="topt", lam=1e-6):
+        """The body of pose_eval_popgs_blocks' loop (:1671-1698) for one candidate: pair the prior's and the candidate's
+        blocks by Gaussian index, score the pairs; -inf when no Gaussian is shared."""
+        idx_train, idx_cur = intersect_sorted(train_vis_idx, cur_vis_idx)
+        if idx_train.numel() == 0:
+            return torch.tensor(float("-inf"), device=Hm_blocks.device)
+        return self._block_opt(Hm_blocks, J_blocks, lam, 0 if criterion.lower() == "topt" else 1, idx_train, idx_cur)
+
+
+def intersect_sorted(a, b):
+    """Positions (ia, ib) with a[ia] == b[ib] for two ascending, duplicate-free int64 tensors: what
+    `np.intersect1d(a, b, return_indices=True)[1:]` returns (gaussian_object.py:1674-1676), on the device."""
+    if a.numel() == 0 or b.numel() == 0:
+        z = torch.empty((0,), dtype=torch.int64, device=a.device)
+        return z, z
+    pos = torch.searchsorted(b, a).clamp_(max=b.numel() - 1)
+    hit = b[pos] == a
+    return torch.nonzero(hit).reshape(-1), pos[hit]

@@ -244,6 +244,34 @@ int fb_count_visible(int N, const float* points, int K, const double* w2c,
                      const double* intr, int img_w, int img_h,
                      int* counts, uint8_t* mask, void* stream);
 
+/* ---- POp-GS block form (models/SLAM/gaussian_object.py) ------------------- */
+
+/* estimate_block_JtJ's accumulation (:2160-2174), one probe per call:
+ *   H_blocks[i] (d x d row-major) += g g^T,  g = row rows[i] of
+ *   [g_mean[P,3] | g_op[P,1]? | g_rot[P,4]? | g_scale[P,3]?]   (NULL = column group absent,
+ *   the reference's use_opacity / use_rot / use_scale switches), d = 3 (+1) (+4) (+3).
+ * The product is rounded before the add like the reference's tensor expression; if
+ * divide_by != 0 every element is multiplied by fl(1/divide_by) after the add (`H_blocks / float(K)`
+ * as torch evaluates it on a CUDA tensor; folded into the last probe).  rows: i64 [Nv] device. */
+int fb_block_outer_accumulate(int Nv, const long long* rows,
+                              const float* g_mean, const float* g_op,
+                              const float* g_rot, const float* g_scale,
+                              float divide_by, float* H_blocks, void* stream);
+
+/* t_opt_blocks (:1720-1724, criterion 0):  -sum_b trace((Hm_b + J_b + lam I)^-1)
+ * d_opt_blocks (:1726-1732, criterion 1):  sum_b logabsdet(Hm_b + lam I + J_b) - logabsdet(Hm_b + lam I)
+ * over n_blocks pairs (Hm_blocks[idx_m[b]], J_blocks[idx_j[b]]); idx_* may be NULL (identity):
+ * they are the reference's `Hm_blocks[idx_train]`, `Jb[idx_cur]` gathers (:1688-1689).
+ * The FP32 matrix is formed as the reference forms it and factorised (LU, partial pivoting)
+ * in FP64.  partial: f64 [fb_block_opt_partials(n_blocks)] device, the score is their sum;
+ * per_block (optional, may be NULL): f32 [n_blocks] the per-block terms.  1 <= d <= 11. */
+int fb_block_opt_partials(int n_blocks);
+int fb_block_opt(int n_blocks, int d,
+                 const float* Hm_blocks, const long long* idx_m,
+                 const float* J_blocks, const long long* idx_j,
+                 float lam, int criterion,
+                 double* partial, float* per_block, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -283,3 +283,54 @@ def pose_eval(rs, params, poses_w2c, H_train_inv, C_H=4, grad_scale=1e-3):
         h, _ = compute_Hessian(rs, params, w2c, C_H, grad_scale)
         out.append(float(np.sum(h * np.asarray(H_train_inv, dtype=np.float64))))
     return np.array(out)
+
+
+# ---- POp-GS block form (models/SLAM/gaussian_object.py), numpy restatement ---------------------------------------
+
+def block_outer(G_rows, K=None):
+    """estimate_block_JtJ's accumulation (gaussian_object.py:2160-2174) for a list of per-probe gradient matrices
+    G_rows[k] = Gv [Nv,d] (visible rows, columns means|opacity|rotations|scales): sum_k Gv (x) Gv, divided by K.
+    FP32 with the reference's rounding points (product rounded, then added; one division at the end)."""
+    H = None
+    for Gv in G_rows:
+        Gv = np.asarray(Gv, dtype=np.float32)
+        o = (Gv[:, :, None] * Gv[:, None, :]).astype(np.float32)
+        H = o if H is None else (H + o).astype(np.float32)
+    return (H / np.float32(len(G_rows) if K is None else K)).astype(np.float32)
+
+
+def t_opt_blocks(Hm_blocks, J_blocks, lam=1e-6):
+    """t_opt_blocks (gaussian_object.py:1720-1724): -sum_b trace((Hm_b + J_b + lam I)^-1).  The matrix is formed in
+    FP32 as the reference forms it and inverted in FP64 (LAPACK LU with partial pivoting, as torch.linalg.inv)."""
+    Hm, J = np.asarray(Hm_blocks, np.float32), np.asarray(J_blocks, np.float32)
+    if Hm.shape[0] == 0:
+        return 0.0
+    I = np.eye(Hm.shape[-1], dtype=np.float32)
+    M = ((Hm + J).astype(np.float32) + np.float32(lam) * I).astype(np.float32)
+    return float(-np.einsum("bii->", np.linalg.inv(M.astype(np.float64))))
+
+
+def d_opt_blocks(Hm_blocks, J_blocks, lam=1e-6):
+    """d_opt_blocks (gaussian_object.py:1726-1732): sum_b logabsdet(Hm_b + lam I + J_b) - logabsdet(Hm_b + lam I)."""
+    Hm, J = np.asarray(Hm_blocks, np.float32), np.asarray(J_blocks, np.float32)
+    if Hm.shape[0] == 0:
+        return 0.0
+    I = np.eye(Hm.shape[-1], dtype=np.float32)
+    M0 = (Hm + np.float32(lam) * I).astype(np.float32)
+    M1 = (M0 + J).astype(np.float32)
+    return float((np.linalg.slogdet(M1.astype(np.float64))[1] - np.linalg.slogdet(M0.astype(np.float64))[1]).sum())
+
+
+def compute_H_train_blocks(per_keyframe):
+    """compute_H_train_blocks (gaussian_object.py:1572-1586) over [(H_blocks, vis_idx), ...]: positional truncation
+    to the smaller visible count."""
+    Hm, vis_ref = None, None
+    for Hb, vis in per_keyframe:
+        if Hm is None:
+            Hm, vis_ref = np.asarray(Hb, np.float32), np.asarray(vis)
+        else:
+            n = min(Hm.shape[0], Hb.shape[0])
+            Hm, vis_ref = (Hm[:n] + np.asarray(Hb, np.float32)[:n]).astype(np.float32), vis_ref[:n]
+    if Hm is None:
+        raise RuntimeError("No keyframes available for POP-GS prior (blocks).")
+    return Hm, vis_ref

@@ -3,6 +3,10 @@
   python tests/golden/make_golden.py gpu   # on the GPU box: runs the unmodified reference CUDA extensions
                                            # (oracle/_ref/ref_dgr, ref_knn; built by oracle/build_ref.py from
                                            # /root/reference) on seeded inputs -> gpurun_out/golden/*.npz
+  python tests/golden/make_golden.py blocks  # in the build container: executes the reference's own t_opt_blocks /
+                                           # d_opt_blocks / topt_score_from_diags / dopt_score_from_diags /
+                                           # compute_H_train_blocks method bodies (models/SLAM/gaussian_object.py,
+                                           # taken by AST: the module imports the whole SLAM stack) on seeded blocks
   python tests/golden/make_golden.py cpu   # in the build container: executes the reference's own numpy
                                            # count_visible_points, taken from /root/reference/tester_navigator.py
                                            # by AST (the module itself imports habitat and cannot be imported)
@@ -116,9 +120,64 @@ def cpu(out_dir):
         print(name, counts)
 
 
+BLOCK_CASES = [("blocks_a", 48, 11, 401), ("blocks_b", 33, 7, 402), ("blocks_c", 20, 3, 403)]
+
+
+def block_inputs(n, d, seed):
+    """Seeded rank-deficient PSD blocks like a few probes x a few keyframes produce (shared with the tests)."""
+    rng = np.random.default_rng(seed)
+    v = rng.standard_normal((n, 4, d)).astype(np.float32)
+    w = rng.standard_normal((n, 2, d)).astype(np.float32)
+    Hm = np.einsum("nri,nrj->nij", v, v).astype(np.float32)
+    J = np.einsum("nri,nrj->nij", w, w).astype(np.float32)
+    return Hm, J
+
+
+def _reference_methods(names):
+    import torch
+    src = open("/root/reference/models/SLAM/gaussian_object.py").read()
+    ns = {"torch": torch, "np": np}
+    for node in ast.walk(ast.parse(src)):
+        if isinstance(node, ast.FunctionDef) and node.name in names and node.name not in ns:
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "gaussian_object.py", "exec"), ns)
+    return [ns[n] for n in names]
+
+
+def blocks(out_dir):
+    import torch
+    t_opt, d_opt, t_diag, d_diag, h_train = _reference_methods(
+        ["t_opt_blocks", "d_opt_blocks", "topt_score_from_diags", "dopt_score_from_diags", "compute_H_train_blocks"])
+    for name, n, d, seed in BLOCK_CASES:
+        Hm, J = block_inputs(n, d, seed)
+        out = dict(n=n, d=d, seed=seed)
+        for lam in (1e-2, 1e-4):
+            # the reference's own arithmetic: FP32 (as the callers run it) and the same method on FP64 tensors
+            for tag, dt in (("f32", torch.float32), ("f64", torch.float64)):
+                a, b = torch.from_numpy(Hm).to(dt), torch.from_numpy(J).to(dt)
+                out[f"topt_{tag}_{lam:g}"] = float(t_opt(None, a, b, lam))
+                out[f"dopt_{tag}_{lam:g}"] = float(d_opt(None, a, b, lam))
+        hd, jd = np.einsum("bii->bi", Hm).reshape(-1), np.einsum("bii->bi", J).reshape(-1)
+        out["topt_diag"] = float(t_diag(None, torch.from_numpy(hd), torch.from_numpy(jd), 1e-6))
+        out["dopt_diag"] = float(d_diag(None, torch.from_numpy(hd), torch.from_numpy(jd), 1e-6))
+
+        # compute_H_train_blocks with three keyframes of different visible counts (its positional truncation)
+        class Stub:
+            keyframe_list = [dict(est_w2c=k) for k in range(3)]
+
+            def estimate_block_JtJ(self, w2c, K=2, **kw):
+                m = [n, n - 5, n - 2][w2c]
+                return torch.from_numpy(Hm[:m] * np.float32(w2c + 1)), torch.arange(m) * (w2c + 1)
+        Hsum, vis = h_train(Stub(), K=2)
+        out["htrain_blocks"], out["htrain_vis"] = Hsum.numpy(), vis.numpy()
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), **out)
+        print(name, {k: v for k, v in out.items() if isinstance(v, float)})
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
-    if mode == "gpu":
+    if mode == "blocks":
+        blocks(HERE)
+    elif mode == "gpu":
         gpu(os.path.join(ROOT, "gpurun_out", "golden"))
     else:
         cpu(HERE)

@@ -206,3 +206,42 @@ def test_argument_validation(oracle):
                        colors_precomp=np.zeros((0, 3), np.float32), scales=np.zeros((0, 3), np.float32),
                        rotations=np.zeros((0, 4), np.float32))
     assert f.num_rendered == 0 and not f.color.any()
+
+
+# ---- POp-GS block form: the numpy restatement against the reference's own method bodies -------------------------
+# (tests/golden/blocks_*.npz: t_opt_blocks / d_opt_blocks / *_score_from_diags / compute_H_train_blocks of
+#  models/SLAM/gaussian_object.py executed by tests/golden/make_golden.py blocks on the seeded blocks below)
+
+@pytest.mark.parametrize("name", ["blocks_a", "blocks_b", "blocks_c"])
+def test_block_scores_match_reference_golden(oracle, name):
+    from tests.golden.make_golden import block_inputs
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    Hm, J = block_inputs(int(g["n"]), int(g["d"]), int(g["seed"]))
+    for lam, rtol32 in ((1e-2, 1e-4), (1e-4, 2e-3)):       # at lam = 1e-4 the reference's FP32 LU is the noisy side
+        t, d = oracle.t_opt_blocks(Hm, J, lam), oracle.d_opt_blocks(Hm, J, lam)
+        np.testing.assert_allclose(t, float(g[f"topt_f32_{lam:g}"]), rtol=rtol32)
+        np.testing.assert_allclose(d, float(g[f"dopt_f32_{lam:g}"]), rtol=rtol32)
+        np.testing.assert_allclose(t, float(g[f"topt_f64_{lam:g}"]), rtol=1e-3 if lam < 1e-3 else 1e-4)   # FP32 rounding of "+ lam"
+        np.testing.assert_allclose(d, float(g[f"dopt_f64_{lam:g}"]), rtol=1e-3 if lam < 1e-3 else 1e-4)   # FP32 rounding of "+ lam"
+    # diagonal blocks reduce to the diagonal formulas (:1705-1718)
+    hd, jd = np.einsum("bii->bi", Hm), np.einsum("bii->bi", J)
+    Hd, Jd = np.zeros_like(Hm), np.zeros_like(J)
+    i = np.arange(Hm.shape[-1])
+    Hd[:, i, i], Jd[:, i, i] = hd, jd
+    np.testing.assert_allclose(oracle.t_opt_blocks(Hd, Jd, 1e-6), float(g["topt_diag"]), rtol=1e-5)
+    np.testing.assert_allclose(oracle.d_opt_blocks(Hd, Jd, 1e-6), float(g["dopt_diag"]), rtol=1e-5)
+    # compute_H_train_blocks: three keyframes with n, n-5, n-2 visible Gaussians -> truncated position by position
+    n = int(g["n"])
+    per_kf = [(Hm[:m] * np.float32(k + 1), np.arange(m) * (k + 1)) for k, m in enumerate([n, n - 5, n - 2])]
+    Hs, vis = oracle.compute_H_train_blocks(per_kf)
+    assert np.array_equal(Hs, g["htrain_blocks"]) and np.array_equal(vis, g["htrain_vis"])
+
+
+def test_block_outer_is_the_tensor_expression(oracle):
+    rng = np.random.default_rng(9)
+    Gs = [rng.standard_normal((17, 11)).astype(np.float32) for _ in range(3)]
+    H = oracle.block_outer(Gs)
+    want = sum(np.einsum("ni,nj->nij", G.astype(np.float64), G.astype(np.float64)) for G in Gs) / 3.0
+    np.testing.assert_allclose(H, want, rtol=1e-5, atol=1e-6)
+    assert np.array_equal(H, H.transpose(0, 2, 1))
+    assert oracle.t_opt_blocks(H[:0], H[:0]) == 0.0

@@ -75,6 +75,9 @@ __device__ __forceinline__ float score_rcp(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));                          // MUFU.RCP
     return r;
 }
+// FB_SCORE_PRESCALE (default with the single-sweep fast path): k_preprocess_score stores the conic pre-multiplied by
+// -log2(e)/2 | -log2(e) and r+g+b instead of rgb, so k_tile_score1's pair body needs no exponent scaling and no
+// colour sum (61 -> 54 instructions per surviving entry).  The two-sweep kernel reads the unscaled records.
 #define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * FB_SCORE_WPC)
 
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam cam, float grad_scale,
@@ -387,21 +390,36 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                     const float4 a = q.a[slot];
                     const float4 co = q.b[slot];
                     const float dx = a.x - pxf, dy = a.y - pyf;
+#if FB_SCORE_PRESCALE
+                    // conic pre-multiplied in k_preprocess_score: power * log2(e) = dx (A dx + B dy) + C dy^2
+                    const float power = fmaf(co.z, dy * dy, dx * fmaf(co.y, dy, co.x * dx));
+                    float G;
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power));
+#else
                     const float power = pair_power(co.x, co.y, co.z, dx, dy);
                     const float G = score_exp(power);
+#endif
                     const float alpha = fminf(0.99f, co.w * G);
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
+                    const float oma = __fsub_rn(1.f, alpha);
+                    const float test_T = __fmul_rn(T, oma);
                     const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                    const bool term = ok && test_T < 0.0001f;
-                    done = done || term;
-                    const bool upd = ok && !term;
+                    const bool upd = ok && !(test_T < 0.0001f);
+                    done = done || (ok && !upd);                         // stop BEFORE the Gaussian that takes T below 1e-4
                     if (!__any_sync(0xffffffffu, upd)) return;           // ~30 % of the entries: nobody contributes
                     const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
-                    const float inv = score_rcp(1.f - alpha);
+                    const float inv = score_rcp(oma);
+#if FB_SCORE_PRESCALE
+                    const float csum = r0.x;
+#else
                     const float csum = (r0.x + r0.y) + r0.z;
+#endif
                     const float Cn = fmaf(csum, alpha * T, Cp);
                     const float A = fmaf(T, csum, Cn * inv);
+#if FB_SCORE_PRESCALE
+                    const float c[13] = {r0.y, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
+#else
                     const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
+#endif
                     const float go = upd ? G * co.w : 0.f;               // select BEFORE the polynomial: no branch around it
                     const float g = (go * go) * eval_poly13(c, dx, dy);
                     const float gA = g * A, gB = g * inv;

@@ -366,7 +366,14 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             }
             GRec r;
             r.a = make_float4(s.px, s.py, hx, hy);
+#if FB_SCORE_PRESCALE
+            // the single-sweep scoring kernel evaluates G = ex2(dx (A dx + B dy) + C dy^2): conic pre-multiplied by
+            // -log2(e)/2, -log2(e), -log2(e)/2 (the sign of the exponent, which the `power > 0` skip tests, is kept)
+            r.b = make_float4(s.ca * -0.72134752044448170368f, s.cb * -1.4426950408889634f,
+                              s.cc * -0.72134752044448170368f, opacity);
+#else
             r.b = make_float4(s.ca, s.cb, s.cc, opacity);
+#endif
             bins.recs[(size_t)v * P + idx] = r;
         }
         __syncthreads();
@@ -397,7 +404,11 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             float coef[13];
             score_coefs<CH>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
             float4* rb = bins.recsB + ((size_t)(v0 + vv) * P + (size_t)blockIdx.x * FB_PS_THREADS + gi) * 4;
+#if FB_SCORE_PRESCALE
+            rb[0] = make_float4((S.col[0][gi] + S.col[1][gi]) + S.col[2][gi], coef[0], 0.f, 0.f);   // r+g+b: the one colour
+#else
             rb[0] = make_float4(S.col[0][gi], S.col[1][gi], S.col[2][gi], coef[0]);
+#endif
             rb[1] = make_float4(coef[1], coef[2], coef[3], coef[4]);
             rb[2] = make_float4(coef[5], coef[6], coef[7], coef[8]);
             rb[3] = make_float4(coef[9], coef[10], coef[11], coef[12]);

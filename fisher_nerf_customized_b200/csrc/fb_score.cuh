@@ -343,9 +343,10 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const uint2 range = bins.tile_range[tile_slot];
     const int n = (int)(range.y - range.x);
     if (n == 0) { if (lane == 0) *out = 0.f; return; }
-    const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
-    const float4* __restrict__ recsB = bins.recsB + (size_t)v * bins.P * 4;
-    const u64* __restrict__ sorted = bins.keys + range.x;
+    // warp-uniform 64-bit bases + 32-bit byte offsets (P <= 2^26 Gaussians): the gathers need no 64-bit address math
+    const char* __restrict__ recs = reinterpret_cast<const char*>(bins.recs + (size_t)v * bins.P);
+    const char* __restrict__ recsB = reinterpret_cast<const char*>(bins.recsB + (size_t)v * bins.P * 4);
+    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = id
     WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
 
     float T = 1.0f, Cp = 0.f, Qaa = 0.f, Qab = 0.f, Qbb = 0.f;
@@ -354,26 +355,26 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
         int qn = 0, qh = 0;
         const int nsteps = (n + 31) >> 5;
         bool v_nxt = lane < n;
-        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
+        unsigned gid_nxt = v_nxt ? sorted[2 * lane] : 0u;
         float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + (gid_nxt << 5)));
+        unsigned key2 = (32 + lane < n) ? sorted[2 * (32 + lane)] : 0u;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
                 const float4 a = a_nxt;
                 const unsigned gid = gid_nxt;
                 const bool valid = v_nxt;
                 v_nxt = (step + 1) * 32 + lane < n;
-                gid_nxt = (unsigned)(key2 & 0xffffffffull);
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+                gid_nxt = key2;
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + (gid_nxt << 5)));
+                key2 = ((step + 2) * 32 + lane < n) ? sorted[2 * ((step + 2) * 32 + lane)] : 0u;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
                     const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
                     q.a[slot] = a;
-                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
-                    const float4* rb = recsB + (size_t)gid * 4;
+                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + (gid << 5)) + 1, 16);
+                    const float4* rb = reinterpret_cast<const float4*>(recsB + (gid << 6));
 #pragma unroll
                     for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + k, 16);
                 }

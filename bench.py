@@ -180,7 +180,8 @@ def run_b200(args):
     t = {k: torch.from_numpy(v).to(dev) for k, v in sc.items()}
     gmap = fb.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"])
     rs = fb.setup_camera(W, H, synth.intrinsics(W, H), np.eye(4, dtype=np.float32), device=dev)
-    scorer = fb.FisherScorer(rs, C_H=C_H, grad_scale=GRAD_SCALE, views_per_chunk=args.views_per_chunk)
+    scorer = fb.FisherScorer(rs, C_H=C_H, grad_scale=GRAD_SCALE, views_per_chunk=args.views_per_chunk,
+                             chunk_lanes=int(os.environ.get("FB_CHUNK_LANES", "2")))
     sharded = fb.ShardedScorer(scorer)
     # untimed set-up: H_train from seeded keyframes (dealt round-robin over ranks + all-reduce), then 1/(H+lambda)
     kf = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(N_KEYFRAMES, seed=synth.SEED_POSES + 1))).to(dev)
@@ -228,15 +229,19 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     scorer.launches = 0
-    _lib.profile_enable(True)
-    _lib.profile_read()
     ms = timed(step_resident, args.steps)
-    prof = _lib.profile_read()
-    _lib.profile_enable(False)
     launches = scorer.launches
     barrier(world)
-    clocks = sampler.stop() if rank == 0 else None
     ms = max_over_ranks(ms, world)
+    # per-kernel CUDA events: the same K steps once more with fb_profile on.  While it is on the library keeps the
+    # chunks on ONE stream (no chunk lanes), so every event pair times its kernel alone, like the ncu launch list.
+    _lib.profile_enable(True)
+    _lib.profile_read()
+    ms_prof = timed(step_resident, args.steps)
+    prof = _lib.profile_read()
+    _lib.profile_enable(False)
+    barrier(world)
+    clocks = sampler.stop() if rank == 0 else None
     R_step, vis_step = scorer.last_instances, scorer.last_visible
     scores_resident = step_resident().cpu().numpy()
 
@@ -272,6 +277,9 @@ def run_b200(args):
                                f"C_H=4, lambda=0.1, H_train from {N_KEYFRAMES} keyframes", "P": P_GAUSS, "K_per_gpu": K_CAND,
                    "views_per_chunk": args.views_per_chunk, "scene": "shell seed 1234",
                    "l2": "256 MiB fill between steps, outside the timed events",
+                   "chunk_lanes": scorer.chunk_lanes,
+                   "kernel_events": "per-kernel CUDA events from a second pass of the same steps with the chunks on one "
+                                    f"stream ({ms_prof / args.steps:.3f} ms per step); value/e2e are timed without them",
                    "instances_per_view": R_step / K_CAND, "visible_per_view": vis_step / K_CAND},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": K_CAND * 64, "d2h_bytes_per_step": K_CAND * 4,
                 "ms_per_step": ms_e2e / args.steps},

@@ -52,6 +52,7 @@ SIGNATURES = {
     "fb_mark_visible": (ci, [ci, vp, C.POINTER(cf), C.POINTER(cf), vp, vp]),
     "fb_debug_export": (ci, [C.POINTER(fb_camera), ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "fb_score_workspace_bytes": (sz, [ci, ci, ci, ci, ll]),
+    "fb_score_set_lanes": (ci, [ci]),
     "fb_score_candidates": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
     "fb_accumulate_hessian": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
     "fb_knn_workspace_bytes": (sz, [ci]),

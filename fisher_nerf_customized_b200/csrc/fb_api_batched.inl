@@ -42,11 +42,14 @@ __global__ void k_debug_inst(Bins b, uint32_t* point_list, u64* point_keys) {
 
 __global__ void k_status_update(const uint32_t* total, const uint32_t* vis_count, int V, int* status) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
-        for (int v = 0; v < V; ++v) status[4] += (int)vis_count[v];
-        if (total[1]) status[0] = FB_E_CAPACITY;
-        if ((int)total[0] > status[1]) status[1] = (int)total[0];
-        if ((int)total[3] > status[2]) status[2] = (int)total[3];
-        status[3] += (int)total[0];
+        // atomics: with two chunk lanes (fb_score_candidates) two of these may run at the same time
+        int nvis = 0;
+        for (int v = 0; v < V; ++v) nvis += (int)vis_count[v];
+        atomicAdd(&status[4], nvis);
+        if (total[1]) atomicExch(&status[0], FB_E_CAPACITY);
+        atomicMax(&status[1], (int)total[0]);
+        atomicMax(&status[2], (int)total[3]);
+        atomicAdd(&status[3], (int)total[0]);
     }
 }
 __global__ void k_fill(float* p, size_t n, float v) {
@@ -132,6 +135,18 @@ size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chun
     return score_layout(P, width, height, views_per_chunk, inst_capacity).total;
 }
 
+// Two chunk lanes.  The launch sequence of a chunk is a chain of kernels with very different limits (preprocess and the
+// pair sweep issue-bound; scan, scatter and sort latency-bound at 50-57 % of the issue slots, the scan a single CTA).
+// When the caller's workspace holds two chunks (>= 2 x fb_score_workspace_bytes), consecutive chunks alternate between
+// the caller's stream and a library-owned stream, each in its own half of the workspace, so the latency-bound kernels
+// of one chunk run under the issue-bound kernels of the other.  Results are unchanged (each chunk's arithmetic is its
+// own); the caller's stream waits for the second lane before fb_score_candidates' work is complete on it.
+// While per-kernel profiling is enabled the chunks stay on one stream so that the event pairs time kernels alone.
+static cudaStream_t g_lane_stream = nullptr;
+static cudaEvent_t g_lane_fork = nullptr, g_lane_join = nullptr;
+static int g_lanes_enabled = 1;
+int fb_score_set_lanes(int on) { g_lanes_enabled = on != 0; return FB_OK; }
+
 int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c, int K, const float* weight, int C_H,
                         float grad_scale, float* scores, int* status_dev, void* workspace, size_t workspace_bytes,
                         int views_per_chunk, long long inst_capacity, void* stream_) {
@@ -156,11 +171,28 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<11>)));
         attr_set = true;
     }
-    FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
-    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
+    cudaStream_t st0 = st;
+    const int lanes = (g_lanes_enabled && !g_prof_on && K > V && workspace_bytes >= 2 * L.total) ? 2 : 1;
+    FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st0));
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st0));
+    if (lanes == 2) {
+        if (!g_lane_stream) {
+            FB_CUDA(cudaStreamCreateWithFlags(&g_lane_stream, cudaStreamNonBlocking));
+            FB_CUDA(cudaEventCreateWithFlags(&g_lane_fork, cudaEventDisableTiming));
+            FB_CUDA(cudaEventCreateWithFlags(&g_lane_join, cudaEventDisableTiming));
+        }
+        FB_CUDA(cudaEventRecord(g_lane_fork, st0));                 // after the status reset and everything queued before
+        FB_CUDA(cudaStreamWaitEvent(g_lane_stream, g_lane_fork, 0));
+        FB_CUDA(cudaMemsetAsync(ws + L.total + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, g_lane_stream));
+    }
     GaussIn gi = map_in(map);
-    for (int k0 = 0; k0 < K; k0 += V) {
+    char* const ws0 = ws;
+    int chunk = 0;
+    for (int k0 = 0; k0 < K; k0 += V, ++chunk) {
         const int Vc = (K - k0 < V) ? (K - k0) : V;
+        const int lane = (lanes == 2) ? (chunk & 1) : 0;
+        st = lane ? g_lane_stream : st0;
+        ws = ws0 + (size_t)lane * L.total;
         Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
         FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
         const float* w2c_k = w2c + (size_t)k0 * 16;
@@ -182,6 +214,10 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }
         FB_LAUNCH_CHECK();
+    }
+    if (lanes == 2) {
+        FB_CUDA(cudaEventRecord(g_lane_join, g_lane_stream));
+        FB_CUDA(cudaStreamWaitEvent(st0, g_lane_join, 0));
     }
     return FB_OK;
 }

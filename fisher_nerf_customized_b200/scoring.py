@@ -127,8 +127,13 @@ class FisherScorer:
     """Scores candidate poses by expected information gain, sum(H_candidate * 1/(H_train + lambda))."""
 
     def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=32,
-                 inst_capacity=None):
+                 inst_capacity=None, chunk_lanes=2):
+        """chunk_lanes=2: the workspace holds two chunks and `fb_score_candidates` alternates consecutive chunks
+        between the caller's stream and a second stream (latency-bound binning kernels of one chunk run under the
+        issue-bound kernels of the other); 1 = one chunk at a time, half the workspace."""
         assert C_H in (4, 11)
+        assert chunk_lanes in (1, 2)
+        self.chunk_lanes = chunk_lanes
         self.cam, self.C_H, self.grad_scale = cam, C_H, float(grad_scale)
         self.V = int(views_per_chunk)
         self.inst_capacity = inst_capacity
@@ -149,6 +154,7 @@ class FisherScorer:
         key = (gmap.P, self.V, cap, gmap.means3D.device)
         if self._ws_key != key:
             n = L.fb_score_workspace_bytes(gmap.P, self.cam.image_width, self.cam.image_height, self.V, cap)
+            n *= self.chunk_lanes
             self._ws = None
             self._ws = torch.empty((n,), dtype=torch.uint8, device=gmap.means3D.device)
             self._ws_key = key

@@ -194,6 +194,14 @@ typedef struct fb_map {
 size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk,
                                 long long inst_capacity);
 
+/* Chunk lanes.  If `workspace_bytes` >= 2 * fb_score_workspace_bytes(...) and K > views_per_chunk,
+ * fb_score_candidates alternates consecutive chunks between the caller's stream and a library-owned
+ * stream, each in its own half of the workspace (the latency-bound binning kernels of one chunk run
+ * under the issue-bound kernels of the other); the caller's stream waits for both before the call's
+ * work is complete on it.  Results do not change.  fb_score_set_lanes(0) keeps every chunk on the
+ * caller's stream; so does fb_profile_enable(1), so that its event pairs time kernels alone. */
+int fb_score_set_lanes(int on);
+
 /* scores[k] = sum_{g,c} H_k[g,c] * weight[g,c]   for k in [0,K)
  * where H_k is the Fisher diagonal of pose k: the grads compute_Hessian
  * concatenates (C_H = 4: d/dmeans3D(3), d/dopacity(1), gaussian.py:1554-1560;

@@ -296,3 +296,32 @@ def test_batched_edge_cases(cuda):
         Hinv = torch.reciprocal(H_want + 0.1)
         s = scorer.score_candidates(gmap, torch.from_numpy(np.stack([eye, eye])).cuda(), Hinv).cpu().numpy()
         np.testing.assert_allclose(s, np.full(2, float((H_want * Hinv).sum())), rtol=RTOL)
+
+
+@pytest.mark.parametrize("C_H", [4, 11])
+def test_chunk_lanes_do_not_change_scores(cuda, C_H):
+    """Two chunk lanes (consecutive chunks on two streams, two workspace halves) vs one: the same bits, the same
+    status counters; also with an odd number of chunks, a ragged last chunk, and a capacity overflow + regrow."""
+    import torch
+    W = H = 64
+    P, K = 6000, 23
+    sc = common.small_scene(P, seed=31)
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    w2c = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(K, seed=32, box=(6.0, 3.0, 6.0)))).cuda()
+    gmap = _gmap(cuda, torch, sc)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    H_inv = torch.rand((P, C_H), generator=g, device="cuda") + 0.1
+    out = {}
+    for lanes in (1, 2):
+        scorer = cuda.FisherScorer(rs, C_H=C_H, views_per_chunk=4, chunk_lanes=lanes, inst_capacity=2000)  # forces a regrow
+        s = scorer.score_candidates(gmap, w2c, H_inv)
+        # a second call on a side stream: the lanes fork from and join the CALLER's stream
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            s2 = scorer.score_candidates(gmap, w2c, H_inv)
+        side.synchronize()
+        out[lanes] = (s.cpu().numpy(), s2.cpu().numpy(), scorer.last_instances, scorer.last_visible)
+    assert np.array_equal(out[1][0], out[2][0]) and np.array_equal(out[2][0], out[2][1])
+    assert out[1][2:] == out[2][2:]
+    assert np.all(out[2][0] > 0)

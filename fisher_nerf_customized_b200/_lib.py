@@ -59,6 +59,8 @@ SIGNATURES = {
     "fb_dist2_knn3": (ci, [ci, vp, vp, vp, sz, vp]),
     "fb_count_visible": (ci, [ci, vp, ci, vp, vp, ci, ci, vp, vp, vp]),
     "fb_block_outer_accumulate": (ci, [ci, vp, vp, vp, vp, vp, cf, vp, vp]),
+    "fb_unproject_append": (ci, [ci, ci, ci, vp, vp, vp, vp, vp, ll, vp, ci, vp, ci, vp, vp, vp, ci,
+                                vp, vp]),
     "fb_block_opt_partials": (ci, [ci]),
     "fb_block_opt": (ci, [ci, ci, vp, vp, vp, vp, cf, ci, vp, vp, vp]),
 }

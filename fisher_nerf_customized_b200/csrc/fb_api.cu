@@ -9,6 +9,7 @@
 #include "fb_backward.cuh"
 #include "fb_stage5.cuh"
 #include "fb_blocks.cuh"
+#include "fb_mapupdate.cuh"
 #include <limits.h>
 #include <string.h>
 
@@ -26,9 +27,9 @@ static thread_local int g_last_cuda = 0;
 // every kernel of a class while enabled; read back (with a sync) by fb_profile_read.  Off by default.
 #include <vector>
 enum { FB_K_PREPROCESS = 0, FB_K_SCAN, FB_K_SCATTER, FB_K_SORT, FB_K_RENDER, FB_K_BWD_TILES, FB_K_EXPAND,
-       FB_K_TILE_SCORE, FB_K_FINALIZE, FB_K_KNN, FB_K_VISIBLE, FB_K_BLOCKS, FB_K_CLASSES };
+       FB_K_TILE_SCORE, FB_K_FINALIZE, FB_K_KNN, FB_K_VISIBLE, FB_K_BLOCKS, FB_K_MAPUPDATE, FB_K_CLASSES };
 static const char* const g_class_names[FB_K_CLASSES] = {"k_preprocess", "k_scan_tiles", "k_scatter_keys", "k_sort_tiles",
-    "k_render_fwd", "k_bwd_tiles", "k_expand", "k_tile_score", "k_score_finalize", "k_knn", "k_count_visible", "k_block"};
+    "k_render_fwd", "k_bwd_tiles", "k_expand", "k_tile_score", "k_score_finalize", "k_knn", "k_count_visible", "k_block", "k_unproject_append"};
 struct ProfRec { int cls; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfRec> g_prof;

@@ -364,4 +364,28 @@ int fb_block_opt(int n_blocks, int d, const float* Hm_blocks, const long long* i
     return FB_OK;
 }
 
+int fb_unproject_append(int width, int height, int downsample, const float* color, const float* depth,
+                        const float* intr, const float* c2w, const long long* pix, long long n,
+                        float* means3D, int mean_stride, float* rgb, int rgb_stride, float* unnorm_rotations,
+                        float* logit_opacities, float* log_scales, int log_scale_cols, float* mean3_sq_dist,
+                        void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (width <= 0 || height <= 0 || downsample <= 0 || n < 0 || !intr || !c2w) return FB_E_INVALID;
+    if (n == 0) return FB_OK;
+    if (!color || !depth || !means3D || !rgb || mean_stride < 3 || rgb_stride < 3 ||
+        (log_scales && log_scale_cols != 1 && log_scale_cols != 3)) return FB_E_INVALID;
+    UnprojectArgs a;
+    a.W = width; a.H = height; a.ds = downsample; a.Wd = (width + downsample - 1) / downsample;
+    if (!pix && n > (long long)a.Wd * ((height + downsample - 1) / downsample)) return FB_E_INVALID;
+    a.intr = intr; a.c2w = c2w;
+    a.color = color; a.depth = depth; a.pix = pix; a.n = n;
+    a.means3D = means3D; a.mean_stride = mean_stride; a.rgb = rgb; a.rgb_stride = rgb_stride;
+    a.rots = unnorm_rotations; a.logit_op = logit_opacities; a.log_scales = log_scales; a.ls_cols = log_scale_cols;
+    a.msd = mean3_sq_dist;
+    { FB_PROF(FB_K_MAPUPDATE); k_unproject_append<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a); }
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
 }  // extern "C"

@@ -280,6 +280,28 @@ int fb_block_opt(int n_blocks, int d,
                  float lam, int criterion,
                  double* partial, float* per_block, void* stream);
 
+/* ---- map update: densification from an RGB-D frame (models/SLAM/gaussian.py) ---- */
+
+/* get_pointcloud (:75-142, transform_pts=True, "projective" mean_sq_dist) + initialize_new_params
+ * (:299-318) for n selected pixels, written in place: row i of the outputs is pixel pix[i] of the
+ * grid downsampled by `downsample` (row-major, row length ceil(width / downsample); pix == NULL
+ * selects pixels 0..n-1).  The caller passes pointers to the FIRST NEW ROW of its parameter arrays
+ * (the reference re-allocates every array with torch.cat, :399-401).
+ *   means3D (stride mean_stride >= 3 floats), rgb (stride rgb_stride >= 3): required; with both
+ *   pointing into one [n,6] array (strides 6) the result is get_pointcloud's point_cld.
+ *   unnorm_rotations [n,4] = (1,0,0,0), logit_opacities [n] = 0, log_scales [n,log_scale_cols]
+ *   = log(sqrt(mean_sq_dist)) (3 columns, or 1 if isotropic), mean3_sq_dist [n]: each optional (NULL).
+ * color [3,H,W], depth [1,H,W], pix (i64), intr = {fx, fy, cx, cy}, c2w = 16 floats row-major (the
+ * inverse of w2c, :105): all device pointers (no host round trip of the pose). */
+int fb_unproject_append(int width, int height, int downsample,
+                        const float* color, const float* depth,
+                        const float* intr, const float* c2w,
+                        const long long* pix, long long n,
+                        float* means3D, int mean_stride, float* rgb, int rgb_stride,
+                        float* unnorm_rotations, float* logit_opacities,
+                        float* log_scales, int log_scale_cols, float* mean3_sq_dist,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

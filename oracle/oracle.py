@@ -334,3 +334,46 @@ def compute_H_train_blocks(per_keyframe):
     if Hm is None:
         raise RuntimeError("No keyframes available for POP-GS prior (blocks).")
     return Hm, vis_ref
+
+
+# ---- map update: get_pointcloud + initialize_new_params (models/SLAM/gaussian.py:75-142, 299-318), numpy ---------
+
+def get_pointcloud(color, depth, intrinsics, w2c, transform_pts=True, downsample=1, mask=None,
+                   compute_mean_sq_dist=False):
+    """FP32 restatement, operation by operation ("projective" mean_sq_dist).  color [3,H,W], depth [1,H,W]."""
+    f = np.float32
+    color, depth, K = np.asarray(color, f), np.asarray(depth, f), np.asarray(intrinsics, f)
+    H, W = color.shape[1], color.shape[2]
+    CX, CY, FX, FY = K[0][2], K[1][2], K[0][0], K[1][1]
+    xg, yg = np.meshgrid(np.arange(0, W, downsample).astype(f), np.arange(0, H, downsample).astype(f), indexing="xy")
+    xx, yy = ((xg - CX) / FX).reshape(-1), ((yg - CY) / FY).reshape(-1)
+    z = depth[0, ::downsample, ::downsample].reshape(-1)
+    pts = np.stack((xx * z, yy * z, z), axis=-1).astype(f)
+    if transform_pts:
+        c2w = np.linalg.inv(np.asarray(w2c, np.float64)).astype(f)
+        pts4 = np.concatenate((pts, np.ones((pts.shape[0], 1), f)), axis=1)
+        pts = (c2w @ pts4.T).T[:, :3].astype(f)
+    msd = None
+    if compute_mean_sq_dist:
+        sg = (f(downsample) * z / ((FX + FY) / f(2))).astype(f)
+        msd = (sg * sg).astype(f)
+    cols = np.transpose(color[:, ::downsample, ::downsample], (1, 2, 0)).reshape(-1, 3)
+    cld = np.concatenate((pts, cols), axis=-1).astype(f)
+    if mask is not None:
+        m = np.asarray(mask).reshape(H, W).astype(bool)
+        Hd, Wd = H // downsample, W // downsample
+        m = m[:Hd * downsample, :Wd * downsample].reshape(Hd, downsample, Wd, downsample).any(axis=(1, 3)).reshape(-1)
+        if m.sum() > 0:
+            cld = cld[m]
+            if msd is not None:
+                msd = msd[m]
+    return (cld, msd) if compute_mean_sq_dist else cld
+
+
+def initialize_new_params(new_pt_cld, mean3_sq_dist, isotropic=False):
+    n = new_pt_cld.shape[0]
+    ls = np.log(np.sqrt(np.asarray(mean3_sq_dist, np.float32))).astype(np.float32)
+    return {"means3D": new_pt_cld[:, :3], "rgb_colors": new_pt_cld[:, 3:6],
+            "unnorm_rotations": np.tile(np.array([1, 0, 0, 0], np.float32), (n, 1)),
+            "logit_opacities": np.zeros((n, 1), np.float32),
+            "log_scales": np.tile(ls[:, None], (1, 1 if isotropic else 3))}

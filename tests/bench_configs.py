@@ -187,14 +187,58 @@ def cfg5(steps):
             "picks_head": [int(p) for p in picks[:8]], "visible_last": int(vis_counts[-1][0])}
 
 
+def cfg5a():
+    """Map-update half of config 5: densify one 256x256 RGB-D frame (5 % of the pixels new, tester_navigator.py:380-381)
+    into a 3M-Gaussian map.  Reference arm: get_pointcloud's tensor program + initialize_new_params + the torch.cat
+    growth of add_new_gaussians (gaussian.py:83-137, 299-318, 399-401) written out with torch on the same GPU."""
+    import torch
+    import fisher_nerf_customized_b200 as fb
+    from tests.golden.make_golden import frame_inputs
+    H = W = 256
+    P = 3_000_000
+    color, depth, K, w2c, _ = frame_inputs(H, W, 5)
+    rng = np.random.default_rng(6)
+    mask = (rng.random(H * W) < 0.05) & (depth.reshape(-1) > 0.01)
+    tc, td, tK, tw, tm = [torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (color, depth, K, w2c, mask)]
+    store = fb.ResidentParams(capacity=P + 64 * 4000)
+    store.n = P
+
+    def ours():
+        store.n = P
+        store.append_from_frame(tc, td, tK, tw, mask=tm)
+    params = {k: torch.zeros((P, c), device="cuda") for k, c in fb.ResidentParams.KEYS}
+
+    def ref():
+        CX, CY, FX, FY = tK[0][2], tK[1][2], tK[0][0], tK[1][1]
+        xg, yg = torch.meshgrid(torch.arange(0, W).cuda().float(), torch.arange(0, H).cuda().float(), indexing="xy")
+        xx, yy = ((xg - CX) / FX).reshape(-1), ((yg - CY) / FY).reshape(-1)
+        z = td[0].reshape(-1)
+        pts4 = torch.cat((torch.stack((xx * z, yy * z, z), dim=-1), torch.ones(H * W, 1).cuda()), dim=1)
+        pts = (torch.inverse(tw).cuda() @ pts4.T).T[:, :3]
+        msd = ((1 * z / ((FX + FY) / 2)) ** 2)[tm]
+        cld = torch.cat((pts, torch.permute(tc, (1, 2, 0)).reshape(-1, 3)), -1)[tm]
+        n = cld.shape[0]
+        rots = torch.zeros((n, 4), device="cuda"); rots[:, 0] = 1
+        new = {"means3D": cld[:, :3], "rgb_colors": cld[:, 3:6], "unnorm_rotations": rots,
+               "logit_opacities": torch.zeros((n, 1), device="cuda"),
+               "log_scales": torch.tile(torch.log(torch.sqrt(msd))[..., None], (1, 3))}
+        return {k: torch.cat((params[k], v), dim=0) for k, v in new.items()}
+    t_ours, t_ref = ev_time(ours, 50), ev_time(ref, 20)
+    grown = ref()
+    got = store.params()
+    ok = all(torch.allclose(got[k][P:], grown[k][P:], rtol=2e-6, atol=2e-6) for k in got)
+    return {"config": "5a: map update, densify one 256x256 RGB-D frame into a 3M-Gaussian map", "new_gaussians": int(mask.sum()),
+            "b200_ms": t_ours, "reference_torch_program_ms": t_ref, "parity": {"new_rows_allclose_2e-6": bool(ok)}}
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="1,2,4,5")
+    ap.add_argument("--only", default="1,2,4,5,5a")
     ap.add_argument("--loop-steps", type=int, default=200)
     args = ap.parse_args()
     from fisher_nerf_customized_b200 import _lib
     _lib.lib()
-    todo = {"1": cfg1, "2": cfg2, "4": cfg4, "5": lambda: cfg5(args.loop_steps)}
+    todo = {"1": cfg1, "2": cfg2, "4": cfg4, "5": lambda: cfg5(args.loop_steps), "5a": cfg5a}
     for k in args.only.split(","):
         print(json.dumps(todo[k.strip()]()), flush=True)
 

@@ -7,6 +7,9 @@
                                            # d_opt_blocks / topt_score_from_diags / dopt_score_from_diags /
                                            # compute_H_train_blocks method bodies (models/SLAM/gaussian_object.py,
                                            # taken by AST: the module imports the whole SLAM stack) on seeded blocks
+  python tests/golden/make_golden.py pointcloud  # in the build container: the reference's get_pointcloud /
+                                           # initialize_new_params bodies (models/SLAM/gaussian.py, by AST) on CPU
+                                           # torch (`.cuda()` made a no-op) on seeded RGB-D frames
   python tests/golden/make_golden.py cpu   # in the build container: executes the reference's own numpy
                                            # count_visible_points, taken from /root/reference/tester_navigator.py
                                            # by AST (the module itself imports habitat and cannot be imported)
@@ -173,9 +176,60 @@ def blocks(out_dir):
         print(name, {k: v for k, v in out.items() if isinstance(v, float)})
 
 
+PCD_CASES = [("pcd_a", 48, 64, 1, 501), ("pcd_b", 48, 64, 2, 502), ("pcd_c", 40, 56, 4, 503)]
+
+
+def frame_inputs(H, W, seed):
+    """Seeded RGB-D frame, intrinsics, w2c and a non-presence-like mask (shared with the tests)."""
+    rng = np.random.default_rng(seed)
+    color = rng.random((3, H, W)).astype(np.float32)
+    depth = (0.5 + 4.0 * rng.random((1, H, W))).astype(np.float32)
+    depth[0, rng.random((H, W)) < 0.05] = 0.0                          # holes, as in sensor depth
+    K = np.array([[W / 2.0, 0, W / 2.0 - 0.5], [0, W / 2.0 + 3.0, H / 2.0 + 0.25], [0, 0, 1]], np.float32)
+    a = 0.3 + 0.1 * seed % 7
+    w2c = np.eye(4, dtype=np.float32)
+    w2c[:3, :3] = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]], np.float32)
+    w2c[:3, 3] = rng.normal(0, 1, 3).astype(np.float32)
+    mask = (rng.random(H * W) < 0.3) & (depth.reshape(-1) > 0.01)
+    return color, depth, K, w2c, mask
+
+
+def pointcloud(out_dir):
+    import torch
+    import torch.nn.functional as F
+    from einops import rearrange
+    src = open("/root/reference/models/SLAM/gaussian.py").read()
+    class TorchOnCpu:                                                  # `device="cuda"` factory calls -> CPU
+        def __getattr__(self, k):
+            v = getattr(torch, k)
+            if k in ("zeros", "ones", "eye", "tensor", "arange", "empty"):
+                return lambda *a, **kw: v(*a, **{x: y for x, y in kw.items() if x != "device"})
+            return v
+    ns = {"torch": TorchOnCpu(), "np": np, "F": F, "rearrange": rearrange}
+    for node in ast.parse(src).body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("get_pointcloud", "initialize_new_params"):
+            exec(compile(ast.Module(body=[node], type_ignores=[]), "gaussian.py", "exec"), ns)
+    torch.Tensor.cuda = lambda self, *a, **k: self                    # the reference's body calls .cuda() on everything
+    for name, H, W, ds, seed in PCD_CASES:
+        color, depth, K, w2c, mask = frame_inputs(H, W, seed)
+        t = lambda x: torch.from_numpy(x)
+        cld, msd = ns["get_pointcloud"](t(color), t(depth), t(K), t(w2c), mask=t(mask), compute_mean_sq_dist=True,
+                                        downsample=ds)
+        cld_all = ns["get_pointcloud"](t(color), t(depth), t(K), t(w2c), downsample=ds)
+        cld_cam = ns["get_pointcloud"](t(color), t(depth), t(K), t(w2c), transform_pts=False, downsample=ds)
+        pos = msd > 0
+        newp = ns["initialize_new_params"](cld[pos], msd[pos], isotropic=(ds == 2))
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), H=H, W=W, ds=ds, seed=seed, cld=cld.numpy(),
+                            msd=msd.numpy(), cld_all=cld_all.numpy(), cld_cam=cld_cam.numpy(),
+                            **{"new_" + k: v.detach().numpy() for k, v in newp.items()})
+        print(name, cld.shape, cld_all.shape, float(msd.min()), float(msd.max()))
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
-    if mode == "blocks":
+    if mode == "pointcloud":
+        pointcloud(HERE)
+    elif mode == "blocks":
         blocks(HERE)
     elif mode == "gpu":
         gpu(os.path.join(ROOT, "gpurun_out", "golden"))

@@ -245,3 +245,27 @@ def test_block_outer_is_the_tensor_expression(oracle):
     np.testing.assert_allclose(H, want, rtol=1e-5, atol=1e-6)
     assert np.array_equal(H, H.transpose(0, 2, 1))
     assert oracle.t_opt_blocks(H[:0], H[:0]) == 0.0
+
+
+# ---- map update: get_pointcloud / initialize_new_params against the reference's own function bodies -------------
+# (tests/golden/pcd_*.npz: models/SLAM/gaussian.py:75-142, 299-318 executed on CPU torch by make_golden.py pointcloud)
+
+@pytest.mark.parametrize("name", ["pcd_a", "pcd_b", "pcd_c"])
+def test_get_pointcloud_matches_reference_golden(oracle, name):
+    from tests.golden.make_golden import frame_inputs
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    H, W, ds = int(g["H"]), int(g["W"]), int(g["ds"])
+    color, depth, K, w2c, mask = frame_inputs(H, W, int(g["seed"]))
+    cld, msd = oracle.get_pointcloud(color, depth, K, w2c, mask=mask, compute_mean_sq_dist=True, downsample=ds)
+    assert cld.shape == g["cld"].shape
+    np.testing.assert_allclose(cld, g["cld"], rtol=2e-6, atol=2e-6)          # c2w @ p: summation order of the matmul
+    np.testing.assert_array_equal(cld[:, 3:], g["cld"][:, 3:])              # colours are copies
+    np.testing.assert_allclose(msd, g["msd"], rtol=1e-6)
+    np.testing.assert_allclose(oracle.get_pointcloud(color, depth, K, w2c, downsample=ds), g["cld_all"], rtol=2e-6, atol=2e-6)
+    np.testing.assert_allclose(oracle.get_pointcloud(color, depth, K, w2c, transform_pts=False, downsample=ds),
+                               g["cld_cam"], rtol=1e-6, atol=1e-7)
+    pos = msd > 0
+    new = oracle.initialize_new_params(cld[pos], msd[pos], isotropic=(ds == 2))
+    for k, v in new.items():
+        assert v.shape == g["new_" + k].shape, k
+        np.testing.assert_allclose(v, g["new_" + k], rtol=2e-6, atol=2e-6, err_msg=k)

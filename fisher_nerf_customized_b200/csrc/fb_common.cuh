@@ -31,6 +31,9 @@
 #ifndef FB_SCORE_SINGLE_PASS
 #define FB_SCORE_SINGLE_PASS 1
 #endif
+#ifndef FB_SCORE_STATS
+#define FB_SCORE_STATS 0          // 1-3: k_tile_score1 returns lane-visit counts instead of scores (measurement builds)
+#endif
 #ifndef FB_SCORE_PRESCALE
 #define FB_SCORE_PRESCALE (FB_SCORE_SINGLE_PASS && FB_SCORE_FAST)
 #endif

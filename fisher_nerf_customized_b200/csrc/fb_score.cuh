@@ -350,6 +350,9 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
 
     float T = 1.0f, Cp = 0.f, Qaa = 0.f, Qab = 0.f, Qbb = 0.f;
+#if FB_SCORE_STATS
+    float stat = 0.f;                                                    // measurement builds only (scratch/lane_stats.py)
+#endif
     bool done = !inside;
     if (!__all_sync(0xffffffffu, done)) {
         int qn = 0, qh = 0;
@@ -406,7 +409,15 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                     const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                     const bool upd = ok && !(test_T < 0.0001f);
                     done = done || (ok && !upd);                         // stop BEFORE the Gaussian that takes T below 1e-4
+#if FB_SCORE_STATS == 1
+                    stat += 1.f;                                         // (lane, survivor) visits
+#elif FB_SCORE_STATS == 3
+                    stat += upd ? 1.f : 0.f;                             // lanes that take the survivor
+#endif
                     if (!__any_sync(0xffffffffu, upd)) return;           // ~30 % of the entries: nobody contributes
+#if FB_SCORE_STATS == 2
+                    stat += 1.f;                                         // (lane, survivor) visits that run the full body
+#endif
                     const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
                     const float inv = score_rcp(oma);
 #if FB_SCORE_PRESCALE
@@ -447,6 +458,9 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const float dpix = inside ? grad_scale : 0.f;
     const float Cf = fmaf(T, (cam.bg[0] + cam.bg[1]) + cam.bg[2], Cp);     // C + T_final * bg
     float score = (dpix * dpix) * fmaf(Cf, fmaf(Cf, Qbb, -2.f * Qab), Qaa);
+#if FB_SCORE_STATS
+    score = stat;
+#endif
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
     if (lane == 0) *out = score;

@@ -26,6 +26,11 @@
  *           models/SLAM/gaussian.py:1338-1375,1503-1570 (11-column variant
  *           models/SLAM/gaussian_object.py:1940-2045)
  *
+ * Threading: one host thread per process drives the library (one process per GPU,
+ * as the reference runs).  Launches are asynchronous on the caller's stream; the
+ * profiling switch, the chunk-lane stream and the kernel-attribute set-up are
+ * process-wide state without locks.
+ *
  * The reference hands the rasteriser three std::function<char*(size_t)> resize
  * callbacks (rasterizer.h:32-34).  That is not C-ABI safe; here the caller asks
  * for sizes (fb_*_bytes) and allocates.  The one size that is only known on the

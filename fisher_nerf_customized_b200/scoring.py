@@ -87,6 +87,14 @@ class GaussianMap:
         self.scales = _f32c(scales)
         self.P = self.means3D.shape[0]
 
+    def inverse_perm(self):
+        """inverse_perm()[c] = resident row of the caller's Gaussian c (built once, on first use)."""
+        if getattr(self, "_inv_perm", None) is None:
+            inv = torch.empty_like(self.perm)
+            inv[self.perm] = torch.arange(self.P, device=self.perm.device)
+            self._inv_perm = inv
+        return self._inv_perm
+
     def to_map_order(self, per_gaussian):
         """[P, ...] tensor in the caller's order -> the resident (Morton) order."""
         return per_gaussian if self.perm is None else per_gaussian.index_select(0, self.perm)
@@ -368,9 +376,7 @@ class FisherScorer:
         if gmap.perm is None:
             rows = vis_idx
         else:                                                             # resident row of each visible Gaussian
-            inv_perm = torch.empty_like(gmap.perm)
-            inv_perm[gmap.perm] = torch.arange(gmap.P, device=dev)
-            rows = inv_perm.index_select(0, vis_idx)
+            rows = gmap.inverse_perm().index_select(0, vis_idx)
         rows = rows.contiguous()
         Nv = int(vis_idx.numel())
         d = 3 + (1 if use_opacity else 0) + (4 if use_rot else 0) + (3 if use_scale else 0)

@@ -26,6 +26,15 @@ namespace fb {
 
 #define FB_WB_X 8      // warp pixel block
 #define FB_WB_Y 4
+// pixel block of the single-sweep scoring kernel (32 pixels: 8x4 default; 4x8 and 16x2 measured)
+#ifndef FB_S1_WX
+#define FB_S1_WX 8
+#endif
+#define FB_S1_WY (32 / FB_S1_WX)
+#ifndef FB_S1_UNROLL
+#define FB_S1_UNROLL 8
+#endif
+constexpr int kS1Unroll = FB_S1_UNROLL;   // (#pragma unroll takes a constant expression, not a macro)
 
 // Warp-autonomous traversal.  There is NO block-wide barrier in the pair loops: each warp walks the
 // tile's sorted list on its own, 32 entries per step (one per lane: key, then the 16-byte {px,py,hx,hy}
@@ -332,12 +341,13 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;
     const unsigned lt = (1u << lane) - 1u;
     const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
-    const int bx = tx * FB_TILE_X + (warp & 1) * FB_WB_X, by = ty * FB_TILE_Y + (warp >> 1) * FB_WB_Y;
-    const int px = bx + (lane & 7), py = by + (lane >> 3);
+    constexpr int BPR = FB_TILE_X / FB_S1_WX;                       // pixel blocks per tile row
+    const int bx = tx * FB_TILE_X + (warp % BPR) * FB_S1_WX, by = ty * FB_TILE_Y + (warp / BPR) * FB_S1_WY;
+    const int px = bx + (lane % FB_S1_WX), py = by + (lane / FB_S1_WX);
     const bool inside = px < cam.W && py < cam.H;
     const float pxf = (float)px, pyf = (float)py;
-    const float cx = (float)bx + 0.5f * (FB_WB_X - 1), cy = (float)by + 0.5f * (FB_WB_Y - 1);
-    const float ex = 0.5f * (FB_WB_X - 1), ey = 0.5f * (FB_WB_Y - 1);
+    const float cx = (float)bx + 0.5f * (FB_S1_WX - 1), cy = (float)by + 0.5f * (FB_S1_WY - 1);
+    const float ex = 0.5f * (FB_S1_WX - 1), ey = 0.5f * (FB_S1_WY - 1);
     float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + warp;
     if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
     const uint2 range = bins.tile_range[tile_slot];
@@ -442,7 +452,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                     T = upd ? test_T : T;
                 };
                 if (cnt == 32) {
-#pragma unroll 4
+#pragma unroll kS1Unroll
                     for (int h = 0; h < 32; ++h) hit(qh + h);
                 } else {
                     for (int h = 0; h < cnt; ++h) hit(qh + h);

@@ -42,6 +42,28 @@ class ShardedScorer:
                 dist.broadcast(t, src=src, group=self.group)
         return tensors
 
+    def broadcast_appended(self, store, r0=None, n=None, src=0):
+        """Delta map update: the rows rank `src` appended to its `ResidentParams` store (the
+        `(r0, n)` that `append_from_frame` returned there) are written behind the live rows of every replica:
+        a 16-byte header, then 56 (+4 timestep) bytes per NEW Gaussian instead of 56*P for the whole map.
+        Every replica must hold the same live rows before the call.  Returns (r0, n) on every rank."""
+        dev = store.timestep.device
+        hdr = torch.tensor([int(r0 or 0), int(n or 0)], dtype=torch.int64, device=dev)
+        if self.world > 1:
+            dist.broadcast(hdr, src=src, group=self.group)
+        r0, n = (int(x) for x in hdr.tolist())
+        if self.rank != src:
+            if store.n != r0:
+                raise RuntimeError(f"replica out of step: {store.n} live rows here, owner appended at row {r0}")
+            store._grow(r0 + n)
+        if self.world > 1 and n > 0:
+            for k in sorted(store.buf):
+                dist.broadcast(store.buf[k][r0:r0 + n], src=src, group=self.group)     # contiguous row slice, in place
+            dist.broadcast(store.timestep[r0:r0 + n], src=src, group=self.group)
+        if self.rank != src:
+            store.n = r0 + n
+        return r0, n
+
     def compute_H_train(self, gmap, keyframe_w2c):
         n = keyframe_w2c.shape[0]
         mine = round_robin(n, self.world, self.rank)

@@ -87,3 +87,53 @@ def test_partition_helpers():
             assert got == list(range(K))
             rr = sorted(sum((round_robin(K, world, r) for r in range(world)), []))
             assert rr == list(range(K))
+
+
+def _append_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from fisher_nerf_customized_b200.mapupdate import ResidentParams
+        store = ResidentParams(capacity=4, device="cpu")          # small: the second update forces every replica to grow
+        sh = ShardedScorer(FakeScorer())
+        g = torch.Generator().manual_seed(7)
+        for step, n_new in enumerate((3, 5, 0)):
+            r0 = n = None
+            if rank == 0:                                          # the owner "densifies": rows written behind the live ones
+                r0, n = store.n, n_new
+                store._grow(r0 + n)
+                for k, v in store.buf.items():
+                    v[r0:r0 + n] = torch.rand((n, v.shape[1]), generator=g) + step
+                store.timestep[r0:r0 + n] = float(step)
+                store.n = r0 + n
+            got = sh.broadcast_appended(store, r0, n, src=0)
+            assert got == (sum((3, 5, 0)[:step]), n_new)
+        out[rank] = ({k: v.clone().numpy() for k, v in store.params().items()}, store.timestep[:store.n].numpy().copy(), store.n)
+        if rank == 1:                                              # a replica that missed an update refuses the next one
+            store.n -= 1
+        try:
+            sh.broadcast_appended(store, store.n if rank == 0 else None, 0, src=0)
+            out[rank] += (None,)
+        except RuntimeError as e:
+            out[rank] += (str(e),)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_delta_map_update_world2():
+    """ShardedScorer.broadcast_appended: only the appended rows travel; replicas grow in step and end up identical."""
+    world = 2
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_append_worker, args=(world, port, out), nprocs=world, join=True)
+    p0, t0, n0, e0 = out[0]
+    p1, t1, n1, e1 = out[1]
+    assert n0 == n1 == 8
+    for k in p0:
+        assert p0[k].shape[0] == 8 and np.array_equal(p0[k], p1[k]), k
+    assert np.array_equal(t0, t1) and t0.tolist() == [0, 0, 0, 1, 1, 1, 1, 1]
+    assert e0 is None and "out of step" in e1

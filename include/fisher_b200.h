@@ -26,6 +26,13 @@
  *           models/SLAM/gaussian.py:1338-1375,1503-1570 (11-column variant
  *           models/SLAM/gaussian_object.py:1940-2045)
  *
+ *   fb_block_outer_accumulate / fb_block_opt   (POp-GS block form)
+ *        <- estimate_block_JtJ, t_opt_blocks, d_opt_blocks, pose_eval_popgs_blocks
+ *           models/SLAM/gaussian_object.py:1660-1732, 2112-2176
+ *   fb_unproject_append   (map update, densification)
+ *        <- get_pointcloud + initialize_new_params + the torch.cat growth of add_new_gaussians
+ *           models/SLAM/gaussian.py:75-142, 299-318, 397-401
+ *
  * Threading: one host thread per process drives the library (one process per GPU,
  * as the reference runs).  Launches are asynchronous on the caller's stream; the
  * profiling switch, the chunk-lane stream and the kernel-attribute set-up are

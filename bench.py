@@ -300,7 +300,7 @@ def run_b200(args):
     print(json.dumps(line))
 
 
-def cpu_baseline(sc, c2w_np, H_inv, scores_gpu, max_views=3):
+def cpu_baseline(sc, c2w_np, H_inv, scores_gpu, max_views=6):
     """The CPU oracle (a scalar port of the reference's path) timed on the first candidates of the same
     workload, and used once more as the checker of the GPU scores it covers."""
     from fisher_nerf_customized_b200 import synth

@@ -45,7 +45,7 @@ class ShardedScorer:
     def broadcast_appended(self, store, r0=None, n=None, src=0):
         """Delta map update: the rows rank `src` appended to its `ResidentParams` store (the
         `(r0, n)` that `append_from_frame` returned there) are written behind the live rows of every replica:
-        a 16-byte header, then 56 (+4 timestep) bytes per NEW Gaussian instead of 56*P for the whole map.
+        a 16-byte header, then ONE broadcast of 56 (+4 timestep) bytes per NEW Gaussian instead of 56*P for the whole map.
         Every replica must hold the same live rows before the call.  Returns (r0, n) on every rank."""
         dev = store.timestep.device
         hdr = torch.tensor([int(r0 or 0), int(n or 0)], dtype=torch.int64, device=dev)
@@ -57,9 +57,20 @@ class ShardedScorer:
                 raise RuntimeError(f"replica out of step: {store.n} live rows here, owner appended at row {r0}")
             store._grow(r0 + n)
         if self.world > 1 and n > 0:
-            for k in sorted(store.buf):
-                dist.broadcast(store.buf[k][r0:r0 + n], src=src, group=self.group)     # contiguous row slice, in place
-            dist.broadcast(store.timestep[r0:r0 + n], src=src, group=self.group)
+            # one payload collective: the new rows of the five arrays + timestep packed side by side ([n, 15] floats;
+            # 13 if isotropic), instead of six launch-latency-bound broadcasts of row slices
+            keys = sorted(store.buf)
+            cols = [store.buf[k].shape[1] for k in keys]
+            pack = torch.empty((n, sum(cols) + 1), dtype=torch.float32, device=dev)
+            if self.rank == src:
+                torch.cat([store.buf[k][r0:r0 + n] for k in keys] + [store.timestep[r0:r0 + n, None]], dim=1, out=pack)
+            dist.broadcast(pack, src=src, group=self.group)
+            if self.rank != src:
+                o = 0
+                for k, c in zip(keys, cols):
+                    store.buf[k][r0:r0 + n] = pack[:, o:o + c]
+                    o += c
+                store.timestep[r0:r0 + n] = pack[:, o]
         if self.rank != src:
             store.n = r0 + n
         return r0, n

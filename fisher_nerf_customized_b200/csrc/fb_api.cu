@@ -11,6 +11,7 @@
 #include "fb_blocks.cuh"
 #include "fb_mapupdate.cuh"
 #include <limits.h>
+#include <stdlib.h>
 #include <string.h>
 
 using namespace fb;

@@ -177,7 +177,16 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st0));
     if (lanes == 2) {
         if (!g_lane_stream) {
-            FB_CUDA(cudaStreamCreateWithFlags(&g_lane_stream, cudaStreamNonBlocking));
+            // FB_LANE_PRIORITY=1 (measurement switch): the second lane at the highest stream priority, so its pending
+            // CTAs are dispatched before the caller's lane's whenever an SM slot frees
+            const char* pr = getenv("FB_LANE_PRIORITY");
+            if (pr && pr[0] == '1') {
+                int lo = 0, hi = 0;
+                FB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+                FB_CUDA(cudaStreamCreateWithPriority(&g_lane_stream, cudaStreamNonBlocking, hi));
+            } else {
+                FB_CUDA(cudaStreamCreateWithFlags(&g_lane_stream, cudaStreamNonBlocking));
+            }
             FB_CUDA(cudaEventCreateWithFlags(&g_lane_fork, cudaEventDisableTiming));
             FB_CUDA(cudaEventCreateWithFlags(&g_lane_join, cudaEventDisableTiming));
         }

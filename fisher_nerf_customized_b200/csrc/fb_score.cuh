@@ -87,6 +87,28 @@ __device__ __forceinline__ float score_rcp(float x) {
 // FB_SCORE_PRESCALE (default with the single-sweep fast path): k_preprocess_score stores the conic pre-multiplied by
 // -log2(e)/2 | -log2(e) and r+g+b instead of rgb, so k_tile_score1's pair body needs no exponent scaling and no
 // colour sum (61 -> 54 instructions per surviving entry).  The two-sweep kernel reads the unscaled records.
+// FB_HESS_FAST: k_tile_hessian (H_train path) with the scoring kernel's MUFU exp / reciprocal instead of expf and the
+// IEEE division of backward.cu:987 (both sweeps use the same exp, so their alpha decisions stay consistent); the H_train
+// path is held to rtol 1e-3 (tests/test_gpu_scoring.py), the MUFU forms are ~1e-6.
+#ifndef FB_HESS_FAST
+#define FB_HESS_FAST 0            // build switch; the default keeps the reference's arithmetic
+#endif
+__device__ __forceinline__ float hess_exp(float x) {
+#if FB_HESS_FAST
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+    return r;
+#else
+    return expf(x);
+#endif
+}
+__device__ __forceinline__ float hess_div(float a, float b) {
+#if FB_HESS_FAST
+    return a * score_rcp(b);
+#else
+    return a / b;
+#endif
+}
 #define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * FB_SCORE_WPC)
 
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam cam, float grad_scale,
@@ -552,7 +574,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, C
                     const float4 co = q.b[slot];
                     const float dx = a.x - pxf, dy = a.y - pyf;
                     const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    const float alpha = fminf(0.99f, co.w * expf(power));
+                    const float alpha = fminf(0.99f, co.w * hess_exp(power));
                     const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
                     const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                     const bool term = ok && test_T < 0.0001f;
@@ -620,12 +642,12 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, C
                     const float4 co = q.b[slot];
                     const float dx = a.x - pxf, dy = a.y - pyf;
                     const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    const float G = expf(power);
+                    const float G = hess_exp(power);
                     const float alpha = fminf(0.99f, co.w * G);
                     const bool ok = __float_as_int(a.z) < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                     if (!__any_sync(0xffffffffu, ok)) continue;
                     const float4 c3 = q.rb[0][slot];
-                    const float Tn = T / (1.f - alpha);
+                    const float Tn = hess_div(T, 1.f - alpha);
                     const float csum = (c3.x + c3.y) + c3.z;
                     const float ar = last_alpha * last_color + (1.f - last_alpha) * accum_rec;
                     float dL_dalpha = (csum - ar) * dpix * Tn;

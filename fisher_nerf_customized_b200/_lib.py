@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-# FISHER_B200_LIB: developer override used to A/B kernel variants built by scratch/variants.sh
+# FISHER_B200_LIB: developer override used to A/B kernel variants built by tools/variants.sh
 LIB_PATH = os.environ.get("FISHER_B200_LIB") or os.path.join(_PKG, "libfisher_b200.so")
 
 FB_OK, FB_E_INVALID, FB_E_WORKSPACE, FB_E_CUDA, FB_E_CAPACITY, FB_E_PREFILTERED = 0, -1, -2, -3, -4, -5
@@ -34,6 +34,7 @@ SIGNATURES = {
     "fb_error_string": (C.c_char_p, [ci]),
     "fb_last_cuda_error": (ci, []),
     "fb_version": (ci, []),
+    "fb_launch_count": (C.c_ulonglong, []),
     "fb_profile_enable": (ci, [ci]),
     "fb_profile_classes": (ci, []),
     "fb_profile_class_name": (C.c_char_p, [ci]),
@@ -51,9 +52,10 @@ SIGNATURES = {
                                 vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "fb_mark_visible": (ci, [ci, vp, C.POINTER(cf), C.POINTER(cf), vp, vp]),
     "fb_debug_export": (ci, [C.POINTER(fb_camera), ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
-    "fb_score_workspace_bytes": (sz, [ci, ci, ci, ci, ll]),
+    "fb_score_workspace_bytes": (sz, [ci, ci, ci, ci, ll, ll]),
+    "fb_hessian_workspace_bytes": (sz, [ci, ci, ci, ci, ll]),
     "fb_score_set_lanes": (ci, [ci]),
-    "fb_score_candidates": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
+    "fb_score_candidates": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, ci, cf, vp, vp, vp, sz, ci, ll, ll, vp]),
     "fb_accumulate_hessian": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
     "fb_knn_workspace_bytes": (sz, [ci]),
     "fb_dist2_knn3": (ci, [ci, vp, vp, vp, sz, vp]),

@@ -41,9 +41,11 @@ static cudaEvent_t prof_event() {
     cudaEventCreate(&e);
     return e;
 }
+static unsigned long long g_launches = 0;      // kernels of this library launched so far (every launch site sits in a ProfScope)
 struct ProfScope {
     int cls; cudaStream_t st; cudaEvent_t a;
     ProfScope(int c, cudaStream_t s) : cls(c), st(s), a(nullptr) {
+        ++g_launches;
         if (g_prof_on) { a = prof_event(); cudaEventRecord(a, st); }
     }
     ~ProfScope() {
@@ -66,9 +68,10 @@ const char* fb_error_string(int s) {
     }
 }
 int fb_last_cuda_error(void) { return g_last_cuda; }
-int fb_version(void) { return 101; }
+int fb_version(void) { return 200; }
 
 int fb_profile_enable(int on) { g_prof_on = on != 0; return FB_OK; }
+unsigned long long fb_launch_count(void) { return g_launches; }
 int fb_profile_classes(void) { return FB_K_CLASSES; }
 const char* fb_profile_class_name(int cls) { return (cls >= 0 && cls < FB_K_CLASSES) ? g_class_names[cls] : ""; }
 int fb_profile_read(float* ms_total, int* launches) {
@@ -115,8 +118,10 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     ImageLayout IL = image_layout(cam.W, cam.H);
     char* gb = (char*)geom; char* ib = (char*)image;
     Bins b;
-    b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr;
+    b.recs = (GRec*)(gb + GL.recs); b.recsB = nullptr; b.recA = nullptr; b.recB = nullptr;
     b.vis_list = (uint4*)(gb + GL.vis_list); b.vis_count = (uint32_t*)(gb + GL.vis_count);
+    b.vis_stride = (size_t)(P > 0 ? P : 1); b.key_is_slot = 0;
+    b.view_total = (u64*)(ib + IL.totals + 64);            // zeroed with the totals (256 B) before every scan
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
     b.tile_order = (uint32_t*)(ib + IL.tile_order);
     b.total = (uint32_t*)(ib + IL.totals);
@@ -269,7 +274,8 @@ int fb_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
     if (!means3D || !present) return FB_E_INVALID;
     Cam cam; memset(&cam, 0, sizeof(cam));
     for (int i = 0; i < 16; ++i) { cam.view[i] = viewmatrix[i]; cam.proj[i] = projmatrix[i]; }
-    k_mark_visible<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, cam, present);
+    cudaStream_t st = (cudaStream_t)stream_;
+    { FB_PROF(FB_K_PREPROCESS); k_mark_visible<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, cam, present); }
     FB_LAUNCH_CHECK();
     return FB_OK;
 }

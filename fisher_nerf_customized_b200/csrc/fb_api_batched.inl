@@ -1,10 +1,20 @@
 // fb_api_batched.inl -- debug export, batched scoring / H_train entry points, stage 5 entry points.
 // Included by fb_api.cu.
 
-#if FB_SCORE_SINGLE_PASS
-#define FB_SCORE_KERNEL k_tile_score1
+// FB_SCORE_PX2 (default): the pair sweep is k_tile_score2 (two pixels per lane, packed FP32); 0 selects k_tile_score1.
+#ifndef FB_SCORE_PX2
+#define FB_SCORE_PX2 1
+#endif
+#if FB_SCORE_PX2
+#define FB_SCORE_KERNEL k_tile_score2
+#define FB_SCORE_BLOCKS FB_S2_BLOCKS
+#define FB_SCORE_KWPC FB_S2_WPC
+#define FB_SCORE_KSMEM FB_S2_SMEM_BYTES
 #else
-#define FB_SCORE_KERNEL k_tile_score
+#define FB_SCORE_KERNEL k_tile_score1
+#define FB_SCORE_BLOCKS FB_TILE_WARPS
+#define FB_SCORE_KWPC FB_SCORE_WPC
+#define FB_SCORE_KSMEM FB_SCORE_SMEM_BYTES
 #endif
 
 namespace fb {
@@ -46,6 +56,7 @@ __global__ void k_status_update(const uint32_t* total, const uint32_t* vis_count
         int nvis = 0;
         for (int v = 0; v < V; ++v) nvis += (int)vis_count[v];
         atomicAdd(&status[4], nvis);
+        atomicMax(&status[5], (int)total[4]);                     // largest visible count of a view
         if (total[1]) atomicExch(&status[0], FB_E_CAPACITY);
         atomicMax(&status[1], (int)total[0]);
         atomicMax(&status[2], (int)total[3]);
@@ -57,39 +68,76 @@ __global__ void k_fill(float* p, size_t n, float v) {
     if (i < n) p[i] = v;
 }
 
+// Control words of one chunk, cleared with ONE memset per chunk: vis_count[64] | totals (uint32[64]) | view_total[64].
+#define FB_CTRL_BYTES (256 + 256 + 512)
+struct CtrlPtrs { uint32_t* vis_count; uint32_t* total; u64* view_total; };
+static CtrlPtrs ctrl_ptrs(char* base) { return CtrlPtrs{(uint32_t*)base, (uint32_t*)(base + 256), (u64*)(base + 512)}; }
+
+// Scoring workspace of one chunk lane.  Records live in the view's visible slot: [V][vis_cap] rows of 16 + 80 + 16
+// bytes (vis_cap = the caller's visible capacity, <= P), not [V][P] rows.
 struct ScoreLayout {
-    size_t recs, recsB, vis_list, vis_count, tile_count, tile_range, tile_order, totals, partial, final_T, n_contrib, color, depth,
-        dpix, keys, keys_alt, total;
+    size_t recA, recB, vis_list, ctrl, tile_count, tile_range, tile_order, partial, keys, keys_alt, total;
 };
-static ScoreLayout score_layout(int P, int W, int H, int V, long long cap) {
-    ScoreLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1), Vv = (size_t)(V > 0 ? V : 1);
-    size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y), HW = (size_t)W * H;
-    L.recs = o;       o = align_up(o + Vv * Pp * sizeof(GRec), 256);
-    L.recsB = o;      o = align_up(o + Vv * Pp * 64, 256);
-    L.vis_list = o;   o = align_up(o + Vv * Pp * 16, 256);
-    L.vis_count = o;  o = align_up(o + Vv * 4, 256);
+static ScoreLayout score_layout(int P, int W, int H, int V, long long cap, long long vis_cap) {
+    ScoreLayout L; size_t o = 0; size_t Vv = (size_t)(V > 0 ? V : 1);
+    size_t vc = (size_t)(vis_cap > 0 && vis_cap < P ? vis_cap : (P > 0 ? P : 1));
+    size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y);
+    L.recA = o;       o = align_up(o + Vv * vc * 16, 256);
+    L.recB = o;       o = align_up(o + Vv * vc * 80, 256);
+    L.vis_list = o;   o = align_up(o + Vv * vc * 16, 256);
+    L.ctrl = o;       o = align_up(o + FB_CTRL_BYTES, 256);
     L.tile_count = o; o = align_up(o + Vv * tiles * 4 * FB_TC_STRIDE, 256);
     L.tile_range = o; o = align_up(o + Vv * tiles * 8, 256);
     L.tile_order = o; o = align_up(o + Vv * tiles * 4, 256);
-    L.totals = o;     o = align_up(o + 256, 256);
     L.partial = o;    o = align_up(o + Vv * tiles * 4 * FB_TILE_WARPS, 256);
-    L.final_T = o;    o = align_up(o + Vv * HW * 4, 256);      // per view: the H_train path batches views too
-    L.n_contrib = o;  o = align_up(o + Vv * HW * 4, 256);
-    L.color = o;      o = align_up(o + Vv * HW * 12, 256);
-    L.depth = o;      o = align_up(o + Vv * HW * 4, 256);
-    L.dpix = o;       o = align_up(o + HW * 12, 256);
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.total = o;
     return L;
 }
-static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& cam, long long cap) {
+static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& cam, long long cap, long long vis_cap) {
     Bins b;
-    b.recs = (GRec*)(ws + L.recs); b.recsB = (float4*)(ws + L.recsB);
-    b.vis_list = (uint4*)(ws + L.vis_list); b.vis_count = (uint32_t*)(ws + L.vis_count);
+    b.recs = nullptr; b.recsB = nullptr;
+    b.recA = (float4*)(ws + L.recA); b.recB = (float4*)(ws + L.recB);
+    b.vis_list = (uint4*)(ws + L.vis_list);
+    b.vis_stride = (size_t)(vis_cap > 0 && vis_cap < P ? vis_cap : P); b.key_is_slot = 1;
+    CtrlPtrs c = ctrl_ptrs(ws + L.ctrl);
+    b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.tile_order = (uint32_t*)(ws + L.tile_order);
-    b.total = (uint32_t*)(ws + L.totals); b.keys = (u64*)(ws + L.keys);
+    b.keys = (u64*)(ws + L.keys);
+    b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
+    return b;
+}
+
+// H_train workspace (fb_accumulate_hessian): records and moment rows are indexed by Gaussian id, [V][P].
+struct HessLayout {
+    size_t recs, mom, vis_list, ctrl, tile_count, tile_range, tile_order, keys, keys_alt, total;
+};
+static HessLayout hess_layout(int P, int W, int H, int V, long long cap) {
+    HessLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1), Vv = (size_t)(V > 0 ? V : 1);
+    size_t tiles = (size_t)((W + FB_TILE_X - 1) / FB_TILE_X) * ((H + FB_TILE_Y - 1) / FB_TILE_Y);
+    L.recs = o;       o = align_up(o + Vv * Pp * sizeof(GRec), 256);
+    L.mom = o;        o = align_up(o + Vv * Pp * FB_NACC * 4, 256);
+    L.vis_list = o;   o = align_up(o + Vv * Pp * 16, 256);
+    L.ctrl = o;       o = align_up(o + FB_CTRL_BYTES, 256);
+    L.tile_count = o; o = align_up(o + Vv * tiles * 4 * FB_TC_STRIDE, 256);
+    L.tile_range = o; o = align_up(o + Vv * tiles * 8, 256);
+    L.tile_order = o; o = align_up(o + Vv * tiles * 4, 256);
+    L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.total = o;
+    return L;
+}
+static Bins hess_bins(const HessLayout& L, char* ws, int P, int V, const Cam& cam, long long cap) {
+    Bins b;
+    b.recs = (GRec*)(ws + L.recs); b.recsB = nullptr; b.recA = nullptr; b.recB = nullptr;
+    b.vis_list = (uint4*)(ws + L.vis_list); b.vis_stride = (size_t)P; b.key_is_slot = 0;
+    CtrlPtrs c = ctrl_ptrs(ws + L.ctrl);
+    b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
+    b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
+    b.tile_order = (uint32_t*)(ws + L.tile_order);
+    b.keys = (u64*)(ws + L.keys);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
@@ -131,79 +179,93 @@ int fb_debug_export(const fb_camera* c, int P, int num_rendered, const void* geo
     return FB_OK;
 }
 
-size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk, long long inst_capacity) {
-    return score_layout(P, width, height, views_per_chunk, inst_capacity).total;
+size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk, long long inst_capacity,
+                                long long vis_capacity) {
+    return score_layout(P, width, height, views_per_chunk, inst_capacity, vis_capacity).total;
+}
+size_t fb_hessian_workspace_bytes(int P, int width, int height, int views_per_chunk, long long inst_capacity) {
+    return hess_layout(P, width, height, views_per_chunk, inst_capacity).total;
+}
+
+// Per-device library state (function attributes are per device; the second chunk lane's stream and events belong to
+// the device they were created on).  Indexed by the CURRENT device of the calling thread, which the host side makes
+// the device of the tensors it passes (torch.cuda.device guard in _lib.py).
+struct DevState {
+    bool score_attr, hess_attr, sort_attr;
+    cudaStream_t lane_stream; cudaEvent_t lane_fork, lane_join;
+};
+static DevState g_dev[64];
+static DevState* dev_state() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return nullptr;
+    return &g_dev[d];
 }
 
 // Two chunk lanes.  The launch sequence of a chunk is a chain of kernels with very different limits (preprocess and the
-// pair sweep issue-bound; scan, scatter and sort latency-bound at 50-57 % of the issue slots, the scan a single CTA).
+// pair sweep issue-bound; scan, scatter and sort latency-bound).
 // When the caller's workspace holds two chunks (>= 2 x fb_score_workspace_bytes), consecutive chunks alternate between
 // the caller's stream and a library-owned stream, each in its own half of the workspace, so the latency-bound kernels
-// of one chunk run under the issue-bound kernels of the other.  Results are unchanged (each chunk's arithmetic is its
+// of one chunk run under the issue-bound kernels of the other.  A single chunk (K <= views_per_chunk) is split in two
+// half chunks so that small candidate sets use both lanes too.  Results are unchanged (each view's arithmetic is its
 // own); the caller's stream waits for the second lane before fb_score_candidates' work is complete on it.
 // While per-kernel profiling is enabled the chunks stay on one stream so that the event pairs time kernels alone.
-static cudaStream_t g_lane_stream = nullptr;
-static cudaEvent_t g_lane_fork = nullptr, g_lane_join = nullptr;
 static int g_lanes_enabled = 1;
 int fb_score_set_lanes(int on) { g_lanes_enabled = on != 0; return FB_OK; }
 
 int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c, int K, const float* weight, int C_H,
                         float grad_scale, float* scores, int* status_dev, void* workspace, size_t workspace_bytes,
-                        int views_per_chunk, long long inst_capacity, void* stream_) {
+                        int views_per_chunk, long long inst_capacity, long long vis_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
-        c->image_width > 4080 || c->image_height > 4080 ||
-        inst_capacity <= 0 || !status_dev) return FB_E_INVALID;
+        c->image_width <= 0 || c->image_height <= 0 || c->image_width > 4080 || c->image_height > 4080 ||
+        inst_capacity <= 0 || vis_capacity < 0 || !status_dev) return FB_E_INVALID;
     if (K == 0) return FB_OK;
     const int P = map->P;
     if (P <= 0 || !map->means3D || !map->opacities || !map->scales || !map->rotations || !map->colors || !w2c ||
         !weight || !scores || !workspace) return FB_E_INVALID;
+    const long long vcap = (vis_capacity > 0 && vis_capacity < P) ? vis_capacity : P;
+    if (vcap * 80ll >= (1ll << 32)) return FB_E_INVALID;       // 32-bit record offsets inside a view (k_tile_score*)
     Cam cam = make_cam(c);
     const int V = views_per_chunk;
-    ScoreLayout L = score_layout(P, cam.W, cam.H, V, inst_capacity);
+    ScoreLayout L = score_layout(P, cam.W, cam.H, V, inst_capacity, vcap);
     if (workspace_bytes < L.total) return FB_E_WORKSPACE;
-    char* ws = (char*)workspace;
-    static bool attr_set = false;
-    if (!attr_set) {
+    DevState* ds = dev_state();
+    if (!ds) return FB_E_CUDA;
+    if (!ds->score_attr) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
-        FB_CUDA(cudaFuncSetAttribute(FB_SCORE_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(FB_SCORE_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_KSMEM));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<4>)));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<11>)));
-        attr_set = true;
+        ds->score_attr = true; ds->sort_attr = true;
     }
     cudaStream_t st0 = st;
-    const int lanes = (g_lanes_enabled && !g_prof_on && K > V && workspace_bytes >= 2 * L.total) ? 2 : 1;
+    const int lanes = (g_lanes_enabled && !g_prof_on && K > 1 && workspace_bytes >= 2 * L.total) ? 2 : 1;
+    // chunk size: V views, or half the candidates when they all fit in one chunk and there are two lanes
+    const int Vstep = (lanes == 2 && K <= V) ? (K + 1) / 2 : V;
+    char* ws = (char*)workspace;
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st0));
-    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st0));
+    const size_t tc_bytes = (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE;
+    FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, tc_bytes, st0));
     if (lanes == 2) {
-        if (!g_lane_stream) {
-            // FB_LANE_PRIORITY=1 (measurement switch): the second lane at the highest stream priority, so its pending
-            // CTAs are dispatched before the caller's lane's whenever an SM slot frees
-            const char* pr = getenv("FB_LANE_PRIORITY");
-            if (pr && pr[0] == '1') {
-                int lo = 0, hi = 0;
-                FB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-                FB_CUDA(cudaStreamCreateWithPriority(&g_lane_stream, cudaStreamNonBlocking, hi));
-            } else {
-                FB_CUDA(cudaStreamCreateWithFlags(&g_lane_stream, cudaStreamNonBlocking));
-            }
-            FB_CUDA(cudaEventCreateWithFlags(&g_lane_fork, cudaEventDisableTiming));
-            FB_CUDA(cudaEventCreateWithFlags(&g_lane_join, cudaEventDisableTiming));
+        if (!ds->lane_stream) {
+            FB_CUDA(cudaStreamCreateWithFlags(&ds->lane_stream, cudaStreamNonBlocking));
+            FB_CUDA(cudaEventCreateWithFlags(&ds->lane_fork, cudaEventDisableTiming));
+            FB_CUDA(cudaEventCreateWithFlags(&ds->lane_join, cudaEventDisableTiming));
         }
-        FB_CUDA(cudaEventRecord(g_lane_fork, st0));                 // after the status reset and everything queued before
-        FB_CUDA(cudaStreamWaitEvent(g_lane_stream, g_lane_fork, 0));
-        FB_CUDA(cudaMemsetAsync(ws + L.total + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, g_lane_stream));
+        FB_CUDA(cudaEventRecord(ds->lane_fork, st0));                 // after the status reset and everything queued before
+        FB_CUDA(cudaStreamWaitEvent(ds->lane_stream, ds->lane_fork, 0));
+        FB_CUDA(cudaMemsetAsync(ws + L.total + L.tile_count, 0, tc_bytes, ds->lane_stream));
     }
     GaussIn gi = map_in(map);
     char* const ws0 = ws;
     int chunk = 0;
-    for (int k0 = 0; k0 < K; k0 += V, ++chunk) {
-        const int Vc = (K - k0 < V) ? (K - k0) : V;
+    for (int k0 = 0; k0 < K; k0 += Vstep, ++chunk) {
+        const int Vc = (K - k0 < Vstep) ? (K - k0) : Vstep;
         const int lane = (lanes == 2) ? (chunk & 1) : 0;
-        st = lane ? g_lane_stream : st0;
+        st = lane ? ds->lane_stream : st0;
         ws = ws0 + (size_t)lane * L.total;
-        Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
-        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
+        Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity, vcap);
+        FB_CUDA(cudaMemsetAsync(ws + L.ctrl, 0, FB_CTRL_BYTES, st));
         const float* w2c_k = w2c + (size_t)k0 * 16;
         const dim3 ps_grid((P + FB_PS_THREADS - 1) / FB_PS_THREADS, min(FB_PS_SPLIT, (Vc + FB_PS_VG - 1) / FB_PS_VG));
         if (C_H == 4)
@@ -211,22 +273,22 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         else
             { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
+        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<Vc, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();
-        k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
-        int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
+        ++g_launches; k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
+        int sblocks = (int)((b.vis_stride + 255) / 256); if (sblocks > 148 * 2) sblocks = 148 * 2;
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_TILE_SCORE); FB_SCORE_KERNEL<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
+        { FB_PROF(FB_K_TILE_SCORE); FB_SCORE_KERNEL<<<dim3(b.tiles * (FB_SCORE_BLOCKS / FB_SCORE_KWPC), Vc), 32 * FB_SCORE_KWPC, FB_SCORE_KSMEM, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }
+        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_SCORE_BLOCKS, scores + k0); }
         FB_LAUNCH_CHECK();
     }
     if (lanes == 2) {
-        FB_CUDA(cudaEventRecord(g_lane_join, g_lane_stream));
-        FB_CUDA(cudaStreamWaitEvent(st0, g_lane_join, 0));
+        FB_CUDA(cudaEventRecord(ds->lane_join, ds->lane_stream));
+        FB_CUDA(cudaStreamWaitEvent(st0, ds->lane_join, 0));
     }
     return FB_OK;
 }
@@ -236,38 +298,40 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
                           long long inst_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
+        c->image_width <= 0 || c->image_height <= 0 || c->image_width > 4080 || c->image_height > 4080 ||
         inst_capacity <= 0 || !status_dev)
-        return FB_E_INVALID;
+        return FB_E_INVALID;                                   // (tile coordinates are packed in 8 bits: 4080 px)
     if (K == 0) return FB_OK;
     const int P = map->P;
     if (P <= 0 || !map->means3D || !map->opacities || !map->scales || !map->rotations || !map->colors || !w2c ||
         !H_out || !workspace) return FB_E_INVALID;
     Cam cam = make_cam(c);
-    ScoreLayout L = score_layout(P, cam.W, cam.H, views_per_chunk, inst_capacity);
+    HessLayout L = hess_layout(P, cam.W, cam.H, views_per_chunk, inst_capacity);
     if (workspace_bytes < L.total) return FB_E_WORKSPACE;
     char* ws = (char*)workspace;
-    static bool attr_set = false;
-    if (!attr_set) {
+    DevState* ds = dev_state();
+    if (!ds) return FB_E_CUDA;
+    if (!ds->hess_attr) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(k_tile_hessian, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
-        attr_set = true;
+        ds->hess_attr = true; ds->sort_attr = true;
     }
     const int V = views_per_chunk;
-    float* mom = (float*)(ws + L.recsB);   // [V][P][16] floats: exactly the scoring-record region
+    float* mom = (float*)(ws + L.mom);     // [V][P][16] floats
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
-    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)V * P * FB_NACC * 4, st));
+    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)V * P * FB_NACC * 4, st));     // k_expand_H clears the rows it consumes
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
     GaussIn gi = map_in(map);
     // V keyframes per launch sequence: a single 256x256 view is 256 CTAs, less than two per SM
     for (int k0 = 0; k0 < K; k0 += V) {
         const int Vc = (K - k0 < V) ? (K - k0) : V;
-        Bins b = score_bins(L, ws, P, Vc, cam, inst_capacity);
+        Bins b = hess_bins(L, ws, P, Vc, cam, inst_capacity);
         const float* w2c_k = w2c + (size_t)k0 * 16;
-        FB_CUDA(cudaMemsetAsync(b.vis_count, 0, (size_t)V * 4, st));
+        FB_CUDA(cudaMemsetAsync(ws + L.ctrl, 0, FB_CTRL_BYTES, st));
         { FB_PROF(FB_K_PREPROCESS); k_preprocess<true, 0><<<dim3((P + 255) / 256, min(FB_PS_SPLIT, Vc)), 256, Vc * 48, st>>>(gi, cam, w2c_k, b, nullptr, nullptr, nullptr, nullptr); }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<1, 1024, 0, st>>>(b); }
-        k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
+        { FB_PROF(FB_K_SCAN); k_scan_tiles<<<Vc, 1024, 0, st>>>(b); }
+        ++g_launches; k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
@@ -309,6 +373,7 @@ int fb_dist2_knn3(int P, const float* points, float* mean_dist2, void* workspace
     size_t need; KnnWs w = knn_ws(P, workspace, &need);
     if (workspace_bytes < need) return FB_E_WORKSPACE;
     const unsigned n = w.cap + 1, nb = (n + 1024 * FB_SCAN_ITEMS - 1) / (1024 * FB_SCAN_ITEMS);
+    g_launches += 8;                                   // the eight helper kernels below; the query counts itself
     k_knn_init<<<148 * 4, 256, 0, st>>>(w);
     k_knn_bbox<<<148 * 4, 256, 0, st>>>(P, points, w);
     k_knn_setup<<<1, 32, 0, st>>>(P, w);

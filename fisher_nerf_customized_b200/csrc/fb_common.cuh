@@ -23,21 +23,6 @@
 
 #define FB_TILE_PIX (FB_TILE_X * FB_TILE_Y)
 
-// Build switches of the scoring path (documented in fb_score.cuh); defaults live here because the record writer
-// (k_preprocess_score, fb_stage12.cuh) and the record reader (k_tile_score1, fb_score.cuh) must agree.
-#ifndef FB_SCORE_FAST
-#define FB_SCORE_FAST 1
-#endif
-#ifndef FB_SCORE_SINGLE_PASS
-#define FB_SCORE_SINGLE_PASS 1
-#endif
-#ifndef FB_SCORE_STATS
-#define FB_SCORE_STATS 0          // 1-3: k_tile_score1 returns lane-visit counts instead of scores (measurement builds)
-#endif
-#ifndef FB_SCORE_PRESCALE
-#define FB_SCORE_PRESCALE (FB_SCORE_SINGLE_PASS && FB_SCORE_FAST)
-#endif
-
 namespace fb {
 
 typedef unsigned long long u64;

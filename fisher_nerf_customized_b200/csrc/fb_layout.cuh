@@ -26,10 +26,16 @@ struct __align__(16) GRec {
 
 // View-batched binning state.  All arrays are [V][...] with the given strides.
 struct Bins {
-    GRec*     recs;        // [V][P]
-    float4*   recsB;       // [V][P][4]  scoring only: {rgb, coef0 | coef1-4 | coef5-8 | coef9-12}
-    uint4*    vis_list;    // [V][P]   visible Gaussians, unordered: {id, depth bits, x0|y0<<8|x1<<16|y1<<24, 0}
+    GRec*     recs;        // [V][P]   drop-in and H_train paths: indexed by Gaussian id
+    float4*   recsB;       // unused by the kernels (the H_train path keeps its moment rows in that region)
+    // scoring path: records live in the view's VISIBLE SLOT (dense, coalesced writes, arrays sized by vis_stride, not P)
+    float4*   recA;        // [V][vis_stride]     {px, py, hx, hy}: all the tile-list scan needs
+    float4*   recB;        // [V][vis_stride][5]  {conic', opacity | r+g+b, coef0, -, - | coef1-4 | coef5-8 | coef9-12}
+    uint4*    vis_list;    // [V][vis_stride]   visible Gaussians, unordered: {id, depth bits, x0|y0<<8|x1<<16|y1<<24, 0}
+    size_t    vis_stride;  // entries per view in vis_list (P, or the scoring path's visible capacity)
+    int       key_is_slot; // scoring path: the low word of a key is the visible slot, not the Gaussian id
     uint32_t* vis_count;   // [V]
+    u64*      view_total;  // [V]  chained scan: (1 << 32 | instances of the view) once published (zeroed per chunk)
     uint32_t* tile_count;  // [V][tiles][FB_TC_STRIDE]  instances per tile (cursor of the scatter); one counter per
                            // 128-byte line: atomics on one L2 line serialise, 32 hot counters per line cost 10x
     uint2*    tile_range;  // [V][tiles]   [start,end) into keys
@@ -56,7 +62,7 @@ static inline __host__ GeomLayout geom_layout(int P) {
     return L;
 }
 struct ImageLayout {
-    size_t final_T, n_contrib, tile_range, tile_count, tile_order, totals, total;
+    size_t final_T, n_contrib, tile_range, tile_count, tile_order, totals, total;   // totals: uint32[16] counters, then u64 view_total[1]
 };
 static inline __host__ ImageLayout image_layout(int W, int H) {
     ImageLayout L; size_t o = 0; size_t HW = (size_t)W * H;

@@ -1,32 +1,28 @@
-// fb_score.cuh -- fused per-(view, tile) candidate-scoring kernel.
+// fb_score.cuh -- fused per-(view, tile) candidate-scoring kernels and the H_train moment kernel.
 //
-// One CTA owns one 16x16 tile of one candidate view; its depth-sorted key segment was produced by
-// k_scatter_keys + k_sort_tiles.  Without leaving the SM it does
-//   (1) front-to-back transmittance pass -> T_final, n_contrib per pixel (registers)      [stage 3]
-//   (2) back-to-front pass: per contributing pair, s = G*o*dL/dalpha and
-//       score += s^2 * poly_g(dx,dy)                                                      [stage 4]
-//   (3) warp reduce -> one float per (view, tile, pixel block); k_score_finalize sums them in fixed order.
-// No image, no final_T/n_contrib round trip, no per-Gaussian Hessian tensor, no atomics.
+// A warp owns one pixel block of one 16x16 tile of one candidate view; the tile's depth-sorted key segment was
+// produced by k_scatter_keys + k_sort_tiles.  Without leaving the SM it makes ONE front-to-back sweep that carries
+// the transmittance and three accumulators per pixel (see "single sweep" below) and reduces them to one float per
+// (view, tile, pixel block); k_score_finalize sums those in fixed order.  No image, no final_T / n_contrib round
+// trip, no per-Gaussian Hessian tensor, no atomics.
 // Replaces the K-iteration Python loop  models/SLAM/gaussian.py:1362-1370  (+ compute_Hessian
 // :1503-1570) around renderCUDA / renderCUDAFused (forward.cu:261-393, backward.cu:850-1140).
 //
 // Pair culling.  The reference tests every pixel of a tile against every Gaussian binned to it and
-// rejects most pairs with `power > 0` / `alpha < 1/255`.  Here each warp owns an 8x4 pixel block and
-// first tests 32 staged Gaussians at once (one per lane) against the block with the precomputed half
-// extents of the alpha >= 1/255 footprint (GRec.a.zw, see k_preprocess); a ballot gives the short,
-// still depth-ordered list of Gaussians that can touch the block, and only those run the pair
-// arithmetic.  A culled pair is one the reference's own alpha test skips, and skipped pairs change no
-// state (T, accum_rec, last_alpha are only updated after the tests), so every pixel's result is
-// unchanged; the per-pair arithmetic itself is identical (pair_power / expf as compiled).
+// rejects most pairs with `power > 0` / `alpha < 1/255`.  Here each warp first tests 32 list entries at once (one per
+// lane) against its pixel block with the precomputed half extents of the alpha >= 1/255 footprint (recA.zw, see
+// k_preprocess_score); a ballot gives the short, still depth-ordered list of Gaussians that can touch the block, and
+// only those run the pair arithmetic.  A culled pair is one the reference's own alpha test skips, and skipped pairs
+// change no state, so every pixel's result is unchanged.
 #pragma once
 #include "fb_stage12.cuh"
 #include <cuda_pipeline.h>
 
 namespace fb {
 
-#define FB_WB_X 8      // warp pixel block
+#define FB_WB_X 8      // warp pixel block of the H_train moment kernel
 #define FB_WB_Y 4
-// pixel block of the single-sweep scoring kernel (32 pixels: 8x4 default; 4x8 and 16x2 measured)
+// pixel block of k_tile_score1 (32 pixels, one per lane: 8x4 default; 4x8 and 16x2 measured)
 #ifndef FB_S1_WX
 #define FB_S1_WX 8
 #endif
@@ -38,18 +34,18 @@ constexpr int kS1Unroll = FB_S1_UNROLL;   // (#pragma unroll takes a constant ex
 
 // Warp-autonomous traversal.  There is NO block-wide barrier in the pair loops: each warp walks the
 // tile's sorted list on its own, 32 entries per step (one per lane: key, then the 16-byte {px,py,hx,hy}
-// half of the record, both prefetched one / two steps ahead), culls them against its 8x4 pixel block
+// record, both prefetched one / two steps ahead), culls them against its pixel block
 // and appends the survivors, in order, to a 64-entry ring in shared memory that is private to the
-// warp.  The appending lane also starts a cp.async of the rest of the record (conic+opacity, and in the
-// backward pass the 64-byte scoring record) into the ring slot, so by the time 32 survivors have
+// warp.  The appending lane also starts a cp.async of the 80-byte scoring record (conic+opacity, colour, 13
+// coefficients) into the ring slot, so by the time 32 survivors have
 // queued up their data has landed; the warp then runs the pair arithmetic for those 32 entries with
 // broadcast shared-memory reads.  Warps of a tile never wait for each other (pixel blocks differ a lot
-// in how many Gaussians touch them), and a warp whose 32 pixels are saturated stops scanning.
+// in how many Gaussians touch them), and a warp whose pixels are saturated stops scanning.
 #define FB_WQ 64   // ring entries per warp
 struct WarpQ {
-    float4 a[FB_WQ];       // px, py, list position (as int bits), -
-    float4 b[FB_WQ];       // conic a, b, c, opacity
-    float4 rb[4][FB_WQ];   // rgb+coef0 | coef1-4 | coef5-8 | coef9-12   (backward pass only)
+    float4 a[FB_WQ];       // px, py, hx, hy
+    float4 b[FB_WQ];       // conic a, b, c (pre-multiplied by -log2(e)/2, -log2(e), -log2(e)/2), opacity
+    float4 rb[4][FB_WQ];   // r+g+b, coef0, -, - | coef1-4 | coef5-8 | coef9-12
 };
 // Warps per CTA.  A warp never talks to another warp, so the CTA is only a launch unit: small CTAs let the
 // SM backfill as soon as a warp's pixel block is finished (with 8-warp CTAs 23 % of all warp samples sat in
@@ -58,46 +54,30 @@ struct WarpQ {
 #define FB_SCORE_WPC 4
 #endif
 #define FB_TILE_WARPS (FB_TILE_PIX / 32)
-// FB_SCORE_FAST (default): the scoring path evaluates exp with MUFU.EX2 (ex2.approx(x*log2e), |x| <= 5.6 here so
-// <= 6 ulp), 1/(1-alpha) with MUFU.RCP, and runs the colour recurrence of backward.cu:997-1008 once on r+g+b
-// (dL/dpix is the same scalar for the three channels in compute_Hessian, gaussian.py:1549, and the recurrence is
-// linear).  These differ from the reference's compiled arithmetic by a few ulp per pair; scores stay far inside the
-// stated rtol 1e-3 (tests/test_gpu_scoring.py).  The drop-in rasteriser kernels keep the as-compiled arithmetic.
-#ifndef FB_SCORE_FAST
-#define FB_SCORE_FAST 1
-#endif
-// FB_SCORE_SINGLE_PASS (default): k_tile_score1 below; 0 selects the two-sweep kernel k_tile_score.
-#ifndef FB_SCORE_SINGLE_PASS
-#define FB_SCORE_SINGLE_PASS 1
-#endif
-__device__ __forceinline__ float score_exp(float x) {
-#if FB_SCORE_FAST
-    float r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));   // FMUL + MUFU.EX2
-    return r;
-#else
-    return expf(x);
-#endif
-}
+// The scoring path evaluates exp with MUFU.EX2 on an exponent that arrives pre-scaled by log2(e) (|x| <= 8 here, <= 2
+// ulp), 1/(1-alpha) with MUFU.RCP, and runs the colour recurrence of backward.cu:997-1008 once on r+g+b (dL/dpix is
+// the same scalar for the three channels in compute_Hessian, gaussian.py:1549, and the recurrence is linear).  These
+// differ from the reference's compiled arithmetic by a few ulp per pair; scores stay far inside the stated rtol 1e-3
+// (tests/test_gpu_scoring.py).  The drop-in rasteriser kernels keep the as-compiled arithmetic.
 __device__ __forceinline__ float score_rcp(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));                          // MUFU.RCP
     return r;
 }
-// FB_SCORE_PRESCALE (default with the single-sweep fast path): k_preprocess_score stores the conic pre-multiplied by
-// -log2(e)/2 | -log2(e) and r+g+b instead of rgb, so k_tile_score1's pair body needs no exponent scaling and no
-// colour sum (61 -> 54 instructions per surviving entry).  The two-sweep kernel reads the unscaled records.
+__device__ __forceinline__ float score_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));                          // MUFU.EX2
+    return r;
+}
 // FB_HESS_FAST: k_tile_hessian (H_train path) with the scoring kernel's MUFU exp / reciprocal instead of expf and the
 // IEEE division of backward.cu:987 (both sweeps use the same exp, so their alpha decisions stay consistent); the H_train
 // path is held to rtol 1e-3 (tests/test_gpu_scoring.py), the MUFU forms are ~1e-6.
 #ifndef FB_HESS_FAST
-#define FB_HESS_FAST 0            // build switch; the default keeps the reference's arithmetic
+#define FB_HESS_FAST 1
 #endif
 __device__ __forceinline__ float hess_exp(float x) {
 #if FB_HESS_FAST
-    float r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
-    return r;
+    return score_ex2(x * 1.4426950408889634f);
 #else
     return expf(x);
 #endif
@@ -111,232 +91,7 @@ __device__ __forceinline__ float hess_div(float a, float b) {
 }
 #define FB_SCORE_SMEM_BYTES ((int)sizeof(WarpQ) * FB_SCORE_WPC)
 
-__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam cam, float grad_scale,
-                                                           float* __restrict__ partial) {
-    extern __shared__ float4 smem[];
-    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;      // CTAs per tile
-    // CTAs are dispatched in linear block order; tile_order lists the (view, tile) slots of the chunk by
-    // descending instance count, so the longest lists start first and the grid drains evenly.
-    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
-    const int tile_slot = (int)bins.tile_order[lin / CPT];
-    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
-    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
-    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;   // pixel block of the tile, 0..7
-    const unsigned lt = (1u << lane) - 1u;
-    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
-    // warp -> 8x4 pixel block of the tile, lane -> pixel of the block
-    const int bx = tx * FB_TILE_X + (warp & 1) * FB_WB_X, by = ty * FB_TILE_Y + (warp >> 1) * FB_WB_Y;
-    const int px = bx + (lane & 7), py = by + (lane >> 3);
-    const bool inside = px < cam.W && py < cam.H;
-    const float pxf = (float)px, pyf = (float)py;
-    const float cx = (float)bx + 0.5f * (FB_WB_X - 1), cy = (float)by + 0.5f * (FB_WB_Y - 1);
-    const float ex = 0.5f * (FB_WB_X - 1), ey = 0.5f * (FB_WB_Y - 1);
-    float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + warp;
-    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
-    const uint2 range = bins.tile_range[tile_slot];
-    const int n = (int)(range.y - range.x);
-    if (n == 0) { if (lane == 0) *out = 0.f; return; }
-    const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
-    const float4* __restrict__ recsB = bins.recsB + (size_t)v * bins.P * 4;
-    const u64* __restrict__ sorted = bins.keys + range.x;
-    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
-
-    // (1) transmittance pass (forward.cu:330-379 without colour / depth)
-    float T = 1.0f;
-    int last = 0;
-    bool done = !inside;
-    if (!__all_sync(0xffffffffu, done)) {
-        int qn = 0, qh = 0;
-        const int nsteps = (n + 31) >> 5;
-        bool v_nxt = lane < n;
-        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
-        for (int step = 0; step <= nsteps; ++step) {
-            unsigned mask = 0u;
-            if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < n;
-                gid_nxt = (unsigned)(key2 & 0xffffffffull);
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
-                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
-                mask = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
-                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(step * 32 + lane), 0.f);
-                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
-                }
-                __pipeline_commit();
-                qn += __popc(mask);
-            }
-            const bool flush = (step == nsteps);
-            if (qn >= 32 || (flush && qn > 0)) {
-                const int cnt = min(qn, 32);
-                __pipeline_wait_prior(0);
-                __syncwarp();
-#if FB_SCORE_FAST
-                // branch-free: nearly every entry of the ring has a contributing lane, so the skips of
-                // forward.cu:343-358 become predicates and selects instead of divergent branches
-#pragma unroll 4
-                for (int h = 0; h < cnt; ++h) {
-                    const int slot = (qh + h) & (FB_WQ - 1);
-                    const float4 a = q.a[slot];
-                    const float4 co = q.b[slot];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    const float alpha = fminf(0.99f, co.w * score_exp(power));
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-                    const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                    const bool term = ok && test_T < 0.0001f;
-                    done = done || term;
-                    const bool upd = ok && !term;
-                    T = upd ? test_T : T;
-                    last = upd ? __float_as_int(a.z) + 1 : last;
-                }
-#else
-                for (int h = 0; h < cnt; ++h) {
-                    if (done) continue;
-                    const int slot = (qh + h) & (FB_WQ - 1);
-                    const float4 a = q.a[slot];
-                    const float4 co = q.b[slot];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    if (power > 0.0f) continue;
-                    const float alpha = fminf(0.99f, co.w * score_exp(power));
-                    if (alpha < 1.0f / 255.0f) continue;
-                    const float test_T = __fmul_rn(T, __fsub_rn(1.f, alpha));
-                    if (test_T < 0.0001f) { done = true; continue; }
-                    T = test_T;
-                    last = __float_as_int(a.z) + 1;
-                }
-#endif
-                __syncwarp();
-                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
-                if (__all_sync(0xffffffffu, done)) break;
-            }
-        }
-        __pipeline_wait_prior(0);
-        __syncwarp();
-    }
-
-    // (2) back-to-front scoring pass (backward.cu:939-1038)
-    const int warp_last = __reduce_max_sync(0xffffffffu, last);
-    const float T_final = T;
-    const float dpix = inside ? grad_scale : 0.f;
-    const float bgdot = (cam.bg[0] + cam.bg[1] + cam.bg[2]) * dpix;
-    float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
-    float last_alpha = 0.f;
-    float score = 0.f;
-    if (warp_last > 0) {
-        // step s, lane l looks at list position warp_last-1 - (32 s + l): descending depth order
-        int qn = 0, qh = 0;
-        const int nsteps = (warp_last + 31) >> 5;
-        bool v_nxt = lane < warp_last;
-        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[warp_last - 1 - lane] & 0xffffffffull) : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-        u64 key2 = (32 + lane < warp_last) ? sorted[warp_last - 1 - 32 - lane] : 0ull;
-        for (int step = 0; step <= nsteps; ++step) {
-            if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < warp_last;
-                gid_nxt = (unsigned)(key2 & 0xffffffffull);
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-                key2 = ((step + 2) * 32 + lane < warp_last) ? sorted[warp_last - 1 - (step + 2) * 32 - lane] : 0ull;
-                const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
-                const unsigned mask = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
-                    q.a[slot] = make_float4(a.x, a.y, __int_as_float(warp_last - 1 - (step * 32 + lane)), 0.f);
-                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
-                    const float4* rb = recsB + (size_t)gid * 4;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + k, 16);
-                }
-                __pipeline_commit();
-                qn += __popc(mask);
-            }
-            const bool flush = (step == nsteps);
-            if (qn >= 32 || (flush && qn > 0)) {
-                const int cnt = min(qn, 32);
-                __pipeline_wait_prior(0);
-                __syncwarp();
-#if FB_SCORE_FAST
-                for (int h = 0; h < cnt; ++h) {
-                    const int slot = (qh + h) & (FB_WQ - 1);
-                    const float4 a = q.a[slot];
-                    const float4 co = q.b[slot];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    const float G = score_exp(power);
-                    const float alpha = fminf(0.99f, co.w * G);
-                    const bool ok = __float_as_int(a.z) < last && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-                    if (!__any_sync(0xffffffffu, ok)) continue;          // a quarter of the entries: nobody contributes
-                    const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
-                    const float inv1ma = score_rcp(1.f - alpha);
-                    const float Tn = T * inv1ma;
-                    const float csum = (r0.x + r0.y) + r0.z;
-                    const float ar = last_alpha * last_color[0] + (1.f - last_alpha) * accum_rec[0];
-                    float dL_dalpha = (csum - ar) * dpix * Tn;
-                    if (bgdot != 0.f) dL_dalpha += (-T_final * inv1ma) * bgdot;
-                    const float sv = ok ? G * (co.w * dL_dalpha) : 0.f;
-                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-                    score += (sv * sv) * eval_poly13(c, dx, dy);
-                    T = ok ? Tn : T;
-                    accum_rec[0] = ok ? ar : accum_rec[0];
-                    last_color[0] = ok ? csum : last_color[0];
-                    last_alpha = ok ? alpha : last_alpha;
-                }
-#else
-                for (int h = 0; h < cnt; ++h) {
-                    const int slot = (qh + h) & (FB_WQ - 1);
-                    const float4 a = q.a[slot];
-                    if (__float_as_int(a.z) >= last) continue;
-                    const float4 co = q.b[slot];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    if (power > 0.0f) continue;
-                    const float G = score_exp(power);
-                    const float alpha = fminf(0.99f, co.w * G);
-                    if (alpha < 1.0f / 255.0f) continue;
-                    const float4 r0 = q.rb[0][slot];
-                    T = T / (1.f - alpha);
-                    const float col[3] = {r0.x, r0.y, r0.z};
-                    float dL_dalpha = 0.0f;
-#pragma unroll
-                    for (int ch = 0; ch < 3; ++ch) {
-                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                        last_color[ch] = col[ch];
-                        dL_dalpha += (col[ch] - accum_rec[ch]) * dpix;
-                    }
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    if (bgdot != 0.f) dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;   // exact: x + (-0) == x
-                    const float s = G * (co.w * dL_dalpha);
-                    const float4 r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
-                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-                    score += (s * s) * eval_poly13(c, dx, dy);
-                }
-#endif
-                __syncwarp();
-                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
-            }
-        }
-    }
-
-    // (3) warp reduce; k_score_finalize adds the (tile, block) partials in fixed order
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
-    if (lane == 0) *out = score;
-}
-
-// ---- single-pass form -------------------------------------------------------------------------
+// ---- single sweep ----------------------------------------------------------------------------------
 // The reference needs two sweeps of a pixel's list: forward for T_final / n_contrib, then backward for
 //   dL/dalpha_i = T_i (c_i - S_i) - T_final bg / (1 - alpha_i),   S_i = colour accumulated BEHIND Gaussian i
 // (backward.cu:978-1017).  With C = sum_j c_j alpha_j T_j the colour of the pixel and Cp_i the same sum over j <= i,
@@ -352,6 +107,9 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score(Bins bins, Cam
 // are those of forward.cu:343-358, which are also the set backward.cu:962-975 revisits.
 // Rounding: the three sums are of non-negative terms and the cancellation happens once per pixel; measured
 // against the reference extension the scores agree to ~1e-5 (tests/test_gpu_scoring.py, rtol 1e-3 required).
+
+// k_tile_score1: one pixel per lane, 8x4 block per warp (the round-1 kernel on the slot-indexed records; built with
+// -DFB_SCORE_PX2=0 as the independent form the parity tests can be run against).
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Cam cam, float grad_scale,
                                                                    float* __restrict__ partial) {
     extern __shared__ float4 smem[];
@@ -375,16 +133,14 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const uint2 range = bins.tile_range[tile_slot];
     const int n = (int)(range.y - range.x);
     if (n == 0) { if (lane == 0) *out = 0.f; return; }
-    // warp-uniform 64-bit bases + 32-bit byte offsets (P <= 2^26 Gaussians): the gathers need no 64-bit address math
-    const char* __restrict__ recs = reinterpret_cast<const char*>(bins.recs + (size_t)v * bins.P);
-    const char* __restrict__ recsB = reinterpret_cast<const char*>(bins.recsB + (size_t)v * bins.P * 4);
-    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = id
+    // warp-uniform 64-bit bases + 32-bit byte offsets (80 B x visible capacity < 4 GB per view, checked by the host
+    // entry point): the gathers need no 64-bit address math
+    const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
+    const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
+    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
     WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
 
     float T = 1.0f, Cp = 0.f, Qaa = 0.f, Qab = 0.f, Qbb = 0.f;
-#if FB_SCORE_STATS
-    float stat = 0.f;                                                    // measurement builds only (scratch/lane_stats.py)
-#endif
     bool done = !inside;
     if (!__all_sync(0xffffffffu, done)) {
         int qn = 0, qh = 0;
@@ -392,7 +148,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
         bool v_nxt = lane < n;
         unsigned gid_nxt = v_nxt ? sorted[2 * lane] : 0u;
         float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + (gid_nxt << 5)));
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
         unsigned key2 = (32 + lane < n) ? sorted[2 * (32 + lane)] : 0u;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
@@ -401,17 +157,17 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                 const bool valid = v_nxt;
                 v_nxt = (step + 1) * 32 + lane < n;
                 gid_nxt = key2;
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + (gid_nxt << 5)));
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
                 key2 = ((step + 2) * 32 + lane < n) ? sorted[2 * ((step + 2) * 32 + lane)] : 0u;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
                     const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
                     q.a[slot] = a;
-                    __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + (gid << 5)) + 1, 16);
-                    const float4* rb = reinterpret_cast<const float4*>(recsB + (gid << 6));
+                    const float4* rb = reinterpret_cast<const float4*>(recB + gid * 80u);
+                    __pipeline_memcpy_async(&q.b[slot], rb, 16);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + k, 16);
+                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + 1 + k, 16);
                 }
                 __pipeline_commit();
                 qn += __popc(mask);
@@ -426,44 +182,22 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
                     const float4 a = q.a[slot];
                     const float4 co = q.b[slot];
                     const float dx = a.x - pxf, dy = a.y - pyf;
-#if FB_SCORE_PRESCALE
                     // conic pre-multiplied in k_preprocess_score: power * log2(e) = dx (A dx + B dy) + C dy^2
                     const float power = fmaf(co.z, dy * dy, dx * fmaf(co.y, dy, co.x * dx));
-                    float G;
-                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power));
-#else
-                    const float power = pair_power(co.x, co.y, co.z, dx, dy);
-                    const float G = score_exp(power);
-#endif
+                    const float G = score_ex2(power);
                     const float alpha = fminf(0.99f, co.w * G);
                     const float oma = __fsub_rn(1.f, alpha);
                     const float test_T = __fmul_rn(T, oma);
                     const bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
                     const bool upd = ok && !(test_T < 0.0001f);
                     done = done || (ok && !upd);                         // stop BEFORE the Gaussian that takes T below 1e-4
-#if FB_SCORE_STATS == 1
-                    stat += 1.f;                                         // (lane, survivor) visits
-#elif FB_SCORE_STATS == 3
-                    stat += upd ? 1.f : 0.f;                             // lanes that take the survivor
-#endif
                     if (!__any_sync(0xffffffffu, upd)) return;           // ~30 % of the entries: nobody contributes
-#if FB_SCORE_STATS == 2
-                    stat += 1.f;                                         // (lane, survivor) visits that run the full body
-#endif
                     const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
                     const float inv = score_rcp(oma);
-#if FB_SCORE_PRESCALE
                     const float csum = r0.x;
-#else
-                    const float csum = (r0.x + r0.y) + r0.z;
-#endif
                     const float Cn = fmaf(csum, alpha * T, Cp);
                     const float A = fmaf(T, csum, Cn * inv);
-#if FB_SCORE_PRESCALE
                     const float c[13] = {r0.y, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-#else
-                    const float c[13] = {r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x, r3.y, r3.z, r3.w};
-#endif
                     const float go = upd ? G * co.w : 0.f;               // select BEFORE the polynomial: no branch around it
                     const float g = (go * go) * eval_poly13(c, dx, dy);
                     const float gA = g * A, gB = g * inv;
@@ -490,7 +224,229 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const float dpix = inside ? grad_scale : 0.f;
     const float Cf = fmaf(T, (cam.bg[0] + cam.bg[1]) + cam.bg[2], Cp);     // C + T_final * bg
     float score = (dpix * dpix) * fmaf(Cf, fmaf(Cf, Qbb, -2.f * Qab), Qaa);
-#if FB_SCORE_STATS
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
+    if (lane == 0) *out = score;
+}
+
+// ---- k_tile_score2: two pixels per lane, packed FP32 ------------------------------------------------
+// The pair loop is bound by instruction issue, not by a pipe or by memory (round 1: 79 % of the issue slots, fma 42 %,
+// alu 42 %).  This form issues fewer instructions per (pixel, Gaussian) pair:
+//   * a warp owns an 8x8 pixel block and a lane a COLUMN of two pixels, (x, y) and (x, y + 4).  Everything that
+//     depends on dx alone is computed once per lane and shared by its two pixels: the exponent's A dx^2 and B dx, and
+//     the quartic written as a polynomial in dy whose five coefficients are polynomials in dx
+//         poly = P0(dx) + dy (P1(dx) + dy (P2(dx) + dy (P3(dx) + dy c12)));
+//   * what differs between the two pixels runs as packed FP32 (fma.rn.f32x2 -> FFMA2: one issue slot for both pixels;
+//     measured on B200: the same FLOP/s as FFMA at half the issue slots; per-Gaussian scalars enter as broadcast
+//     operands, no register duplication);
+//   * half as many warps scan a tile's list (4 blocks of 8x8 instead of 8 of 8x4);
+//   * each batch of 32 ring entries is first tested EXACTLY, one entry per lane: the maximum of the (concave) exponent
+//     over the block's pixel-centre rectangle is compared with the alpha >= 1/255 threshold, so entries whose bounding
+//     box touches the block but whose ellipse does not (a third of them) never reach the pair loop.
+// Per surviving entry: 64 pixel-visits in ~66 issue slots (k_tile_score1: 32 in 54).
+typedef float2 f32x2;
+__device__ __forceinline__ f32x2 f2_pack(float lo, float hi) { return make_float2(lo, hi); }
+__device__ __forceinline__ f32x2 f2_dup(float s) { return make_float2(s, s); }
+__device__ __forceinline__ float f2_lo(f32x2 v) { return v.x; }
+__device__ __forceinline__ float f2_hi(f32x2 v) { return v.y; }
+#ifndef FB_S2_PACKED
+#define FB_S2_PACKED 1            // 0: the same kernel with scalar FP32 (A/B measurement of FFMA2)
+#endif
+#if FB_S2_PACKED
+__device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) { return __fadd2_rn(a, b); }
+#else
+__device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+__device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+__device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+#endif
+__device__ __forceinline__ void f2_acc(f32x2& acc, f32x2 a, f32x2 b) { acc = f2_fma(a, b, acc); }
+#ifndef FB_S2_EXACT
+#define FB_S2_EXACT 1             // exact ellipse / block test of every ring batch
+#endif
+#ifndef FB_S2_ANY
+#define FB_S2_ANY 1               // skip the rest of the body when no pixel of the block takes the entry
+#endif
+#ifndef FB_S2_STATS
+#define FB_S2_STATS 0             // measurement builds (tools/lane_stats.py): the "score" of a view becomes a count --
+#endif                            // 1 scan steps, 2 ring entries, 3 entries after the exact test, 4 full bodies, 5 contributing pixel pairs
+#define FB_S2_BLOCKS 4            // 8x8 pixel blocks per 16x16 tile
+#ifndef FB_S2_WPC
+#define FB_S2_WPC 4               // warps per CTA
+#endif
+#define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ) * FB_S2_WPC)
+
+__global__ void __launch_bounds__(32 * FB_S2_WPC) k_tile_score2(Bins bins, Cam cam, float grad_scale,
+                                                                 float* __restrict__ partial) {
+    extern __shared__ float4 smem[];
+    constexpr int CPT = FB_S2_BLOCKS / FB_S2_WPC;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+    const int warp = (int)(lin % CPT) * FB_S2_WPC + wq;            // 8x8 block of the tile, 0..3
+    const unsigned lt = (1u << lane) - 1u;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
+    const int px = bx + (lane & 7), py0 = by + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < cam.W && py0 < cam.H, in1 = px < cam.W && py1 < cam.H;
+    const float pxf = (float)px;
+    const f32x2 npy = f2_pack(-(float)py0, -(float)py1);
+    const float cx = (float)bx + 3.5f, cy = (float)by + 3.5f;
+    float* out = partial + (size_t)tile_slot * FB_S2_BLOCKS + warp;
+    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
+    const uint2 range = bins.tile_range[tile_slot];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) { if (lane == 0) *out = 0.f; return; }
+    const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
+    const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
+    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
+    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
+
+    f32x2 T = f2_dup(1.0f), Cp = f2_dup(0.f), Qaa = f2_dup(0.f), Qab = f2_dup(0.f), Qbb = f2_dup(0.f);
+#if FB_S2_STATS
+    float stat = 0.f;
+#endif
+    float athr0 = in0 ? 1.0f / 255.0f : 2.0f, athr1 = in1 ? 1.0f / 255.0f : 2.0f;
+    if (__any_sync(0xffffffffu, in0 || in1)) {
+        int qn = 0, qh = 0;
+        const int nsteps = (n + 31) >> 5;
+        bool v_nxt = lane < n;
+        unsigned gid_nxt = v_nxt ? sorted[2 * lane] : 0u;
+        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
+        unsigned key2 = (32 + lane < n) ? sorted[2 * (32 + lane)] : 0u;
+        for (int step = 0; step <= nsteps; ++step) {
+            if (step < nsteps) {
+                const float4 a = a_nxt;
+                const unsigned gid = gid_nxt;
+                const bool valid = v_nxt;
+                v_nxt = (step + 1) * 32 + lane < n;
+                gid_nxt = key2;
+                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
+                key2 = ((step + 2) * 32 + lane < n) ? sorted[2 * ((step + 2) * 32 + lane)] : 0u;
+                const bool hit = valid && (fabsf(a.x - cx) <= a.z + 3.5f) && (fabsf(a.y - cy) <= a.w + 3.5f);
+                const unsigned mask = __ballot_sync(0xffffffffu, hit);
+#if FB_S2_STATS == 1
+                if (lane == 0) stat += 1.f;
+#elif FB_S2_STATS == 2
+                if (lane == 0) stat += (float)__popc(mask);
+#endif
+                if (hit) {
+                    const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                    q.a[slot] = a;
+                    const float4* rb = reinterpret_cast<const float4*>(recB + gid * 80u);
+                    __pipeline_memcpy_async(&q.b[slot], rb, 16);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + 1 + k, 16);
+                }
+                __pipeline_commit();
+                qn += __popc(mask);
+            }
+            const bool flush = (step == nsteps);
+            if (qn >= 32 || (flush && qn > 0)) {
+                const int cnt = min(qn, 32);
+                __pipeline_wait_prior(0);
+                __syncwarp();
+                // batches are 32 entries except the last one, so qh is 0 or 32 and qh + h never wraps
+                unsigned todo = cnt == 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+#if FB_S2_EXACT
+                {
+                    // lane h tests ring entry qh + h: max over the block's pixel-centre rectangle of the exponent
+                    // p(d) = A dx^2 + B dx dy + C dy^2 (A, C < 0, negative definite; d = mean - pixel) against
+                    // alpha >= 1/255  <=>  p >= -log2(255 o).  0.02 in log2 units (1.4 % in alpha) of slack covers the
+                    // approximate reciprocals and every rounding below.  The maximum sits at d = 0 when the mean is
+                    // inside the rectangle, else on one of the four edges (a clamped 1-D parabola each).
+                    const float4 a = q.a[qh + lane];
+                    const float4 co = q.b[qh + lane];
+                    const float X1 = a.x - (float)bx, X0 = X1 - 7.f, Y1 = a.y - (float)by, Y0 = Y1 - 7.f;
+                    const float ia = score_rcp(co.x + co.x), ic = score_rcp(co.z + co.z);       // 1 / (2A), 1 / (2C)
+                    auto pw = [&](float x, float y) { return fmaf(co.z, y * y, x * fmaf(co.y, y, co.x * x)); };
+                    auto ex_ = [&](float Y) { return pw(fminf(fmaxf(-co.y * Y * ia, X0), X1), Y); };
+                    auto ey_ = [&](float X) { return pw(X, fminf(fmaxf(-co.y * X * ic, Y0), Y1)); };
+                    float m = fmaxf(fmaxf(ex_(Y0), ex_(Y1)), fmaxf(ey_(X0), ey_(X1)));
+                    if (X0 <= 0.f && X1 >= 0.f && Y0 <= 0.f && Y1 >= 0.f) m = 0.f;
+                    float lg;
+                    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(255.0f * co.w));
+                    const bool keep = !(m < -lg - 0.02f);                 // NaN (degenerate conic) keeps the entry
+                    todo &= __ballot_sync(0xffffffffu, keep);
+                }
+#endif
+#if FB_S2_STATS == 3
+                if (lane == 0) stat += (float)__popc(todo);
+#endif
+                while (todo) {
+                    const int h = __ffs(todo) - 1;
+                    todo &= todo - 1u;
+                    const int slot = qh + h;
+                    const float2 mu = *reinterpret_cast<const float2*>(&q.a[slot]);
+                    const float4 co = q.b[slot];
+                    const float dx = mu.x - pxf;
+                    const f32x2 dy = f2_add(f2_dup(mu.y), npy);
+                    const float Adx = co.x * dx;
+                    const float q0 = Adx * dx, q1 = co.y * dx;
+                    const f32x2 pw = f2_fma(f2_fma(f2_dup(co.z), dy, f2_dup(q1)), dy, f2_dup(q0));
+                    const float G0 = score_ex2(f2_lo(pw)), G1 = score_ex2(f2_hi(pw));
+                    const f32x2 oG = f2_mul(f2_dup(co.w), f2_pack(G0, G1));
+                    const float al0 = fminf(0.99f, f2_lo(oG)), al1 = fminf(0.99f, f2_hi(oG));
+                    const f32x2 oma = f2_fma(f2_pack(al0, al1), f2_dup(-1.f), f2_dup(1.f));   // 1 - alpha, one rounding
+                    const f32x2 tT = f2_mul(T, oma);
+                    // (the exponent of a negative-definite form is <= 0 up to rounding: the reference's `power > 0`
+                    //  skip, forward.cu:343, can only fire within ~1e-7 px of the mean and is not tested here)
+                    // athr = 1/255 while the pixel is live, 2 once it is done (alpha <= 0.99 never reaches it)
+                    const bool ok0 = al0 >= athr0, ok1 = al1 >= athr1;
+                    const bool upd0 = ok0 && !(f2_lo(tT) < 0.0001f), upd1 = ok1 && !(f2_hi(tT) < 0.0001f);
+                    athr0 = (ok0 && !upd0) ? 2.0f : athr0;               // stop BEFORE the Gaussian that takes T below 1e-4
+                    athr1 = (ok1 && !upd1) ? 2.0f : athr1;
+#if FB_S2_ANY
+                    if (!__any_sync(0xffffffffu, upd0 || upd1)) continue;
+#endif
+#if FB_S2_STATS == 4
+                    if (lane == 0) stat += 1.f;
+#elif FB_S2_STATS == 5
+                    stat += (upd0 ? 1.f : 0.f) + (upd1 ? 1.f : 0.f);
+#endif
+                    const float4 r0 = q.rb[0][slot], r1 = q.rb[1][slot], r2 = q.rb[2][slot], r3 = q.rb[3][slot];
+                    const f32x2 inv = f2_pack(score_rcp(f2_lo(oma)), score_rcp(f2_hi(oma)));
+                    // a pixel that does not take the entry runs the same arithmetic with go = alpha = 0: nothing changes
+                    const f32x2 go = f2_pack(upd0 ? f2_lo(oG) : 0.f, upd1 ? f2_hi(oG) : 0.f);
+                    const f32x2 aT = f2_mul(f2_pack(fminf(0.99f, f2_lo(go)), fminf(0.99f, f2_hi(go))), T);
+                    const float csum = r0.x;
+                    f2_acc(Cp, f2_dup(csum), aT);                                          // colour up to and including this one
+                    const f32x2 A = f2_fma(T, f2_dup(csum), f2_mul(Cp, inv));
+                    f2_acc(T, aT, f2_dup(-1.f));                                           // T (1 - alpha) as T - alpha T
+                    // coefficients in monomial order (1, dx2, dxdy, dy2, dx3, dx2dy, dxdy2, dy3, dx4, dx3dy, dx2dy2, dxdy3, dy4)
+                    //                               = r0.y r1.x r1.y  r1.z r1.w r2.x   r2.y   r2.z r2.w r3.x   r3.y    r3.z   r3.w
+                    const float dx2 = dx * dx;
+                    const float P0 = fmaf(dx2, fmaf(dx, fmaf(dx, r2.w, r1.w), r1.x), r0.y);
+                    const float P1 = dx * fmaf(dx, fmaf(dx, r3.x, r2.x), r1.y);
+                    const float P2 = fmaf(dx, fmaf(dx, r3.y, r2.y), r1.z);
+                    const float P3 = fmaf(dx, r3.z, r2.z);
+                    f32x2 poly = f2_fma(f2_dup(r3.w), dy, f2_dup(P3));
+                    poly = f2_fma(poly, dy, f2_dup(P2));
+                    poly = f2_fma(poly, dy, f2_dup(P1));
+                    poly = f2_fma(poly, dy, f2_dup(P0));
+                    const f32x2 g = f2_mul(f2_mul(go, go), poly);
+                    const f32x2 gA = f2_mul(g, A), gB = f2_mul(g, inv);
+                    f2_acc(Qaa, gA, A);
+                    f2_acc(Qab, gA, inv);
+                    f2_acc(Qbb, gB, inv);
+                }
+                __syncwarp();
+                qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+                if (__all_sync(0xffffffffu, athr0 > 1.f && athr1 > 1.f)) break;
+            }
+        }
+        __pipeline_wait_prior(0);
+        __syncwarp();
+    }
+    const float bgs = (cam.bg[0] + cam.bg[1]) + cam.bg[2];
+    const float Cf0 = fmaf(f2_lo(T), bgs, f2_lo(Cp)), Cf1 = fmaf(f2_hi(T), bgs, f2_hi(Cp));     // C + T_final * bg
+    const float s0 = fmaf(Cf0, fmaf(Cf0, f2_lo(Qbb), -2.f * f2_lo(Qab)), f2_lo(Qaa));
+    const float s1 = fmaf(Cf1, fmaf(Cf1, f2_hi(Qbb), -2.f * f2_hi(Qab)), f2_hi(Qaa));
+    float score = (grad_scale * grad_scale) * ((in0 ? s0 : 0.f) + (in1 ? s1 : 0.f));
+#if FB_S2_STATS
     score = stat;
 #endif
 #pragma unroll

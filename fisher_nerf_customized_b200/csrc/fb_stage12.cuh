@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(256) k_preprocess(GaussIn g, Cam cam, const fl
             base = __shfl_sync(0xffffffffu, base, leader);
             if (vis) {
                 unsigned slot = base + __popc(m & ((1u << lane) - 1u));
-                bins.vis_list[(size_t)v * P + slot] =
+                bins.vis_list[(size_t)v * bins.vis_stride + slot] =
                     make_uint4((unsigned)idx, __float_as_uint(s.depth),
                                (unsigned)s.x0 | ((unsigned)s.y0 << 8) | ((unsigned)s.x1 << 16) | ((unsigned)s.y1 << 24), 0u);
                 GRec r;
@@ -279,10 +279,16 @@ template <int CH> struct PSmem {
     float p[3][FB_PS_THREADS], cov6[6][FB_PS_THREADS], op[FB_PS_THREADS], sc[3][FB_PS_THREADS], q[4][FB_PS_THREADS],
         col[3][FB_PS_THREADS], w[CH][FB_PS_THREADS];
     float w2c[FB_PS_VG * 12];
+    unsigned qslot[FB_PS_THREADS * FB_PS_VG];          // visible slot of the queued (Gaussian, view) pair
     unsigned short queue[FB_PS_THREADS * FB_PS_VG];
     unsigned qcount;
 };
 
+// Records are written in the view's VISIBLE SLOT (the position the warp-aggregated atomicAdd on vis_count hands out),
+// not at the Gaussian's index: the arrays are dense ([V][vis_stride], vis_stride = the caller's visible capacity), a
+// warp's visible lanes own consecutive slots (coalesced 16-B rows in phase 1, contiguous 80-B rows in phase 2), and the
+// scoring kernel's tile-list scan touches two records per 32-B sector.  A view with more visible Gaussians than
+// vis_stride raises the overflow flag in k_scan_tiles (status FB_E_CAPACITY, the caller grows and re-runs).
 template <int CH>
 #ifndef FB_PS_MINB
 #define FB_PS_MINB 3
@@ -295,6 +301,7 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
     const int tid = threadIdx.x, lane = tid & 31;
     const int idx = blockIdx.x * FB_PS_THREADS + tid;
     const bool live = idx < P;
+    const unsigned vcap = (unsigned)bins.vis_stride;
     float3 p = make_float3(0.f, 0.f, 0.f);
     float cov6[6] = {0, 0, 0, 0, 0, 0};
     float opacity = 0.f;
@@ -351,8 +358,11 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             qbase = __shfl_sync(0xffffffffu, qbase, leader);
             if (!vis) continue;
             const unsigned rank = __popc(bm & ((1u << lane) - 1u));
+            const unsigned slot = base + rank;
             S.queue[qbase + rank] = (unsigned short)(tid | (vv << 8));
-            bins.vis_list[(size_t)v * P + base + rank] =
+            S.qslot[qbase + rank] = slot;
+            if (slot >= vcap) continue;                        // overflow: the chunk is void (k_scan_tiles flags it)
+            bins.vis_list[(size_t)v * vcap + slot] =
                 make_uint4((unsigned)idx, __float_as_uint(s.depth),
                            (unsigned)s.x0 | ((unsigned)s.y0 << 8) | ((unsigned)s.x1 << 16) | ((unsigned)s.y1 << 24), 0u);
             // half extents of the alpha >= 1/255 footprint (see k_preprocess)
@@ -364,23 +374,15 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
                 hy = sqrtf(tau2 * s.ca / dq) * 1.001f + 0.05f;
                 if (!(dq > 0.f) || !(hx == hx) || !(hy == hy)) { hx = 3.0e38f; hy = 3.0e38f; }
             }
-            GRec r;
-            r.a = make_float4(s.px, s.py, hx, hy);
-#if FB_SCORE_PRESCALE
-            // the single-sweep scoring kernel evaluates G = ex2(dx (A dx + B dy) + C dy^2): conic pre-multiplied by
-            // -log2(e)/2, -log2(e), -log2(e)/2 (the sign of the exponent, which the `power > 0` skip tests, is kept)
-            r.b = make_float4(s.ca * -0.72134752044448170368f, s.cb * -1.4426950408889634f,
-                              s.cc * -0.72134752044448170368f, opacity);
-#else
-            r.b = make_float4(s.ca, s.cb, s.cc, opacity);
-#endif
-            bins.recs[(size_t)v * P + idx] = r;
+            bins.recA[(size_t)v * vcap + slot] = make_float4(s.px, s.py, hx, hy);
         }
         __syncthreads();
         // ---- phase 2
         const unsigned qn = S.qcount;
         for (unsigned i = tid; i < qn; i += FB_PS_THREADS) {
             const unsigned e = S.queue[i];
+            const unsigned slot = S.qslot[i];
+            if (slot >= vcap) continue;
             const int gi = e & 255, vv = e >> 8;
             const float* m = S.w2c + vv * 12;
             const float3 pw = make_float3(S.p[0][gi], S.p[1][gi], S.p[2][gi]);
@@ -403,104 +405,122 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             for (int k = 0; k < CH; ++k) wv[k] = S.w[k][gi];
             float coef[13];
             score_coefs<CH>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
-            float4* rb = bins.recsB + ((size_t)(v0 + vv) * P + (size_t)blockIdx.x * FB_PS_THREADS + gi) * 4;
-#if FB_SCORE_PRESCALE
-            rb[0] = make_float4((S.col[0][gi] + S.col[1][gi]) + S.col[2][gi], coef[0], 0.f, 0.f);   // r+g+b: the one colour
-#else
-            rb[0] = make_float4(S.col[0][gi], S.col[1][gi], S.col[2][gi], coef[0]);
-#endif
-            rb[1] = make_float4(coef[1], coef[2], coef[3], coef[4]);
-            rb[2] = make_float4(coef[5], coef[6], coef[7], coef[8]);
-            rb[3] = make_float4(coef[9], coef[10], coef[11], coef[12]);
+            float4* rb = bins.recB + ((size_t)(v0 + vv) * vcap + slot) * 5;
+            // the scoring kernel evaluates G = ex2(dx (A dx + B dy) + C dy^2): conic pre-multiplied by
+            // -log2(e)/2, -log2(e), -log2(e)/2 (the sign of the exponent is kept); r+g+b is the one colour
+            rb[0] = make_float4(ca * -0.72134752044448170368f, cb * -1.4426950408889634f, cc * -0.72134752044448170368f, S.op[gi]);
+            rb[1] = make_float4((S.col[0][gi] + S.col[1][gi]) + S.col[2][gi], coef[0], 0.f, 0.f);
+            rb[2] = make_float4(coef[1], coef[2], coef[3], coef[4]);
+            rb[3] = make_float4(coef[5], coef[6], coef[7], coef[8]);
+            rb[4] = make_float4(coef[9], coef[10], coef[11], coef[12]);
         }
     }
 }
 
-// ---- stage 2a: counts -> segment offsets (one CTA, V*tiles entries) -------------------------
+// ---- stage 2a: counts -> segment offsets (one CTA per view, chained) ---------------------------
 // Empty tiles get range (0,0) as in the reference (cudaMemset + identifyTileRanges,
 // rasterizer_impl.cu:311-319).  total[0] = instance count, total[1] = overflow flag,
-// total[3] = largest tile segment.
+// total[3] = largest tile segment, total[4] = largest visible count of a view.
+// CTA v scans the counters of view v, publishes the view's instance total, then adds the totals of the views
+// before it: CTAs of a grid are dispatched in index order, so every CTA this one waits for is resident or done
+// (the chained-scan argument).  V <= 64 CTAs replace the single CTA that walked all V * tiles counters
+// (45 us per 64 views on the critical path of every chunk).  bins.view_total and bins.total are zeroed per chunk.
+// Work order for the sort and pair-sweep kernels: each view's tile slots by descending instance count (counting sort,
+// 1024 buckets over [0, max of the view]), interleaved over the views -- tile_order[rank * V + v] -- so the heaviest
+// tiles of every view start first.  The order only decides when a tile is scheduled, never what it computes.
 __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
     __shared__ unsigned warp_sums[32];
-    __shared__ unsigned carry_s;
-    __shared__ unsigned maxc_s;
-    const int n = bins.V * bins.tiles;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { carry_s = 0; maxc_s = 0; }
+    __shared__ unsigned carry_s, maxc_s, base_s;
+    __shared__ unsigned bucket[1024];
+    const int v = blockIdx.x, V = bins.V, n = bins.tiles;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t* tc = bins.tile_count + (size_t)v * n * FB_TC_STRIDE;
+    uint2* tr = bins.tile_range + (size_t)v * n;
+    if (tid == 0) { carry_s = 0; maxc_s = 0; base_s = 0; }
     __syncthreads();
     unsigned local_max = 0;
-    for (int base = 0; base < n; base += blockDim.x) {
-        int i = base + threadIdx.x;
-        unsigned c = (i < n) ? bins.tile_count[(size_t)i * FB_TC_STRIDE] : 0u;
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const unsigned c = (i < n) ? tc[(size_t)i * FB_TC_STRIDE] : 0u;
         local_max = max(local_max, c);
         unsigned x = c;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            unsigned y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
-        }
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
         if (lane == 31) warp_sums[wid] = x;
         __syncthreads();
         if (wid == 0) {
             unsigned w = warp_sums[lane];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                unsigned y = __shfl_up_sync(0xffffffffu, w, o);
-                if (lane >= o) w += y;
-            }
+            for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
             warp_sums[lane] = w;
         }
         __syncthreads();
-        unsigned incl = x + (wid > 0 ? warp_sums[wid - 1] : 0u) + carry_s;
-        if (i < n) {
-            unsigned start = incl - c;
-            bins.tile_range[i] = c ? make_uint2(start, incl) : make_uint2(0u, 0u);
-        }
+        const unsigned incl = x + (wid > 0 ? warp_sums[wid - 1] : 0u) + carry_s;
+        if (i < n) tr[i] = make_uint2(incl - c, incl);          // relative to the view's first instance, for now
         __syncthreads();
-        if (threadIdx.x == blockDim.x - 1) carry_s = incl;
+        if (tid == 1023) carry_s = incl;
         __syncthreads();
     }
-    atomicMax(&maxc_s, local_max);
+    local_max = __reduce_max_sync(0xffffffffu, local_max);
+    if (lane == 0) atomicMax(&maxc_s, local_max);
+    const unsigned my_total = carry_s;
+    if (tid == 0) {
+        atomicExch(reinterpret_cast<unsigned long long*>(&bins.view_total[v]), (1ull << 32) | (u64)my_total);
+    }
+    // instances of the views before this one
+    if (tid < v) {
+        const volatile u64* vt = reinterpret_cast<const volatile u64*>(bins.view_total);
+        u64 x;
+        do { x = vt[tid]; } while ((x >> 32) == 0ull);
+        atomicAdd(&base_s, (unsigned)(x & 0xffffffffull));      // (sums of unsigned wrap alike in any order)
+    }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        bins.total[0] = carry_s;
-        bins.total[1] = ((long long)carry_s > bins.capacity) ? 1u : 0u;
-        bins.total[3] = maxc_s;
+    const unsigned base_inst = base_s;
+    const unsigned maxc_view = maxc_s;
+    for (int i = tid; i < n; i += 1024) {
+        const uint2 r = tr[i];
+        tr[i] = (r.y > r.x) ? make_uint2(r.x + base_inst, r.y + base_inst) : make_uint2(0u, 0u);
+    }
+    if (tid == 0) {
+        atomicMax(&bins.total[3], maxc_view);
+        atomicMax(&bins.total[4], bins.vis_count[v]);
+        if (bins.vis_count[v] > (unsigned)bins.vis_stride) atomicExch(&bins.total[1], 1u);
+        if (v == V - 1) {
+            const u64 all = (u64)base_inst + (u64)my_total;
+            bins.total[0] = (unsigned)min(all, (u64)0xffffffffu);
+            if ((long long)all > bins.capacity) atomicExch(&bins.total[1], 1u);
+        }
     }
     if (bins.tile_order == nullptr) return;
-    // Work order for the scoring kernel: counting sort of the tile slots by descending instance count
-    // (1024 buckets over [0, max]).  The order inside a bucket is whatever the atomics give; it only decides
-    // when a tile is scheduled, never what it computes.
-    __shared__ unsigned bucket[1024];
-    const unsigned maxc = maxc_s > 0u ? maxc_s : 1u;
-    bucket[threadIdx.x] = 0u;
+    const unsigned maxc = maxc_view > 0u ? maxc_view : 1u;
+    bucket[tid] = 0u;
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const unsigned c = bins.tile_range[i].y - bins.tile_range[i].x;
+    for (int i = tid; i < n; i += 1024) {
+        const unsigned c = tc[(size_t)i * FB_TC_STRIDE];
         atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
     }
     __syncthreads();
     {
-        const unsigned c = bucket[threadIdx.x];
+        const unsigned c = bucket[tid];
         unsigned x = c;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
         if (lane == 31) warp_sums[wid] = x;
         __syncthreads();
         if (wid == 0) {
             unsigned w = warp_sums[lane];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+            for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
             warp_sums[lane] = w;
         }
         __syncthreads();
-        bucket[threadIdx.x] = x - c + (wid > 0 ? warp_sums[wid - 1] : 0u);
+        bucket[tid] = x - c + (wid > 0 ? warp_sums[wid - 1] : 0u);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const unsigned c = bins.tile_range[i].y - bins.tile_range[i].x;
+    for (int i = tid; i < n; i += 1024) {
+        const unsigned c = tc[(size_t)i * FB_TC_STRIDE];
         const unsigned pos = atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
-        bins.tile_order[pos] = (unsigned)i;
+        bins.tile_order[(size_t)pos * V + v] = (unsigned)(v * n + i);
     }
 }
 
@@ -522,9 +542,10 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     for (unsigned i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; i0 < nvis; i0 += gridDim.x * blockDim.x) {
         const unsigned i = i0 + (threadIdx.x & 31);
         uint4 e = make_uint4(0u, 0u, 0u, 0u);
-        if (i < nvis) e = bins.vis_list[(size_t)v * bins.P + i];
+        if (i < nvis) e = bins.vis_list[(size_t)v * bins.vis_stride + i];
         const int x0 = e.z & 0xff, y0 = (e.z >> 8) & 0xff, x1 = (e.z >> 16) & 0xff, y1 = e.z >> 24;
-        const u64 key = ((u64)e.y << 32) | (u64)e.x;
+        // low word: the Gaussian id, or (scoring path) the visible slot its records live in
+        const u64 key = ((u64)e.y << 32) | (u64)(bins.key_is_slot ? i : e.x);
         warp_tiles<true>(x0, y0, x1, y1, cam.tiles_x, key,
                    [&](int t, unsigned n) { return atomicSub(&tc[t * FB_TC_STRIDE], n); },
                    [&](int t, unsigned old, unsigned rank, u64 k) { bins.keys[tr[t].x + old - 1u - rank] = k; });
@@ -599,8 +620,19 @@ __device__ __forceinline__ bool radix_pass_u64(const u64* __restrict__ src, u64*
     return true;
 }
 
-// Orders runs of equal depth bits by id (full 64-bit compare).  Runs are disjoint, one thread each.
-__device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
+// Total order of the keys: depth bits, then GAUSSIAN id (the reference's stable sort keeps emission order = ascending
+// Gaussian index among equal depths, rasterizer_impl.cu:92-108).  On the scoring path the low word of a key is the
+// visible slot (assigned by atomics, in no particular order), so equal depths -- rare -- look the id up in the view's
+// visible list; elsewhere the low word is the id itself and this is the plain 64-bit compare.
+__device__ __forceinline__ bool key_less(u64 a, u64 b, const uint4* __restrict__ vis) {
+    const unsigned da = (unsigned)(a >> 32), db = (unsigned)(b >> 32);
+    if (da != db) return da < db;
+    if (vis == nullptr) return (unsigned)a < (unsigned)b;
+    return vis[(unsigned)a].x < vis[(unsigned)b].x;
+}
+
+// Orders runs of equal depth bits by id (key_less).  Runs are disjoint, one thread each.
+__device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n, const uint4* __restrict__ vis) {
     for (int k = threadIdx.x; k + 1 < n; k += blockDim.x) {
         const unsigned d = (unsigned)(a[k] >> 32);
         if ((unsigned)(a[k + 1] >> 32) != d) continue;
@@ -610,7 +642,7 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n) {
         for (int i = k + 1; i < e; ++i) {                          // insertion sort (runs are short)
             const u64 x = a[i];
             int j = i - 1;
-            while (j >= k && a[j] > x) { a[j + 1] = a[j]; --j; }
+            while (j >= k && key_less(x, a[j], vis)) { a[j + 1] = a[j]; --j; }
             a[j + 1] = x;
         }
     }
@@ -668,6 +700,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
     const int n = (int)(r.y - r.x);
     if (n < 2) return;
     u64* seg = bins.keys + r.x;
+    const uint4* __restrict__ vis = bins.key_is_slot ? bins.vis_list + (size_t)(slot / (unsigned)bins.tiles) * bins.vis_stride : nullptr;
     bool radix = false;
     {
         // Segments that fit: keys staged and scattered in shared memory, 2048 fine buckets in `work`.
@@ -760,8 +793,19 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
                 const u64 k = s_out[i];
                 const unsigned f = FB_FINE_BUCKET((unsigned)(k >> 32));
                 const unsigned e = fine[FB_FIDX(f)], b0 = f ? fine[FB_FIDX(f - 1)] : 0u;
-                unsigned rank = 0;
-                for (unsigned j = b0; j < e; ++j) rank += (s_out[j] < k) ? 1u : 0u;
+                // rank inside the bucket by depth; keys of EQUAL depth (rare) are ranked among themselves by id
+                const unsigned dk = (unsigned)(k >> 32);
+                unsigned rank = 0, ties = 0;
+                for (unsigned j = b0; j < e; ++j) {
+                    const unsigned dj = (unsigned)(s_out[j] >> 32);
+                    rank += (dj < dk) ? 1u : 0u;
+                    ties += (dj == dk) ? 1u : 0u;
+                }
+                if (ties > 1u)
+                    for (unsigned j = b0; j < e; ++j) {
+                        const u64 o = s_out[j];
+                        if ((unsigned)(o >> 32) == dk && o != k && key_less(o, k, vis)) ++rank;
+                    }
                 seg[b0 + rank] = k;
             }
             return;
@@ -778,7 +822,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
         for (int pass = 0; pass < 4; ++pass) {
             if (radix_pass_u64(a, b, n, 32 + 8 * pass, hist)) { u64* tmp = a; a = b; b = tmp; }
         }
-        fix_equal_depth_runs(a, n);
+        fix_equal_depth_runs(a, n, vis);
         if (a != seg) {
             for (int i = tid; i < n; i += blockDim.x) seg[i] = a[i];
         }

@@ -47,7 +47,11 @@ __global__ void __launch_bounds__(256) k_knn_bbox(int P, const float* __restrict
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
 #pragma unroll
-        for (int a = 0; a < 3; ++a) { float c = pts[3 * (size_t)i + a]; mn[a] = fminf(mn[a], c); mx[a] = fmaxf(mx[a], c); }
+        for (int a = 0; a < 3; ++a) {
+            // non-finite coordinates (a diverged map) stay out of the bounding box; such points land in a border cell
+            float c = pts[3 * (size_t)i + a];
+            if (fabsf(c) <= FLT_MAX) { mn[a] = fminf(mn[a], c); mx[a] = fmaxf(mx[a], c); }
+        }
     }
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -69,18 +73,24 @@ __global__ void k_knn_setup(int P, KnnWs ws) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     float mn[3], ex[3];
     float emax = 0.f;
-    for (int a = 0; a < 3; ++a) { mn[a] = ord2f(ws.bbox[a]); ex[a] = ord2f(ws.bbox[3 + a]) - mn[a]; emax = fmaxf(emax, ex[a]); }
+    for (int a = 0; a < 3; ++a) {
+        mn[a] = ord2f(ws.bbox[a]); ex[a] = ord2f(ws.bbox[3 + a]) - mn[a];
+        if (!(ex[a] >= 0.f) || !(ex[a] <= FLT_MAX)) { ex[a] = 0.f; if (!(fabsf(mn[a]) <= FLT_MAX)) mn[a] = 0.f; }   // no finite point on this axis
+        emax = fmaxf(emax, ex[a]);
+    }
     if (!(emax > 0.f)) emax = 1.f;
     double vol = 1.0;
     for (int a = 0; a < 3; ++a) vol *= (double)fmaxf(ex[a], 1e-3f * emax);
     double h = cbrt(vol / (2.0 * (double)(P > 0 ? P : 1)));
-    int n[3];
-    for (;;) {
+    int n[3] = {1, 1, 1};
+    bool fits = false;
+    for (int it = 0; it < 96 && !fits; ++it) {         // bounded: h grows 2x every 3 rounds, 2^32 over 96
         double prod = 1.0;
-        for (int a = 0; a < 3; ++a) { double d = floor((double)ex[a] / h) + 1.0; if (d > 2048.0) d = 2048.0; n[a] = (int)d; prod *= d; }
-        if (prod <= (double)ws.cap) break;
-        h *= 1.2599210498948732;
+        for (int a = 0; a < 3; ++a) { double d = floor((double)ex[a] / h) + 1.0; if (!(d <= 2048.0)) d = 2048.0; n[a] = (int)d; prod *= d; }
+        fits = prod <= (double)ws.cap;
+        if (!fits) h *= 1.2599210498948732;
     }
+    if (!fits || !(h > 0.0) || !(h <= 3.0e38)) { n[0] = n[1] = n[2] = 1; h = (double)emax > 0.0 ? (double)emax : 1.0; }   // one cell: brute force, still exact
     KnnGrid g;
     g.minx = mn[0]; g.miny = mn[1]; g.minz = mn[2];
     g.h = (float)h; g.inv_h = (float)(1.0 / h);

@@ -6,9 +6,10 @@ f32[P], the mean of the three smallest squared distances to other points (KNN/si
 import torch
 
 from . import _lib
-from .rasterizer import _stream
+from .rasterizer import _on_tensor_device, _stream
 
 
+@_on_tensor_device
 def distCUDA2(points):
     if not points.is_cuda:
         raise RuntimeError("distCUDA2 takes a CUDA tensor (there is no CPU path)")

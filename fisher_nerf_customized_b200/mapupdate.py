@@ -10,7 +10,7 @@ There is no CPU fallback: the CUDA library must be present.
 import torch
 
 from . import _lib
-from .rasterizer import _f32c, _stream
+from .rasterizer import _f32c, _on_tensor_device, _stream
 
 
 def _intr4(intrinsics, dev):
@@ -39,6 +39,7 @@ def _selected_pixels(mask, height, width, downsample):
     return idx.contiguous()
 
 
+@_on_tensor_device
 def _launch(color, depth, intrinsics, w2c, downsample, pix, n, means3D, mean_stride, rgb, rgb_stride, rots=None,
             logit=None, log_scales=None, ls_cols=3, msd=None):
     L = _lib.lib()

@@ -92,6 +92,21 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+def _on_tensor_device(fn):
+    """Run `fn` with the device of its first CUDA tensor argument current: the library keeps per-device state (function
+    attributes, the second chunk lane) for the CURRENT device, and `_stream()` is the current device's stream."""
+    import functools
+
+    @functools.wraps(fn)
+    def guarded(*args, **kw):
+        for a in list(args) + list(kw.values()):
+            if isinstance(a, torch.Tensor) and a.is_cuda:
+                with torch.cuda.device(a.device):
+                    return fn(*args, **kw)
+        return fn(*args, **kw)
+    return guarded
+
+
 def _gauss(P, means3D, opacity, sh, colors, scales, rotations, cov3D):
     g = _lib.fb_gaussians()
     g.P = P
@@ -104,6 +119,7 @@ class _CModule:
     """Same three entry points, argument order and return tuples as the reference's pybind `_C`."""
 
     @staticmethod
+    @_on_tensor_device
     def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                             projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered):
         if means3D.ndim != 2 or means3D.size(1) != 3:
@@ -137,6 +153,7 @@ class _CModule:
         return R, out_color, radii, geom, inst, img, out_depth
 
     @staticmethod
+    @_on_tensor_device
     def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                      viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                      geomBuffer, R, binningBuffer, imageBuffer, power):
@@ -167,6 +184,7 @@ class _CModule:
         return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
 
     @staticmethod
+    @_on_tensor_device
     def mark_visible(means3D, viewmatrix, projmatrix):
         L = _lib.lib()
         P = means3D.size(0)

@@ -14,7 +14,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from .rasterizer import GaussianRasterizationSettings, _camera, _f32c, _stream
+from .rasterizer import GaussianRasterizationSettings, _camera, _f32c, _on_tensor_device, _stream
 
 
 def setup_camera(w, h, k, w2c, near=0.01, far=100, device="cuda"):
@@ -135,7 +135,7 @@ class FisherScorer:
     """Scores candidate poses by expected information gain, sum(H_candidate * 1/(H_train + lambda))."""
 
     def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=32,
-                 inst_capacity=None, chunk_lanes=2):
+                 inst_capacity=None, chunk_lanes=2, vis_capacity=None):
         """chunk_lanes=2: the workspace holds two chunks and `fb_score_candidates` alternates consecutive chunks
         between the caller's stream and a second stream (latency-bound binning kernels of one chunk run under the
         issue-bound kernels of the other); 1 = one chunk at a time, half the workspace."""
@@ -145,8 +145,8 @@ class FisherScorer:
         self.cam, self.C_H, self.grad_scale = cam, C_H, float(grad_scale)
         self.V = int(views_per_chunk)
         self.inst_capacity = inst_capacity
+        self.vis_capacity = vis_capacity
         self._ws = None
-        self._ws_key = None
         self.last_status = None
         self.last_instances = 0
         self.last_visible = 0
@@ -157,15 +157,12 @@ class FisherScorer:
         return _camera(rs.bg, rs.scale_modifier, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
                        rs.image_width, rs.sh_degree, 0, rs.campos, rs.prefiltered)
 
-    def _workspace(self, gmap, cap):
-        L = _lib.lib()
-        key = (gmap.P, self.V, cap, gmap.means3D.device)
-        if self._ws_key != key:
-            n = L.fb_score_workspace_bytes(gmap.P, self.cam.image_width, self.cam.image_height, self.V, cap)
-            n *= self.chunk_lanes
+    def _workspace(self, gmap, nbytes):
+        """One grow-only device buffer shared by the scoring and the H_train entry points."""
+        dev = gmap.means3D.device
+        if self._ws is None or self._ws.device != dev or self._ws.numel() < nbytes:
             self._ws = None
-            self._ws = torch.empty((n,), dtype=torch.uint8, device=gmap.means3D.device)
-            self._ws_key = key
+            self._ws = torch.empty((int(nbytes),), dtype=torch.uint8, device=dev)
         return self._ws
 
     def _capacity(self, gmap):
@@ -174,21 +171,34 @@ class FisherScorer:
             self.inst_capacity = max(1 << 20, int(1.5 * gmap.P) * self.V)
         return int(self.inst_capacity)
 
+    def _vis_capacity(self, gmap):
+        """Visible Gaussians (radii > 0) a single view may have; the per-view records are sized by it.  Small maps:
+        everything; large maps: half the map (an indoor view sees 10-35 % of it), grown on overflow."""
+        if self.vis_capacity is None or self.vis_capacity > gmap.P:
+            self.vis_capacity = gmap.P if gmap.P <= (1 << 17) else max(1 << 17, gmap.P // 2)
+        return int(self.vis_capacity)
+
     def _run(self, fn_name, gmap, w2c, extra):
-        """Common driver with grow-on-overflow.  Reads the 12-byte status once per call (the only sync)."""
+        """Common driver with grow-on-overflow.  Reads the 32-byte status once per call (the only sync)."""
         L = _lib.lib()
-        w2c = _f32c(w2c.to(device=gmap.means3D.device, dtype=torch.float32).reshape(-1, 4, 4))
+        dev = gmap.means3D.device
+        w2c = _f32c(w2c.to(device=dev, dtype=torch.float32).reshape(-1, 4, 4))
         K = w2c.shape[0]
         cam, m = self._c_cam(), gmap.c_struct()
-        status = torch.zeros((8,), dtype=torch.int32, device=gmap.means3D.device)
+        status = torch.zeros((8,), dtype=torch.int32, device=dev)
+        W, H = self.cam.image_width, self.cam.image_height
         while True:
-            cap = self._capacity(gmap)
-            ws = self._workspace(gmap, cap)
-            rc = extra(L, cam, m, w2c, K, status, ws, cap)
+            cap, vcap = self._capacity(gmap), self._vis_capacity(gmap)
+            if fn_name == "fb_score_candidates":
+                n = L.fb_score_workspace_bytes(gmap.P, W, H, self.V, cap, vcap) * self.chunk_lanes
+            else:
+                n = L.fb_hessian_workspace_bytes(gmap.P, W, H, self.V, cap)
+            ws = self._workspace(gmap, n)
+            n0 = L.fb_launch_count()
+            with torch.cuda.device(dev):              # library state (second lane's stream, attributes) is per device
+                rc = extra(L, cam, m, w2c, K, status, ws, n, cap, vcap)
             _lib.check(rc, fn_name)
-            tiles = ((self.cam.image_width + 15) // 16) * ((self.cam.image_height + 15) // 16)
-            nchunks = (K + self.V - 1) // self.V
-            self.launches += nchunks * 7 if fn_name == "fb_score_candidates" else nchunks * 7
+            self.launches += int(L.fb_launch_count() - n0)
             st = status.tolist()
             self.last_status = st
             self.last_instances = st[3]   # sum of num_rendered over the poses of this call
@@ -196,7 +206,10 @@ class FisherScorer:
             if st[0] == 0:
                 return
             if st[0] == _lib.FB_E_CAPACITY:
-                self.inst_capacity = int(st[1] * 1.25) + 1024
+                if st[1] > cap:
+                    self.inst_capacity = int(st[1] * 1.25) + 1024
+                if fn_name == "fb_score_candidates" and st[5] > vcap:
+                    self.vis_capacity = min(gmap.P, int(st[5] * 1.25) + 1024)
                 continue
             _lib.check(st[0], fn_name)
 
@@ -208,10 +221,10 @@ class FisherScorer:
         weight = _f32c(gmap.to_map_order(H_train_inv.reshape(gmap.P, self.C_H)))
         scores = torch.zeros((K,), dtype=torch.float32, device=gmap.means3D.device)
 
-        def call(L, cam, m, w2c_t, K_, status, ws, cap):
+        def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
             return L.fb_score_candidates(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, weight.data_ptr(), self.C_H,
                                          self.grad_scale, scores.data_ptr(), status.data_ptr(), ws.data_ptr(),
-                                         ws.numel(), self.V, cap, _stream())
+                                         nbytes, self.V, cap, vcap, _stream())
         self._run("fb_score_candidates", gmap, w2c, call)
         return scores
 
@@ -220,10 +233,10 @@ class FisherScorer:
         """H_train[P,C_H] = sum over keyframes of the per-view Fisher diagonal (gaussian.py:1338-1348)."""
         H = torch.zeros((gmap.P, self.C_H), dtype=torch.float32, device=gmap.means3D.device)   # map order
 
-        def call(L, cam, m, w2c_t, K_, status, ws, cap):
+        def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
             H.zero_()
             return L.fb_accumulate_hessian(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, self.C_H, self.grad_scale,
-                                           H.data_ptr(), status.data_ptr(), ws.data_ptr(), ws.numel(), self.V, cap,
+                                           H.data_ptr(), status.data_ptr(), ws.data_ptr(), nbytes, self.V, cap,
                                            _stream())
         self._run("fb_accumulate_hessian", gmap, keyframe_w2c, call)
         H = gmap.to_caller_order(H)
@@ -353,6 +366,7 @@ class FisherScorer:
 
     # ---- POp-GS block form (gaussian_object.py:1572-1586, 1660-1703, 1720-1732, 2112-2176) ----
     @torch.no_grad()
+    @_on_tensor_device
     def estimate_block_JtJ(self, gmap: GaussianMap, w2c, K=2, use_rot=True, use_scale=True, use_opacity=True,
                            probes=None, generator=None):
         """estimate_block_JtJ (gaussian_object.py:2112-2176): d x d blocks 1/K * sum_k g_k g_k^T of the Gaussians with
@@ -413,6 +427,7 @@ class FisherScorer:
             raise RuntimeError("No keyframes available for POP-GS prior (blocks).")   # :1585
         return Hm, vis_ref
 
+    @_on_tensor_device
     def _block_opt(self, Hm_blocks, J_blocks, lam, criterion, idx_m=None, idx_j=None, per_block=False):
         L = _lib.lib()
         Hm_blocks, J_blocks = _f32c(Hm_blocks), _f32c(J_blocks)

@@ -9,7 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .rasterizer import _stream
+from .rasterizer import _on_tensor_device, _stream
 
 
 def _intr(intrinsics):
@@ -25,6 +25,7 @@ def _w2c64(c2w):
     return np.stack([np.linalg.inv(m) for m in c2w]).astype(np.float64)
 
 
+@_on_tensor_device
 def count_visible_batch(points, c2w, intrinsics, img_size, return_mask=False):
     """points: f32 [N,3] CUDA tensor; c2w: [K,4,4] (numpy or tensor).  Returns int32 counts [K] on the
     device (and, optionally, the bool mask [K,N])."""

@@ -102,6 +102,8 @@ typedef struct fb_gaussians {
 const char* fb_error_string(int status);
 int         fb_last_cuda_error(void);     /* cudaError_t of the last FB_E_CUDA, as int */
 int         fb_version(void);
+/* Number of kernels this library has launched in this process so far (every launch site counts itself). */
+unsigned long long fb_launch_count(void);
 
 /* Optional per-kernel timing for bench.py's roofline: while enabled, CUDA events are recorded on the
  * launching stream around every kernel launch; fb_profile_read synchronises on them, sums the elapsed
@@ -200,18 +202,26 @@ typedef struct fb_map {
 } fb_map;
 
 /* Workspace for scoring `views_per_chunk` (1..64) poses at a time with room for
- * `inst_capacity` (Gaussian,tile) instances per chunk.  The map may be given in any order; a spatially
- * coherent order (the Python GaussianMap stores it Morton-sorted) lets the kernels aggregate their tile
- * counters per warp and is ~20 % faster, with the same results. */
+ * `inst_capacity` (Gaussian,tile) instances per chunk and `vis_capacity` visible Gaussians (radii > 0) per
+ * view (0 or >= P: P).  Per-view records are stored in the view's visible slot, so the workspace is
+ * 112 * views_per_chunk * vis_capacity bytes plus keys, not 112 * views_per_chunk * P.  The map may be given in
+ * any order; a spatially coherent order (the Python GaussianMap stores it Morton-sorted) lets the kernels
+ * aggregate their tile counters per warp and is ~20 % faster, with the same results. */
 size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chunk,
-                                long long inst_capacity);
+                                long long inst_capacity, long long vis_capacity);
+/* Workspace of fb_accumulate_hessian (per-view records and moment rows are indexed by Gaussian id). */
+size_t fb_hessian_workspace_bytes(int P, int width, int height, int views_per_chunk,
+                                  long long inst_capacity);
 
-/* Chunk lanes.  If `workspace_bytes` >= 2 * fb_score_workspace_bytes(...) and K > views_per_chunk,
+/* Chunk lanes.  If `workspace_bytes` >= 2 * fb_score_workspace_bytes(...) and K > 1,
  * fb_score_candidates alternates consecutive chunks between the caller's stream and a library-owned
  * stream, each in its own half of the workspace (the latency-bound binning kernels of one chunk run
- * under the issue-bound kernels of the other); the caller's stream waits for both before the call's
- * work is complete on it.  Results do not change.  fb_score_set_lanes(0) keeps every chunk on the
- * caller's stream; so does fb_profile_enable(1), so that its event pairs time kernels alone. */
+ * under the issue-bound kernels of the other; K <= views_per_chunk is split into two half chunks); the
+ * caller's stream waits for both before the call's work is complete on it.  Results do not change.
+ * fb_score_set_lanes(0) keeps every chunk on the caller's stream; so does fb_profile_enable(1), so that
+ * its event pairs time kernels alone.  Library state (the second stream, function attributes) is kept per
+ * device and belongs to the device that is CURRENT when the call is made: make the device of the buffers
+ * current before calling (one host thread per device). */
 int fb_score_set_lanes(int on);
 
 /* scores[k] = sum_{g,c} H_k[g,c] * weight[g,c]   for k in [0,K)
@@ -223,22 +233,23 @@ int fb_score_set_lanes(int on);
  * w2c: K row-major 4x4 world-to-camera matrices (the poses AFTER torch.linalg.inv,
  * gaussian.py:1364); means are moved to the camera frame with them while rotations
  * stay in the world frame, exactly as the reference does (gaussian.py:1527-1529).
- * status_dev (8 ints): [0] 0 or FB_E_CAPACITY, [1] the instance count the largest chunk needed,
- * [2] the longest per-tile list seen, [3] total (Gaussian,tile) instances over all K poses
- * (the reference's num_rendered summed), [4] total visible Gaussians (radii > 0) over all K poses,
- * [5..7] reserved; read it whenever the scores are read.  No host sync inside. */
+ * status_dev (8 ints): [0] 0 or FB_E_CAPACITY (inst_capacity or vis_capacity too small: grow and call again),
+ * [1] the instance count the largest chunk needed, [2] the longest per-tile list seen, [3] total
+ * (Gaussian,tile) instances over all K poses (the reference's num_rendered summed), [4] total visible
+ * Gaussians (radii > 0) over all K poses, [5] the largest visible count of a single pose (what vis_capacity
+ * must hold), [6..7] reserved; read it whenever the scores are read.  No host sync inside. */
 int fb_score_candidates(const fb_camera* cam, const fb_map* map,
                         const float* w2c, int K,
                         const float* weight, int C_H, float grad_scale,
                         float* scores, int* status_dev,
                         void* workspace, size_t workspace_bytes,
-                        int views_per_chunk, long long inst_capacity,
+                        int views_per_chunk, long long inst_capacity, long long vis_capacity,
                         void* stream);
 
 /* H_out[g,c] += sum_k H_k[g,c]   (compute_H_train, gaussian.py:1338-1348).
  * H_out is [P,C_H], caller-initialised.  Keyframes are processed views_per_chunk (<= 64) per launch
  * sequence; the per-Gaussian sum over the views of a chunk is formed in a fixed order (no atomics on H_out).
- * Same workspace (fb_score_workspace_bytes) and status convention as fb_score_candidates. */
+ * Workspace: fb_hessian_workspace_bytes; same status convention as fb_score_candidates. */
 int fb_accumulate_hessian(const fb_camera* cam, const fb_map* map,
                           const float* w2c, int K,
                           int C_H, float grad_scale,

@@ -33,7 +33,11 @@ def test_host_only_entry_points():
     assert L.fb_geom_bytes(1000) >= 1000 * 32 and L.fb_geom_bytes(0) > 0
     assert L.fb_image_bytes(256, 256) >= 256 * 256 * 8
     assert L.fb_inst_bytes(10) >= 80
-    assert L.fb_score_workspace_bytes(1000, 256, 256, 4, 1 << 16) > 4 * 1000 * 96
+    assert L.fb_score_workspace_bytes(1000, 256, 256, 4, 1 << 16, 0) > 4 * 1000 * 112
+    # records are sized by the visible capacity, not by the map
+    assert L.fb_score_workspace_bytes(100000, 256, 256, 4, 1 << 16, 25000) < L.fb_score_workspace_bytes(100000, 256, 256, 4, 1 << 16, 0) // 2
+    assert L.fb_hessian_workspace_bytes(1000, 256, 256, 4, 1 << 16) > 4 * 1000 * 112
+    assert L.fb_launch_count() == 0
     assert L.fb_knn_workspace_bytes(1000) > 0
 
 

@@ -71,7 +71,7 @@ def test_sh_colours_forward(cuda, oracle, degree):
     ref = _ref_ext()
     if ref is not None:
         # Integers only: in this build the reference extension's SH forward returns an image that depends on what
-        # ran before it (all zeros, or not, for the same call; scratch/dbg_sh2.py), so its colours cannot serve as
+        # ran before it (all zeros, or not, for the same call), so its colours cannot serve as
         # the expected value.  No reference caller passes SH (colors_precomp always, gaussian.py:1536-1543); the
         # colours are checked against the CPU restatement of forward.cu:20-71 below.
         want = _fwd(ref, torch, rs, t, shs=shs, degree=degree)

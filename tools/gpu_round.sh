@@ -1,6 +1,6 @@
 #!/bin/bash
 # One GPU-box visit: parity tests, both bench arms, ncu launch list, ncu --set full of the top kernels.
-# usage: scratch/gpu_round.sh <tag> [skip_tests] [skip_ref]
+# usage: tools/gpu_round.sh <tag> [skip_tests] [skip_ref]
 TAG=${1:-run}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${TAG}_smi.txt 2>&1

@@ -1,4 +1,4 @@
-"""torchrun --nproc-per-node 2 scratch/nccl_delta.py : delta map update over NCCL (owner densifies a frame, replicas
+"""torchrun --nproc-per-node 2 tools/nccl_delta.py : delta map update over NCCL (owner densifies a frame, replicas
 receive only the new rows), then both ranks score the same candidates on the grown map and compare."""
 import os, sys
 import numpy as np, torch, torch.distributed as dist

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Summarise an ncu report: scratch/ncu_summary.py gpurun_out/x.ncu-rep"""
+"""Summarise an ncu report: tools/ncu_summary.py gpurun_out/x.ncu-rep"""
 import csv, subprocess, sys, io
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

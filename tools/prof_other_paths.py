@@ -1,5 +1,5 @@
 """One pass over the kernels OFF the headline bench (drop-in single view, H_train, stage 5, block form, densify) for an
-ncu capture: python scratch/prof_other_paths.py [reps]"""
+ncu capture: python tools/prof_other_paths.py [reps]"""
 import numpy as np, torch, sys, os, time
 sys.path.insert(0, os.getcwd())
 import fisher_nerf_customized_b200 as fb

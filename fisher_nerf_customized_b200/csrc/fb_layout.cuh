@@ -17,7 +17,9 @@ namespace fb {
 static inline __host__ __device__ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // One projected Gaussian of one view: 32 bytes, 32-byte aligned.
+#ifndef FB_TC_STRIDE
 #define FB_TC_STRIDE 32   // uint32 slots per tile counter (128 B)
+#endif
 
 struct __align__(16) GRec {
     float4 a;  // px, py, depth, opacity

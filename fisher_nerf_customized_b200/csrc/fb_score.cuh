@@ -275,9 +275,16 @@ __device__ __forceinline__ void f2_acc(f32x2& acc, f32x2 a, f32x2 b) { acc = f2_
 #ifndef FB_S2_WPC
 #define FB_S2_WPC 4               // warps per CTA
 #endif
-#define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ) * FB_S2_WPC)
+#ifndef FB_S2_MINB
+#define FB_S2_MINB 8              // minimum resident CTAs per SM asked of ptxas (register budget)
+#endif
+#ifndef FB_S2_LIST
+#define FB_S2_LIST 1              // 1: surviving ring slots are compacted into a byte list (no BREV/FLO in the loop)
+#endif
+struct WarpQ2 { WarpQ q; unsigned char list[32]; unsigned char pad[96]; };
+#define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ2) * FB_S2_WPC)
 
-__global__ void __launch_bounds__(32 * FB_S2_WPC) k_tile_score2(Bins bins, Cam cam, float grad_scale,
+__global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins bins, Cam cam, float grad_scale,
                                                                  float* __restrict__ partial) {
     extern __shared__ float4 smem[];
     constexpr int CPT = FB_S2_BLOCKS / FB_S2_WPC;
@@ -302,7 +309,8 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC) k_tile_score2(Bins bins, Cam c
     const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
     const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
     const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
-    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
+    WarpQ2& q2 = reinterpret_cast<WarpQ2*>(smem)[wq];
+    WarpQ& q = q2.q;
 
     f32x2 T = f2_dup(1.0f), Cp = f2_dup(0.f), Qaa = f2_dup(0.f), Qab = f2_dup(0.f), Qbb = f2_dup(0.f);
 #if FB_S2_STATS
@@ -376,10 +384,18 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC) k_tile_score2(Bins bins, Cam c
 #if FB_S2_STATS == 3
                 if (lane == 0) stat += (float)__popc(todo);
 #endif
+#if FB_S2_LIST
+                if ((todo >> lane) & 1u) q2.list[__popc(todo & lt)] = (unsigned char)(qh + lane);
+                __syncwarp();
+                const int nkeep = __popc(todo);
+                for (int i = 0; i < nkeep; ++i) {
+                    const int slot = q2.list[i];
+#else
                 while (todo) {
                     const int h = __ffs(todo) - 1;
                     todo &= todo - 1u;
                     const int slot = qh + h;
+#endif
                     const float2 mu = *reinterpret_cast<const float2*>(&q.a[slot]);
                     const float4 co = q.b[slot];
                     const float dx = mu.x - pxf;

@@ -111,8 +111,62 @@ class ShardedScorer:
         out.copy_(torch.cat(parts))
 
     def pose_eval(self, gmap, poses_c2w, keyframe_w2c, H_reg_lambda=0.1):
-        H_train = self.compute_H_train(gmap, keyframe_w2c)
-        H_train_inv = torch.reciprocal(H_train + H_reg_lambda)
-        w2c = torch.linalg.inv(poses_c2w.float())
-        scores = self.score_candidates(gmap, w2c, H_train_inv)
-        return scores, (int(torch.argmax(scores).item()) if scores.numel() else -1)
+        """One planning step (pose_eval, gaussian.py:1354-1375) over the ranks: H_train from round-robin keyframes +
+        all-reduce, reciprocal, this rank's block of candidates, all-gather, argmax.  Returns (scores [K], argmax) --
+        identical on every rank.
+        With a scorer that can defer its status check (FisherScorer: `deferred`), the whole step has ONE host sync:
+        both status blocks travel with the scores in the all-gather payload and are read with them; if any rank reports
+        a capacity overflow every rank grows and the step is repeated (all ranks see all status blocks, so they agree)."""
+        if not getattr(self.scorer, "deferred", False):
+            H_train = self.compute_H_train(gmap, keyframe_w2c)
+            H_train_inv = torch.reciprocal(H_train + H_reg_lambda)
+            w2c = torch.linalg.inv(poses_c2w.float())
+            scores = self.score_candidates(gmap, w2c, H_train_inv)
+            return scores, (int(torch.argmax(scores).item()) if scores.numel() else -1)
+        dev = gmap.means3D.device
+        sc = self.scorer
+        K = int(poses_c2w.shape[0])
+        w2c = torch.linalg.inv(poses_c2w.to(device=dev, dtype=torch.float32).reshape(-1, 4, 4))
+        kf = keyframe_w2c.to(device=dev, dtype=torch.float32).reshape(-1, 4, 4)
+        mine = round_robin(int(kf.shape[0]), self.world, self.rank)
+        lo, hi = shard_bounds(K, self.world, self.rank)
+        per = (K + self.world - 1) // self.world if K > 0 else 0
+        zero_status = torch.zeros((8,), dtype=torch.int32, device=dev)
+        while True:
+            if mine:
+                H, st_h = sc.compute_H_train(gmap, kf[mine], sync=False, map_order=True)
+            else:
+                H, st_h = torch.zeros((gmap.P, sc.C_H), dtype=torch.float32, device=dev), zero_status
+            if self.world > 1:
+                dist.all_reduce(H, op=dist.ReduceOp.SUM, group=self.group)
+            H_inv = torch.reciprocal(H + H_reg_lambda)
+            payload = torch.zeros((per + 16,), dtype=torch.int32, device=dev)
+            st_s = zero_status
+            if hi > lo:
+                local, st_s = sc.score_candidates(gmap, w2c[lo:hi], H_inv, sync=False, map_order=True)
+                payload[: hi - lo] = local.view(torch.int32)
+            payload[per: per + 8] = st_h
+            payload[per + 8: per + 16] = st_s
+            if self.world > 1:
+                gathered = torch.empty((self.world * (per + 16),), dtype=torch.int32, device=dev)
+                if dev.type == "cuda":
+                    dist.all_gather_into_tensor(gathered, payload, group=self.group)
+                else:
+                    self._gather_cpu(gathered, payload)
+            else:
+                gathered = payload
+            host = gathered.cpu().reshape(self.world, per + 16)          # the step's one host sync
+            ok = True
+            for r in range(self.world):
+                # every rank digests every rank's status: capacities grow alike, so replicas stay in step
+                mine_r = r == self.rank
+                st_h_r, st_s_r = host[r, per: per + 8].tolist(), host[r, per + 8: per + 16].tolist()
+                if mine_r:
+                    ok_h = sc.accept_status(st_h_r, "fb_accumulate_hessian", gmap.P)
+                    ok_s = sc.accept_status(st_s_r, "fb_score_candidates", gmap.P)
+                    ok = ok and ok_h and ok_s
+                else:
+                    ok = ok and st_h_r[0] == 0 and st_s_r[0] == 0
+            if ok:
+                scores = host[:, :per].contiguous().view(torch.float32).reshape(-1)[:K]
+                return scores, (int(torch.argmax(scores)) if K else -1)

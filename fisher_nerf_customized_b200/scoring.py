@@ -134,6 +134,8 @@ class GaussianMap:
 class FisherScorer:
     """Scores candidate poses by expected information gain, sum(H_candidate * 1/(H_train + lambda))."""
 
+    deferred = True       # score_candidates / compute_H_train take sync=False (ShardedScorer.pose_eval: one sync per step)
+
     def __init__(self, cam: GaussianRasterizationSettings, C_H=4, grad_scale=1e-3, views_per_chunk=32,
                  inst_capacity=None, chunk_lanes=2, vis_capacity=None):
         """chunk_lanes=2: the workspace holds two chunks and `fb_score_candidates` alternates consecutive chunks
@@ -178,8 +180,11 @@ class FisherScorer:
             self.vis_capacity = gmap.P if gmap.P <= (1 << 17) else max(1 << 17, gmap.P // 2)
         return int(self.vis_capacity)
 
-    def _run(self, fn_name, gmap, w2c, extra):
-        """Common driver with grow-on-overflow.  Reads the 32-byte status once per call (the only sync)."""
+    def _run(self, fn_name, gmap, w2c, extra, sync=True):
+        """Common driver with grow-on-overflow.  sync=True reads the 32-byte status once per call (the only host
+        sync) and re-runs with larger capacities if the device reported an overflow.  sync=False launches once and
+        returns the device status tensor instead: the caller reads it together with its own results (one sync per
+        planning step instead of one per call) and hands it to `accept_status`."""
         L = _lib.lib()
         dev = gmap.means3D.device
         w2c = _f32c(w2c.to(device=dev, dtype=torch.float32).reshape(-1, 4, 4))
@@ -199,38 +204,51 @@ class FisherScorer:
                 rc = extra(L, cam, m, w2c, K, status, ws, n, cap, vcap)
             _lib.check(rc, fn_name)
             self.launches += int(L.fb_launch_count() - n0)
-            st = status.tolist()
-            self.last_status = st
-            self.last_instances = st[3]   # sum of num_rendered over the poses of this call
-            self.last_visible = st[4]     # sum of (radii > 0) over the poses of this call
-            if st[0] == 0:
-                return
-            if st[0] == _lib.FB_E_CAPACITY:
-                if st[1] > cap:
-                    self.inst_capacity = int(st[1] * 1.25) + 1024
-                if fn_name == "fb_score_candidates" and st[5] > vcap:
-                    self.vis_capacity = min(gmap.P, int(st[5] * 1.25) + 1024)
-                continue
-            _lib.check(st[0], fn_name)
+            if not sync:
+                return status
+            if self.accept_status(status.tolist(), fn_name, gmap.P):
+                return status
+
+    def accept_status(self, st, fn_name="fb_score_candidates", P=None):
+        """Digest a status block read from the device (8 ints).  True: the call's results are valid.  False: a capacity
+        was too small; it has been grown and the call must be repeated.  Other errors raise."""
+        st = [int(x) for x in st]
+        self.last_status = st
+        self.last_instances = st[3]   # sum of num_rendered over the poses of this call
+        self.last_visible = st[4]     # sum of (radii > 0) over the poses of this call
+        if st[0] == 0:
+            return True
+        if st[0] == _lib.FB_E_CAPACITY:
+            if st[1] > int(self.inst_capacity or 0):
+                self.inst_capacity = int(st[1] * 1.25) + 1024
+            if fn_name == "fb_score_candidates" and st[5] > int(self.vis_capacity or 0):
+                self.vis_capacity = int(st[5] * 1.25) + 1024 if P is None else min(P, int(st[5] * 1.25) + 1024)
+            return False
+        _lib.check(st[0], fn_name)
 
     @torch.no_grad()
-    def score_candidates(self, gmap: GaussianMap, w2c, H_train_inv):
+    def score_candidates(self, gmap: GaussianMap, w2c, H_train_inv, sync=True, map_order=False):
         """scores[k] = sum(H_k * H_train_inv), H_k the Fisher diagonal of pose k (gaussian.py:1362-1370).
-        w2c: [K,4,4] world-to-camera (already inverted).  Returns a CUDA float tensor [K]."""
+        w2c: [K,4,4] world-to-camera (already inverted).  Returns a CUDA float tensor [K].
+        map_order=True: H_train_inv is already in the map's resident order (what compute_H_train(map_order=True)
+        returns), no permutation.  sync=False: no host sync; returns (scores, status tensor), see `_run`."""
         K = w2c.reshape(-1, 4, 4).shape[0]
-        weight = _f32c(gmap.to_map_order(H_train_inv.reshape(gmap.P, self.C_H)))
+        H_train_inv = H_train_inv.reshape(gmap.P, self.C_H)
+        weight = _f32c(H_train_inv if map_order else gmap.to_map_order(H_train_inv))
         scores = torch.zeros((K,), dtype=torch.float32, device=gmap.means3D.device)
 
         def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
             return L.fb_score_candidates(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, weight.data_ptr(), self.C_H,
                                          self.grad_scale, scores.data_ptr(), status.data_ptr(), ws.data_ptr(),
                                          nbytes, self.V, cap, vcap, _stream())
-        self._run("fb_score_candidates", gmap, w2c, call)
-        return scores
+        status = self._run("fb_score_candidates", gmap, w2c, call, sync=sync)
+        return scores if sync else (scores, status)
 
     @torch.no_grad()
-    def compute_H_train(self, gmap: GaussianMap, keyframe_w2c, out=None):
-        """H_train[P,C_H] = sum over keyframes of the per-view Fisher diagonal (gaussian.py:1338-1348)."""
+    def compute_H_train(self, gmap: GaussianMap, keyframe_w2c, out=None, sync=True, map_order=False):
+        """H_train[P,C_H] = sum over keyframes of the per-view Fisher diagonal (gaussian.py:1338-1348), in the
+        caller's Gaussian order (map_order=True: in the map's resident order, no permutation).
+        sync=False: no host sync; returns (H, status tensor), see `_run`."""
         H = torch.zeros((gmap.P, self.C_H), dtype=torch.float32, device=gmap.means3D.device)   # map order
 
         def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
@@ -238,12 +256,13 @@ class FisherScorer:
             return L.fb_accumulate_hessian(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, self.C_H, self.grad_scale,
                                            H.data_ptr(), status.data_ptr(), ws.data_ptr(), nbytes, self.V, cap,
                                            _stream())
-        self._run("fb_accumulate_hessian", gmap, keyframe_w2c, call)
-        H = gmap.to_caller_order(H)
+        status = self._run("fb_accumulate_hessian", gmap, keyframe_w2c, call, sync=sync)
+        if not map_order:
+            H = gmap.to_caller_order(H)
         if out is not None:
             out += H
-            return out
-        return H
+            H = out
+        return H if sync else (H, status)
 
     @torch.no_grad()
     def compute_Hessian(self, gmap: GaussianMap, rel_w2c):

@@ -29,6 +29,34 @@ class FakeScorer:
         return kf[:, 0, 3].sum() * torch.ones((gmap.P, self.C_H))
 
 
+class FakeDeferredScorer(FakeScorer):
+    """The sync=False protocol of FisherScorer: results + a device status block, digested by accept_status.  The first
+    scoring call of rank 1 reports a capacity overflow, so every rank must repeat the step."""
+    deferred = True
+
+    def __init__(self, rank):
+        self.rank, self.calls, self.grown = rank, 0, 0
+
+    def compute_H_train(self, gmap, kf, sync=True, map_order=False):
+        assert sync is False and map_order is True
+        return FakeScorer.compute_H_train(self, gmap, kf), torch.zeros(8, dtype=torch.int32)
+
+    def score_candidates(self, gmap, w2c, weight, sync=True, map_order=False):
+        assert sync is False and map_order is True
+        st = torch.zeros(8, dtype=torch.int32)
+        self.calls += 1
+        if self.rank == 1 and self.calls == 1:
+            st[0], st[1] = -4, 12345
+        return FakeScorer.score_candidates(self, gmap, w2c, weight), st
+
+    def accept_status(self, st, fn_name="", P=None):
+        if st[0] == 0:
+            return True
+        assert st[0] == -4
+        self.grown += 1
+        return False
+
+
 def _poses(n, off=0.0):
     p = torch.eye(4).repeat(n, 1, 1)
     p[:, 0, 3] = torch.arange(n, dtype=torch.float32) + 1 + off
@@ -48,6 +76,12 @@ def _worker(rank, world, port, K, NKF, out):
         t = [torch.full((3,), float(rank))]
         sh.broadcast_map(t, src=0)
         scores, best = sh.pose_eval(gmap, torch.linalg.inv(_poses(K, 0.25)), _poses(NKF), 0.1)
+        # the one-sync form of the same step (status blocks ride in the all-gather payload; rank 1 overflows once)
+        dsc = FakeDeferredScorer(rank)
+        scores_d, best_d = ShardedScorer(dsc).pose_eval(gmap, torch.linalg.inv(_poses(K, 0.25)), _poses(NKF), 0.1)
+        assert torch.equal(scores_d, scores) and best_d == best
+        if K >= 2:
+            assert dsc.calls == 2 and dsc.grown == (1 if rank == 1 else 0)    # every rank repeated the step
         out[rank] = (H.numpy(), s.numpy(), t[0].numpy(), scores.numpy(), best)
     finally:
         dist.destroy_process_group()

@@ -8,6 +8,10 @@ One "step" = one pass of the hot path over one batch of candidate poses: every r
 256 candidate poses (BASELINE cfg 3: 500k Gaussians, 256 candidates, 256x256, C_H = 4, lambda = 0.1)
 against its replica of the Gaussian map, then the per-candidate scores are all-gathered (weak scaling:
 per-GPU work is fixed; the candidate set shards with no data-path exchange inside a view).
+The same line carries `strong_k256`: BASELINE cfg 3 as written -- ONE set of 256 candidates and 32 keyframes for
+the whole job, split over the N ranks (ShardedScorer.pose_eval: round-robin H_train + all-reduce, reciprocal, K/N
+candidates per rank, all-gather, argmax), every collective inside the timed region -- and `per_rank` (ms and
+instances of each rank) so that a loss at N = 8 can be attributed.
 
 Keys of the JSON line: see the contract in the task statement.  `value` is device-resident throughput
 (CUDA events, L2 flushed between steps, max over ranks); `e2e` goes through the public API with HOST
@@ -38,6 +42,15 @@ LAMBDA = 0.1
 GRAD_SCALE = 1e-3
 METRIC = "candidate views scored/s (500k Gaussians, 256^2, Fisher diag)"
 UNIT = "views/s"
+
+
+def workload_config():
+    """The workload, worded identically by both arms (implementation details go under `notes`, outside `config`)."""
+    return {"workload": "cfg3: EIG scoring, 500k Gaussians x 256 candidate poses per GPU per step at 256x256, C_H=4, "
+                        f"lambda=0.1, H_train from {N_KEYFRAMES} keyframes",
+            "P": P_GAUSS, "K_per_gpu": K_CAND, "image": f"{W}x{H}", "C_H": C_H, "lambda": LAMBDA,
+            "keyframes": N_KEYFRAMES, "scene": "shell seed 1234", "poses": "seed 5678 + 100 * rank",
+            "l2": "256 MiB fill between steps, outside the timed events"}
 
 
 def parse():
@@ -175,7 +188,7 @@ def run_b200(args):
 
     rank, world, local = dist_setup(args)
     dev = torch.device("cuda", local)
-    _lib.lib()   # raises if libfisher_b200.so is missing: no fallback
+    L = _lib.lib()   # raises if libfisher_b200.so is missing: no fallback
     sc = synth.activate(synth.make_scene(P_GAUSS))
     t = {k: torch.from_numpy(v).to(dev) for k, v in sc.items()}
     gmap = fb.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"])
@@ -209,7 +222,7 @@ def run_b200(args):
         scores_pinned.copy_(s, non_blocking=True)                   # D2H: K x 4 B
         return s
 
-    def timed(fn, steps, profile=False):
+    def timed(fn, steps):
         tot = 0.0
         for _ in range(steps):
             flush.fill_(1)                                           # L2 flush, outside the timed events
@@ -222,17 +235,28 @@ def run_b200(args):
             tot += a.elapsed_time(b)
         return tot
 
+    def per_rank(values):
+        """[world, len(values)] float64 on every rank (one tiny all-gather, outside every timed region)."""
+        x = torch.tensor(values, dtype=torch.float64, device=dev)
+        if world == 1:
+            return x.reshape(1, -1).cpu().numpy()
+        out = torch.empty((world, len(values)), dtype=torch.float64, device=dev)
+        torch.distributed.all_gather_into_tensor(out, x)
+        return out.cpu().numpy()
+
     for _ in range(max(args.warmup, 3)):
         step_resident()
     barrier(world)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    scorer.launches = 0
-    ms = timed(step_resident, args.steps)
-    launches = scorer.launches
+    n0 = L.fb_launch_count()
+    ms_rank = timed(step_resident, args.steps)
+    launches = int(L.fb_launch_count() - n0)                        # counted by the library at every launch site
     barrier(world)
-    ms = max_over_ranks(ms, world)
+    ms = max_over_ranks(ms_rank, world)
+    R_step, vis_step = scorer.last_instances, scorer.last_visible
+    ranks = per_rank([ms_rank / args.steps, float(R_step), float(vis_step)])
     # per-kernel CUDA events: the same K steps once more with fb_profile on.  While it is on the library keeps the
     # chunks on ONE stream (no chunk lanes), so every event pair times its kernel alone, like the ncu launch list.
     _lib.profile_enable(True)
@@ -242,7 +266,6 @@ def run_b200(args):
     _lib.profile_enable(False)
     barrier(world)
     clocks = sampler.stop() if rank == 0 else None
-    R_step, vis_step = scorer.last_instances, scorer.last_visible
     scores_resident = step_resident().cpu().numpy()
 
     for _ in range(2):
@@ -252,6 +275,45 @@ def run_b200(args):
     barrier(world)
     ms_e2e = max_over_ranks(ms_e2e, world)
     assert np.allclose(scores_pinned.numpy(), scores_resident, rtol=1e-4), "e2e and resident paths disagree"
+
+    # ---- strong scaling of BASELINE cfg 3 as written: ONE candidate set (rank 0's) and the 32 keyframes for the whole
+    # job; ShardedScorer.pose_eval end to end per step, collectives and the one host sync inside the timed region.
+    c2w_all = torch.from_numpy(synth.make_poses(K_CAND, seed=synth.SEED_POSES)).to(dev)
+    for _ in range(3):
+        s_strong, best_strong = sharded.pose_eval(gmap, c2w_all, kf, LAMBDA)
+    barrier(world)
+    ms_strong_rank = timed(lambda: sharded.pose_eval(gmap, c2w_all, kf, LAMBDA), args.steps)
+    barrier(world)
+    ms_strong = max_over_ranks(ms_strong_rank, world)
+    strong_ranks = per_rank([ms_strong_rank / args.steps])
+    single_ms = None
+    coll = None
+    if world > 1:
+        # the same step on ONE GPU of this box (rank 0 alone, the others wait), for the in-run efficiency
+        if rank == 0:
+            solo = fb.ShardedScorer.__new__(fb.ShardedScorer)
+            solo.scorer, solo.group, solo.world, solo.rank = scorer, None, 1, 0
+            for _ in range(2):
+                s_solo, best_solo = solo.pose_eval(gmap, c2w_all, kf, LAMBDA)
+            single_ms = timed(lambda: solo.pose_eval(gmap, c2w_all, kf, LAMBDA), args.steps) / args.steps
+            assert best_solo == best_strong
+            np.testing.assert_allclose(s_solo.numpy(), s_strong.numpy(), rtol=1e-3)   # all-reduce order differs
+        barrier(world)
+        # the two collectives alone (device time, mean of 20)
+        Hbuf = torch.zeros((P_GAUSS, C_H), dtype=torch.float32, device=dev)
+        small = torch.zeros(((K_CAND + world - 1) // world + 16,), dtype=torch.int32, device=dev)
+        big = torch.empty((world * small.numel(),), dtype=torch.int32, device=dev)
+        coll = {}
+        for name, fn in (("all_reduce_H_us", lambda: torch.distributed.all_reduce(Hbuf)),
+                         ("all_gather_scores_us", lambda: torch.distributed.all_gather_into_tensor(big, small))):
+            for _ in range(5):
+                fn()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(); a.record()
+            for _ in range(20):
+                fn()
+            b.record(); b.synchronize()
+            coll[name] = max_over_ranks(a.elapsed_time(b) / 20 * 1e3, world)
 
     if rank != 0:
         return
@@ -269,18 +331,27 @@ def run_b200(args):
                                          R_step / K_CAND * per_launch_views, W * H, tiles)
     achieved = bytes_per_launch / (dom_ms / dom_n * 1e-3) / 1e9
     B_view = 56.0 * P_GAUSS + 4.0 * C_H * P_GAUSS + 108.0 * (R_step / K_CAND) + 44.0 * W * H + 4
+    strong = {"workload": "cfg3 as written: 256 candidates and 32 keyframes IN TOTAL, split over the ranks; "
+                          "ShardedScorer.pose_eval per step (H_train round-robin + all-reduce, reciprocal, K/N candidates, "
+                          "all-gather with the status blocks, argmax), one host sync, all inside the timed region",
+              "ms_per_plan_step": ms_strong / args.steps, "views_per_s": K_CAND / (ms_strong / args.steps * 1e-3),
+              "argmax": int(best_strong), "per_rank_ms": [float(x) for x in strong_ranks[:, 0]]}
+    if single_ms is not None:
+        strong["single_gpu_ms_same_box"] = single_ms
+        strong["efficiency_vs_n1"] = single_ms / (world * ms_strong / args.steps)
+        strong["collectives_alone"] = coll
+    cfg = workload_config()
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg3: EIG scoring, 500k Gaussians x 256 candidate poses per GPU per step at 256x256, "
-                               f"C_H=4, lambda=0.1, H_train from {N_KEYFRAMES} keyframes", "P": P_GAUSS, "K_per_gpu": K_CAND,
-                   "views_per_chunk": args.views_per_chunk, "scene": "shell seed 1234",
-                   "l2": "256 MiB fill between steps, outside the timed events",
-                   "chunk_lanes": scorer.chunk_lanes,
-                   "kernel_events": "per-kernel CUDA events from a second pass of the same steps with the chunks on one "
-                                    f"stream ({ms_prof / args.steps:.3f} ms per step); value/e2e are timed without them",
-                   "instances_per_view": R_step / K_CAND, "visible_per_view": vis_step / K_CAND},
+        "config": cfg,
+        "notes": {"views_per_chunk": args.views_per_chunk, "chunk_lanes": scorer.chunk_lanes,
+                  "kernel_events": "per-kernel CUDA events from a second pass of the same steps with the chunks on one "
+                                   f"stream ({ms_prof / args.steps:.3f} ms per step); value/e2e are timed without them",
+                  "instances_per_view": R_step / K_CAND, "visible_per_view": vis_step / K_CAND,
+                  "workspace_bytes": int(scorer._ws.numel()) if scorer._ws is not None else None,
+                  "vis_capacity": scorer.vis_capacity, "inst_capacity": scorer.inst_capacity},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": K_CAND * 64, "d2h_bytes_per_step": K_CAND * 4,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
@@ -293,6 +364,9 @@ def run_b200(args):
                      "kernels": {k: {"ms": v[0], "launches": v[1], "share": v[0] / tot_prof} for k, v in prof.items()}},
         "clocks": clocks,
         "argmax": int(np.argmax(scores_resident)),
+        "per_rank": {"ms_per_step": [float(x) for x in ranks[:, 0]], "instances_per_step": [int(x) for x in ranks[:, 1]],
+                     "visible_per_step": [int(x) for x in ranks[:, 2]]},
+        "strong_k256": strong,
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(sc, c2w_np, H_inv.cpu().numpy(), scores_resident)
@@ -350,13 +424,16 @@ def visibility_baseline(dev, N=1_000_000, K=64):
 def run_reference(args):
     """The UNMODIFIED reference CUDA extension (oracle/_ref/ref_dgr, rebuilt for sm_100a from the sources
     under /root/reference) driven exactly as the reference's caller drives it: the per-pose Python loop of
-    pose_eval -> compute_Hessian (models/SLAM/gaussian.py:1362-1370, 1503-1570), one .item() per pose.
-    The reference has no CPU implementation of this path; its own implementation is this extension."""
+    pose_eval -> compute_Hessian (models/SLAM/gaussian.py:1362-1370, 1503-1570) on the raw parameters -- world->camera
+    matmul, normalize / sigmoid / exp per view (:1523-1533), rasterise, backward with 1e-3 * ones, one .item() per pose.
+    The reference has no CPU implementation of this path; its own implementation is this extension.
+    Every step scores ALL 256 candidates of the repo arm's rank-0 set, so `argmax` is comparable."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return                                  # rank 0 alone runs the reference arm
     import torch
+    import torch.nn.functional as F
     from oracle import build_ref
     from fisher_nerf_customized_b200 import synth
     ref_C = build_ref.import_ref("ref_dgr")
@@ -365,8 +442,8 @@ def run_reference(args):
         return
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
     dev = torch.device("cuda", torch.cuda.current_device())
-    sc = synth.activate(synth.make_scene(P_GAUSS))
-    t = {k: torch.from_numpy(v).to(dev) for k, v in sc.items()}
+    raw = synth.make_scene(P_GAUSS)
+    params = {k: torch.from_numpy(np.asarray(v, np.float32)).to(dev) for k, v in raw.items()}
     from oracle import oracle as O
     rs = O.setup_camera_np(W, H, synth.intrinsics(W, H), np.eye(4))
     bg = torch.zeros(3, device=dev)
@@ -374,15 +451,19 @@ def run_reference(args):
     proj = torch.from_numpy(rs["projmatrix"]).to(dev).unsqueeze(0)
     campos = torch.from_numpy(rs["campos"]).to(dev)
     e = torch.Tensor([])
-    pts4 = torch.cat((t["means3D"], torch.ones(P_GAUSS, 1, device=dev)), dim=1)
     dpix = torch.ones((3, H, W), device=dev) * GRAD_SCALE
 
     def compute_Hessian(rel_w2c):
+        pts = params["means3D"]
+        pts4 = torch.cat((pts, torch.ones(pts.shape[0], 1, device=dev)), dim=1)          # gaussian.py:1523-1527
         tp = (rel_w2c @ pts4.T).T[:, :3].contiguous()
+        rot = F.normalize(params["unnorm_rotations"])                                      # :1529
+        op = torch.sigmoid(params["logit_opacities"])                                      # :1530
+        scl = torch.exp(params["log_scales"])                                              # :1531-1533
         R, color, radii, geom, binning, img, depth = ref_C.rasterize_gaussians(
-            bg, tp, t["rgb_colors"], t["opacities"], t["scales"], t["rotations"], 1.0, e, view, proj, rs["tanfovx"],
+            bg, tp, params["rgb_colors"], op, scl, rot, 1.0, e, view, proj, rs["tanfovx"],
             rs["tanfovy"], H, W, e, 0, campos, False)
-        g = ref_C.rasterize_gaussians_backward(bg, tp, radii, t["rgb_colors"], t["scales"], t["rotations"], 1.0, e, view,
+        g = ref_C.rasterize_gaussians_backward(bg, tp, radii, params["rgb_colors"], scl, rot, 1.0, e, view,
                                                proj, rs["tanfovx"], rs["tanfovy"], dpix, e, 0, campos, geom, R, binning,
                                                img, 2)
         vis_count = int((radii > 0).sum().item())   # gaussian.py:1552
@@ -392,6 +473,7 @@ def run_reference(args):
     H_train = sum(compute_Hessian(w)[0] for w in kf)
     H_inv = torch.reciprocal(H_train + LAMBDA)
     c2w = torch.from_numpy(synth.make_poses(K_CAND, seed=synth.SEED_POSES)).to(dev)
+    flush = torch.empty((256 << 20,), dtype=torch.uint8, device=dev)
 
     def pose_eval(poses):
         out = []
@@ -401,34 +483,41 @@ def run_reference(args):
             out.append(torch.sum(cur_H * H_inv).item())
         return out
 
-    # bounded sample: as many of the 256 candidates per step as keep one step under ~2 s
+    # all 256 candidates per step unless that would take the run past a few minutes (then a bounded sample, said so)
     torch.cuda.synchronize()
     t0 = time.perf_counter(); pose_eval(c2w[:4]); torch.cuda.synchronize()
     per_view = (time.perf_counter() - t0) / 4
-    sample = int(max(8, min(K_CAND, 2.0 / max(per_view, 1e-6))))
+    budget_s = 150.0
+    total_steps = args.steps + max(args.warmup, 3)
+    sample = K_CAND if per_view * K_CAND * total_steps <= budget_s else int(max(8, min(K_CAND, budget_s / total_steps / max(per_view, 1e-6))))
     for _ in range(max(args.warmup, 3)):
         pose_eval(c2w[:sample])
     torch.cuda.synchronize()
     sampler = ClockSampler(torch.cuda.current_device()); sampler.start()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
+    ms = 0.0
     for _ in range(args.steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
         scores = pose_eval(c2w[:sample])
-    b.record(); b.synchronize()
-    ms = a.elapsed_time(b)
+        b.record(); b.synchronize()
+        ms += a.elapsed_time(b)
     clocks = sampler.stop()
     value = sample * args.steps / (ms * 1e-3)
-    desc = f"first {sample} of the 256 candidate poses per step, same 500k-Gaussian map"
+    desc = (f"all {K_CAND} candidate poses per step" if sample == K_CAND else
+            f"first {sample} of the {K_CAND} candidate poses per step") + ", same 500k-Gaussian map"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg3: EIG scoring, 500k Gaussians x 256 candidate poses at 256x256, C_H=4, lambda=0.1",
-                   "sample": desc, "device": "reference CUDA extension rebuilt for sm_100a on one B200, driven by the "
-                                             "reference's per-pose Python loop"},
+        "config": workload_config(),
+        "notes": {"sample": desc, "device": "reference CUDA extension rebuilt for sm_100a on one B200, driven by the "
+                                            "reference's per-pose Python loop on the raw parameters"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference", "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "clocks": clocks, "argmax": int(np.argmax(scores)), "requested_gpus": world}))
+        "clocks": clocks, "argmax": int(np.argmax(scores)), "candidates_scored_per_step": sample,
+        "requested_gpus": world}))
 
 
 def main():

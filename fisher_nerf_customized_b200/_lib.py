@@ -56,6 +56,8 @@ SIGNATURES = {
     "fb_hessian_workspace_bytes": (sz, [ci, ci, ci, ci, ll]),
     "fb_score_set_lanes": (ci, [ci]),
     "fb_score_candidates": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, ci, cf, vp, vp, vp, sz, ci, ll, ll, vp]),
+    "fb_score_candidates_sets": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, vp, vp, ci, cf, vp, vp, vp, sz, ci, ll, ll, vp]),
+    "fb_accumulate_hessian_sets": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, ci, cf, vp, vp, vp, vp, sz, ci, ll, vp]),
     "fb_accumulate_hessian": (ci, [C.POINTER(fb_camera), C.POINTER(fb_map), vp, ci, ci, cf, vp, vp, vp, sz, ci, ll, vp]),
     "fb_knn_workspace_bytes": (sz, [ci]),
     "fb_dist2_knn3": (ci, [ci, vp, vp, vp, sz, vp]),

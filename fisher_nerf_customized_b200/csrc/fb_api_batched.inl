@@ -215,6 +215,14 @@ int fb_score_set_lanes(int on) { g_lanes_enabled = on != 0; return FB_OK; }
 int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c, int K, const float* weight, int C_H,
                         float grad_scale, float* scores, int* status_dev, void* workspace, size_t workspace_bytes,
                         int views_per_chunk, long long inst_capacity, long long vis_capacity, void* stream_) {
+    return fb_score_candidates_sets(c, map, w2c, K, weight, nullptr, C_H, grad_scale, scores, status_dev, workspace,
+                                    workspace_bytes, views_per_chunk, inst_capacity, vis_capacity, stream_);
+}
+
+int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float* w2c, int K, const float* weight,
+                             const int* weight_set, int C_H, float grad_scale, float* scores, int* status_dev,
+                             void* workspace, size_t workspace_bytes, int views_per_chunk, long long inst_capacity,
+                             long long vis_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
         c->image_width <= 0 || c->image_height <= 0 || c->image_width > 4080 || c->image_height > 4080 ||
@@ -269,9 +277,9 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
         const float* w2c_k = w2c + (size_t)k0 * 16;
         const dim3 ps_grid((P + FB_PS_THREADS - 1) / FB_PS_THREADS, min(FB_PS_SPLIT, (Vc + FB_PS_VG - 1) / FB_PS_VG));
         if (C_H == 4)
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<4><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<4>), st>>>(gi, cam, w2c_k, b, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<4><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<4>), st>>>(gi, cam, w2c_k, b, weight, weight_set ? weight_set + k0 : nullptr); }
         else
-            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight); }
+            { FB_PROF(FB_K_PREPROCESS); k_preprocess_score<11><<<ps_grid, FB_PS_THREADS, sizeof(PSmem<11>), st>>>(gi, cam, w2c_k, b, weight, weight_set ? weight_set + k0 : nullptr); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<Vc, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();
@@ -296,6 +304,13 @@ int fb_score_candidates(const fb_camera* c, const fb_map* map, const float* w2c,
 int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2c, int K, int C_H, float grad_scale,
                           float* H_out, int* status_dev, void* workspace, size_t workspace_bytes, int views_per_chunk,
                           long long inst_capacity, void* stream_) {
+    return fb_accumulate_hessian_sets(c, map, w2c, K, C_H, grad_scale, H_out, nullptr, status_dev, workspace,
+                                      workspace_bytes, views_per_chunk, inst_capacity, stream_);
+}
+
+int fb_accumulate_hessian_sets(const fb_camera* c, const fb_map* map, const float* w2c, int K, int C_H, float grad_scale,
+                               float* H_out, const int* out_set, int* status_dev, void* workspace, size_t workspace_bytes,
+                               int views_per_chunk, long long inst_capacity, void* stream_) {
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !map || K < 0 || (C_H != 4 && C_H != 11) || views_per_chunk <= 0 || views_per_chunk > 64 ||
         c->image_width <= 0 || c->image_height <= 0 || c->image_width > 4080 || c->image_height > 4080 ||
@@ -319,7 +334,7 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
     const int V = views_per_chunk;
     float* mom = (float*)(ws + L.mom);     // [V][P][16] floats
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st));
-    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)V * P * FB_NACC * 4, st));     // k_expand_H clears the rows it consumes
+    FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)(K < V ? K : V) * P * FB_NACC * 4, st));   // k_expand_H clears the rows it consumes
     FB_CUDA(cudaMemsetAsync(ws + L.tile_count, 0, (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE, st));
     GaussIn gi = map_in(map);
     // V keyframes per launch sequence: a single 256x256 view is 256 CTAs, less than two per SM
@@ -339,8 +354,9 @@ int fb_accumulate_hessian(const fb_camera* c, const fb_map* map, const float* w2
         { FB_PROF(FB_K_BWD_TILES); k_tile_hessian<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
               b, cam, map->colors, grad_scale, mom); }
         FB_LAUNCH_CHECK();
-        if (C_H == 4) { FB_PROF(FB_K_EXPAND); k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }
-        else { FB_PROF(FB_K_EXPAND); k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out); }
+        const int* set_k = out_set ? out_set + k0 : nullptr;
+        if (C_H == 4) { FB_PROF(FB_K_EXPAND); k_expand_H<4><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out, set_k); }
+        else { FB_PROF(FB_K_EXPAND); k_expand_H<11><<<(P + 127) / 128, 128, 0, st>>>(b, gi, cam, w2c_k, mom, H_out, set_k); }
         FB_LAUNCH_CHECK();
     }
     return FB_OK;

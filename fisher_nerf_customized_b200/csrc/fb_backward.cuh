@@ -169,7 +169,11 @@ __global__ void __launch_bounds__(128) k_expand_grads(int P, GaussIn g, Cam cam,
 // after use so the buffer is all-zero again for the next batch.  w2c: V row-major 4x4 matrices.
 template <int CH>
 __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam, const float* __restrict__ w2c_all,
-                                                 float* __restrict__ mom_all, float* __restrict__ H_out) {
+                                                 float* __restrict__ mom_all, float* __restrict__ H_out,
+                                                 const int* __restrict__ out_set) {
+    // out_set (optional): the term of view v is added to H_out[out_set[v]] of a [sets][P][CH] array (path evaluation:
+    // one running Hessian per path); NULL: every view goes to the one [P][CH] tensor.  Consecutive views of one set are
+    // summed in registers in view order and added once, as before.
     const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (unsigned)bins.P) return;
     constexpr int NOUT = (CH == 11) ? 10 : 3;
@@ -177,8 +181,21 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
     double Hop = 0.0;
 #pragma unroll
     for (int k = 0; k < NOUT; ++k) Hk[k] = 0.0;
-    bool any = false;
+    bool any = false, pending = false;
+    int cur_set = 0;
     float3 p, sc; float4 q; float cov6[6]; SRCtx sr;
+    auto flush = [&]() {
+        float* H = H_out + ((size_t)cur_set * bins.P + idx) * CH;
+#pragma unroll
+        for (int k = 0; k < NOUT; ++k) {
+            const int c = (k < 3) ? k : k + 1;
+            H[c] += (float)Hk[k];
+            Hk[k] = 0.0;
+        }
+        H[3] += (float)Hop;
+        Hop = 0.0;
+        pending = false;
+    };
     for (int v = 0; v < bins.V; ++v) {
         float acc[FB_NACC];
         float4* row = reinterpret_cast<float4*>(mom_all + ((size_t)v * bins.P + idx) * FB_NACC);
@@ -192,6 +209,10 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
         if (!nz) continue;
 #pragma unroll
         for (int k = 0; k < 4; ++k) row[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int set = out_set ? out_set[v] : 0;
+        if (pending && set != cur_set) flush();
+        cur_set = set;
+        pending = true;
         if (!any) {
             any = true;
             p = make_float3(g.means3D[3 * idx], g.means3D[3 * idx + 1], g.means3D[3 * idx + 2]);
@@ -235,14 +256,7 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
         }
         Hop += (double)(acc[0] / (r.b.w * r.b.w));          // batched record layout: opacity in b.w
     }
-    if (!any) return;
-    float* H = H_out + (size_t)idx * CH;
-#pragma unroll
-    for (int k = 0; k < NOUT; ++k) {
-        const int c = (k < 3) ? k : k + 1;
-        H[c] += (float)Hk[k];
-    }
-    H[3] += (float)Hop;
+    if (pending) flush();
 }
 
 }  // namespace fb

@@ -294,7 +294,10 @@ template <int CH>
 #define FB_PS_MINB 3
 #endif
 __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
-                                                                    Bins bins, const float* __restrict__ weight) {
+                                                                    Bins bins, const float* __restrict__ weight,
+                                                                    const int* __restrict__ weight_set) {
+    // weight_set (optional): view v scores against weight tensor weight_set[v] of a [sets][P][CH] array (path
+    // evaluation: every path carries its own running Hessian); NULL: one tensor for all views, staged in shared memory
     extern __shared__ __align__(16) unsigned char ps_raw[];
     PSmem<CH>& S = *reinterpret_cast<PSmem<CH>*>(ps_raw);
     const int P = bins.P, V = bins.V;
@@ -401,8 +404,14 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             const SRCtx sr = make_sr(make_float3(S.sc[0][gi], S.sc[1][gi], S.sc[2][gi]), cam.scale_modifier,
                                      make_float4(S.q[0][gi], S.q[1][gi], S.q[2][gi], S.q[3][gi]));
             float wv[CH];
+            if (weight_set == nullptr) {
 #pragma unroll
-            for (int k = 0; k < CH; ++k) wv[k] = S.w[k][gi];
+                for (int k = 0; k < CH; ++k) wv[k] = S.w[k][gi];
+            } else {
+                const float* wsrc = weight + ((size_t)weight_set[v0 + vv] * P + (size_t)blockIdx.x * FB_PS_THREADS + gi) * CH;
+#pragma unroll
+                for (int k = 0; k < CH; ++k) wv[k] = wsrc[k];
+            }
             float coef[13];
             score_coefs<CH>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
             float4* rb = bins.recB + ((size_t)(v0 + vv) * vcap + slot) * 5;

@@ -227,20 +227,30 @@ class FisherScorer:
         _lib.check(st[0], fn_name)
 
     @torch.no_grad()
-    def score_candidates(self, gmap: GaussianMap, w2c, H_train_inv, sync=True, map_order=False):
+    def score_candidates(self, gmap: GaussianMap, w2c, H_train_inv, sync=True, map_order=False, weight_set=None):
         """scores[k] = sum(H_k * H_train_inv), H_k the Fisher diagonal of pose k (gaussian.py:1362-1370).
         w2c: [K,4,4] world-to-camera (already inverted).  Returns a CUDA float tensor [K].
         map_order=True: H_train_inv is already in the map's resident order (what compute_H_train(map_order=True)
-        returns), no permutation.  sync=False: no host sync; returns (scores, status tensor), see `_run`."""
+        returns), no permutation.  sync=False: no host sync; returns (scores, status tensor), see `_run`.
+        weight_set (i32 [K]): H_train_inv is [S,P,C_H] (map order) and pose k scores against tensor weight_set[k]."""
         K = w2c.reshape(-1, 4, 4).shape[0]
-        H_train_inv = H_train_inv.reshape(gmap.P, self.C_H)
-        weight = _f32c(H_train_inv if map_order else gmap.to_map_order(H_train_inv))
-        scores = torch.zeros((K,), dtype=torch.float32, device=gmap.means3D.device)
+        dev = gmap.means3D.device
+        if weight_set is not None:
+            assert map_order, "weight sets are given in the map's resident order"
+            weight = _f32c(H_train_inv.reshape(-1, gmap.P, self.C_H))
+            wset = weight_set.to(device=dev, dtype=torch.int32).contiguous()
+            assert wset.numel() == K
+        else:
+            H_train_inv = H_train_inv.reshape(gmap.P, self.C_H)
+            weight = _f32c(H_train_inv if map_order else gmap.to_map_order(H_train_inv))
+            wset = None
+        scores = torch.zeros((K,), dtype=torch.float32, device=dev)
 
         def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
-            return L.fb_score_candidates(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, weight.data_ptr(), self.C_H,
-                                         self.grad_scale, scores.data_ptr(), status.data_ptr(), ws.data_ptr(),
-                                         nbytes, self.V, cap, vcap, _stream())
+            return L.fb_score_candidates_sets(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, weight.data_ptr(),
+                                              None if wset is None else wset.data_ptr(), self.C_H,
+                                              self.grad_scale, scores.data_ptr(), status.data_ptr(), ws.data_ptr(),
+                                              nbytes, self.V, cap, vcap, _stream())
         status = self._run("fb_score_candidates", gmap, w2c, call, sync=sync)
         return scores if sync else (scores, status)
 
@@ -268,6 +278,79 @@ class FisherScorer:
     def compute_Hessian(self, gmap: GaussianMap, rel_w2c):
         """cur_H[P,C_H] for one pose (return_points=True form of the reference's compute_Hessian)."""
         return self.compute_H_train(gmap, rel_w2c.reshape(1, 4, 4))
+
+    @torch.no_grad()
+    def accumulate_hessian_sets(self, gmap: GaussianMap, w2c, H_sets, set_index):
+        """H_sets[set_index[k]] += cur_H(pose k) for all k in one launch sequence (H_sets: [S,P,C_H], map order, updated in
+        place): the `H_train_path = H_train_path + cur_H` of every path of a planning step at once."""
+        dev = gmap.means3D.device
+        assert H_sets.is_contiguous() and H_sets.shape[1:] == (gmap.P, self.C_H)
+        sets = set_index.to(device=dev, dtype=torch.int32).contiguous()
+
+        def call(L, cam, m, w2c_t, K_, status, ws, nbytes, cap, vcap):
+            # (a repeat after a capacity overflow is safe: an overflowing chunk adds nothing)
+            return L.fb_accumulate_hessian_sets(C.byref(cam), C.byref(m), w2c_t.data_ptr(), K_, self.C_H, self.grad_scale,
+                                                H_sets.data_ptr(), sets.data_ptr(), status.data_ptr(), ws.data_ptr(), nbytes,
+                                                self.V, cap, _stream())
+        self._run("fb_accumulate_hessian", gmap, w2c, call)
+        return H_sets
+
+    @torch.no_grad()
+    def plan_best_path(self, gmap: GaussianMap, paths_w2c, final_EIGs, H_train, H_reg_lambda=0.1, acc_H_train_every=5,
+                       path_pose_weight=0.2, path_point_weight=1.0, path_end_weight=1.0, max_paths=21,
+                       object_variant=False):
+        """The path loop of plan_best_path (tester_gaussians_navigation.py:1664-1721) / path_evaluation (:1899-1973) for
+        all candidate paths at once.  paths_w2c: list of [L_p,4,4] world-to-camera poses, one per action of path p (the
+        caller's compute_next_campos + np.linalg.inv, :1686-1687); final_EIGs: the global goals' scores; H_train [P,C_H]
+        in the caller's order.  Reference arithmetic, per path (only the first 21 paths are looked at, :1669-1672):
+            step i = 1..L:  pose_EIG = log det(pose_H) with pose_H = I (compute_Hessian returns eye(6), gaussian.py:1570)
+                            total += path_pose_weight * pose_EIG
+                            if (i + 1) % acc_H_train_every == 0:  total += path_point_weight * log sum(cur_H / (H_path + lambda));
+                                                                  H_path += cur_H
+            total = total / L + path_end_weight * final_EIG   if path_end_weight > 0 else (total + final_EIG) / L
+        (object_variant: point_EIG is overwritten with 0 and the end rule is total + object_path_end_weight * final_EIG,
+        :1929-1960; pass that weight as path_end_weight.)  The point term of a non-accumulating step is computed and
+        dropped by the reference; here it is never computed.  All paths' j-th accumulation poses are ONE
+        fb_score_candidates_sets + ONE fb_accumulate_hessian_sets launch sequence (every path scores against, and adds
+        to, its own running Hessian): L/acc levels instead of sum(L_p) per-pose Hessians with a host sync each.
+        Returns (total_path_EIGs [n] list of floats, best index or None, point_EIG [n, levels] CPU tensor, NaN-padded)."""
+        dev = gmap.means3D.device
+        paths = [torch.as_tensor(p, dtype=torch.float32).reshape(-1, 4, 4) for p in list(paths_w2c)[:max_paths]]
+        n = len(paths)
+        acc = int(acc_H_train_every)
+        steps = [[i for i in range(1, int(p.shape[0]) + 1) if (i + 1) % acc == 0] for p in paths]     # 1-based, :1703
+        levels = max((len(s) for s in steps), default=0)
+        point = torch.full((n, max(levels, 1)), float("nan"), dtype=torch.float32)
+        totals = [0.0] * n
+        if not object_variant and levels > 0 and n > 0:
+            S = gmap.to_map_order(H_train.reshape(gmap.P, self.C_H)).unsqueeze(0).repeat(n, 1, 1).contiguous()
+            for j in range(levels):
+                active = [p for p in range(n) if len(steps[p]) > j]
+                poses = torch.stack([paths[p][steps[p][j] - 1] for p in active]).to(dev)
+                sets = torch.tensor(active, dtype=torch.int32, device=dev)
+                W = torch.reciprocal(S + H_reg_lambda)
+                sc = self.score_candidates(gmap, poses, W, map_order=True, weight_set=sets)
+                e = torch.log(sc).cpu()                               # -inf if nothing is visible, as the reference
+                for a, p in enumerate(active):
+                    point[p, j] = e[a]
+                    totals[p] += path_point_weight * float(e[a])
+                if j + 1 < levels:
+                    self.accumulate_hessian_sets(gmap, poses, S, sets)
+        out = []
+        for p in range(n):
+            L = int(paths[p].shape[0])
+            total = totals[p] + path_pose_weight * 0.0 * L           # log det(eye(6)) = 0 at every step
+            fe = float(final_EIGs[p])
+            if object_variant:
+                total = total + path_end_weight * fe if path_end_weight > 0 else (total + fe) / max(L, 1)
+            else:
+                total = total / L + path_end_weight * fe if path_end_weight > 0 else (total + fe) / L
+            out.append(total)
+        best, best_val = None, -1.0                                   # best_path_EIG = -1., :1652 / :1891
+        for p, v in enumerate(out):
+            if v > best_val:
+                best, best_val = p, v
+        return out, best, point
 
     @torch.no_grad()
     def path_point_eig(self, gmap: GaussianMap, path_w2c, H_train, H_reg_lambda=0.1, acc_H_train_every=5):

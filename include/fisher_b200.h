@@ -246,6 +246,17 @@ int fb_score_candidates(const fb_camera* cam, const fb_map* map,
                         int views_per_chunk, long long inst_capacity, long long vis_capacity,
                         void* stream);
 
+/* Path evaluation (plan_best_path / path_evaluation, tester_gaussians_navigation.py:1659-1727, 1886-1975): every
+ * candidate path carries its own running Hessian, so the poses of one launch score against different weights.
+ * `weight` is [sets][P][C_H]; pose k uses tensor weight_set[k] (i32 [K], device; NULL = tensor 0 for all). */
+int fb_score_candidates_sets(const fb_camera* cam, const fb_map* map,
+                             const float* w2c, int K,
+                             const float* weight, const int* weight_set, int C_H, float grad_scale,
+                             float* scores, int* status_dev,
+                             void* workspace, size_t workspace_bytes,
+                             int views_per_chunk, long long inst_capacity, long long vis_capacity,
+                             void* stream);
+
 /* H_out[g,c] += sum_k H_k[g,c]   (compute_H_train, gaussian.py:1338-1348).
  * H_out is [P,C_H], caller-initialised.  Keyframes are processed views_per_chunk (<= 64) per launch
  * sequence; the per-Gaussian sum over the views of a chunk is formed in a fixed order (no atomics on H_out).
@@ -257,6 +268,16 @@ int fb_accumulate_hessian(const fb_camera* cam, const fb_map* map,
                           void* workspace, size_t workspace_bytes,
                           int views_per_chunk, long long inst_capacity,
                           void* stream);
+
+/* As fb_accumulate_hessian, with H_out = [sets][P][C_H] and the term of pose k added to tensor out_set[k]
+ * (i32 [K], device; NULL = tensor 0): the per-path `H_train_path + cur_H` of path evaluation for all paths at once. */
+int fb_accumulate_hessian_sets(const fb_camera* cam, const fb_map* map,
+                               const float* w2c, int K,
+                               int C_H, float grad_scale,
+                               float* H_out, const int* out_set, int* status_dev,
+                               void* workspace, size_t workspace_bytes,
+                               int views_per_chunk, long long inst_capacity,
+                               void* stream);
 
 /* ---- stage 5 ------------------------------------------------------------- */
 

@@ -325,3 +325,68 @@ def test_chunk_lanes_do_not_change_scores(cuda, C_H):
     assert np.array_equal(out[1][0], out[2][0]) and np.array_equal(out[2][0], out[2][1])
     assert out[1][2:] == out[2][2:]
     assert np.all(out[2][0] > 0)
+
+
+def test_plan_best_path_vs_reference_extension_loop(cuda):
+    """all candidate paths of a planning step in one launch sequence per accumulation level, against the
+    reference's loop (tester_gaussians_navigation.py:1664-1721) run pose by pose through the UNMODIFIED reference
+    extension: per-path totals within rtol 1e-3 (they are sums of logs), the same best path."""
+    import torch
+    from oracle import build_ref
+    ref_C = build_ref.import_ref("ref_dgr")
+    if ref_C is None:
+        pytest.skip("oracle/_ref/ref_dgr not built")
+    W = H = 128
+    P, acc, lam = 40000, 5, 0.1
+    sc = synth.activate(synth.make_scene(P, seed=13, focal=64.0))
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    gmap = _gmap(cuda, torch, sc)
+    lengths = [14, 9, 4, 11, 19, 5]                      # 2, 1, 0, 2, 3, 1 accumulation levels
+    all_poses = synth.w2c_from_c2w(synth.make_poses(sum(lengths) + 3, seed=17))
+    kf, rest = all_poses[:3], all_poses[3:]
+    paths, o = [], 0
+    for L in lengths:
+        paths.append(rest[o:o + L]); o += L
+    final_EIGs = [0.3, 1.7, 0.9, 0.2, 1.1, 0.5]
+    e = torch.Tensor([])
+    pts4 = torch.cat((t["means3D"], torch.ones(P, 1, device="cuda")), dim=1)
+    dpix = torch.full((3, H, W), 1e-3, device="cuda")
+
+    def ref_H(w2c):
+        tp = (torch.from_numpy(w2c).cuda() @ pts4.T).T[:, :3].contiguous()
+        R, color, radii, geom, binning, img, depth = ref_C.rasterize_gaussians(
+            rs.bg, tp, t["rgb_colors"], t["opacities"], t["scales"], t["rotations"], 1.0, e, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, H, W, e, 0, rs.campos, False)
+        g = ref_C.rasterize_gaussians_backward(rs.bg, tp, radii, t["rgb_colors"], t["scales"], t["rotations"], 1.0, e,
+                                               rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, dpix, e, 0,
+                                               rs.campos, geom, R, binning, img, 2)
+        return torch.cat([g[3], g[2].reshape(-1, 1)], dim=1), torch.eye(6, device="cuda")
+
+    H_train = sum(ref_H(w)[0] for w in kf)
+    pose_w, point_w, end_w = 0.2, 1.0, 1.0
+    want = []
+    for path, fe in zip(paths, final_EIGs):              # the reference's loop, statement by statement
+        H_path = H_train.clone()
+        total, curr_action = 0, []
+        for w2c in path:
+            cur_H, pose_H = ref_H(w2c)
+            H_inv_path = torch.reciprocal(H_path + lam)
+            point_EIG = torch.log(torch.sum(cur_H * H_inv_path))
+            pose_EIG = torch.log(torch.linalg.det(pose_H))
+            curr_action.append(1)
+            total += pose_w * pose_EIG.item()
+            if (len(curr_action) + 1) % acc == 0:
+                total += point_w * point_EIG.item()
+                H_path = H_path + cur_H
+        want.append(total / len(curr_action) + end_w * fe)
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=8)
+    got, best, point = scorer.plan_best_path(gmap, paths, final_EIGs, H_train, lam, acc, pose_w, point_w, end_w)
+    np.testing.assert_allclose(np.array(got), np.array(want), rtol=1e-3, atol=1e-5)
+    assert best == int(np.argmax(want))
+    assert int(torch.isfinite(point).sum()) == 2 + 1 + 0 + 2 + 3 + 1
+    # the object variant drops the point term (:1929, :1936) and only the end term decides
+    got_o, best_o, _ = scorer.plan_best_path(gmap, paths, final_EIGs, H_train, lam, acc, pose_w, point_w, end_w,
+                                             object_variant=True)
+    np.testing.assert_allclose(np.array(got_o), np.array(final_EIGs), rtol=1e-6)
+    assert best_o == 1

@@ -14,3 +14,4 @@ from .visibility import count_visible_points, count_visible_batch  # noqa: F401
 from .scoring import FisherScorer, GaussianMap, setup_camera  # noqa: F401
 from .parallel import ShardedScorer, shard_bounds, round_robin  # noqa: F401
 from .mapupdate import ResidentParams, get_pointcloud, initialize_new_params  # noqa: F401
+from .mapnbr import OccupancyMap, count_gaussians_vs_mask  # noqa: F401

@@ -10,6 +10,7 @@
 #include "fb_stage5.cuh"
 #include "fb_blocks.cuh"
 #include "fb_mapupdate.cuh"
+#include "fb_mapnbr.cuh"
 #include <limits.h>
 #include <stdlib.h>
 #include <string.h>

@@ -478,4 +478,53 @@ int fb_unproject_append(int width, int height, int downsample, const float* colo
     return FB_OK;
 }
 
+size_t fb_occ_workspace_bytes(int gx, int gz) {
+    const size_t n = (size_t)(gx > 0 ? gx : 1) * (gz > 0 ? gz : 1);
+    return fb::align_up(n * 4, 256) * 2 + fb::align_up(n, 256) + 256;
+}
+
+int fb_occ_update(float* occ_map, int gx, int gz, const float* depth, int width, int height, int downsample,
+                  const float* c2w, const float* intr, const float* planes, const float* map_center, float cell_size,
+                  float height_lower, float height_upper, float far_distance, int* cam_cell, void* workspace,
+                  size_t workspace_bytes, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!occ_map || gx <= 0 || gz <= 0 || !depth || width <= 0 || height <= 0 || downsample <= 0 || !c2w || !intr ||
+        !planes || !map_center || !(cell_size > 0.f) || !workspace) return FB_E_INVALID;
+    if (workspace_bytes < fb_occ_workspace_bytes(gx, gz)) return FB_E_WORKSPACE;
+    const size_t n = (size_t)gx * gz;
+    char* ws = (char*)workspace;
+    OccArgs a;
+    a.occ_map = occ_map; a.gx = gx; a.gz = gz; a.depth = depth; a.W = width; a.H = height; a.ds = downsample;
+    a.c2w = c2w; a.intr = intr; a.planes = planes; a.map_center = map_center;
+    a.cell = cell_size; a.h_lo = height_lower; a.h_hi = height_upper; a.far = far_distance;
+    a.cnt_free = (int*)ws; a.cnt_occ = (int*)(ws + align_up(n * 4, 256));
+    a.canvas = (unsigned char*)(ws + 2 * align_up(n * 4, 256));
+    a.cam_cell = (int*)(ws + 2 * align_up(n * 4, 256) + align_up(n, 256));
+    FB_CUDA(cudaMemsetAsync(ws, 0, 2 * align_up(n * 4, 256) + align_up(n, 256), st));
+    const long long pts = (long long)((width + downsample - 1) / downsample) * ((height + downsample - 1) / downsample) * 11;
+    { FB_PROF(FB_K_MAPUPDATE); k_occ_points<<<(unsigned)((pts + 255) / 256), 256, 0, st>>>(a); }
+    FB_LAUNCH_CHECK();
+    { FB_PROF(FB_K_MAPUPDATE); k_occ_lines<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a); }
+    { FB_PROF(FB_K_MAPUPDATE); k_occ_fuse<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a); }
+    FB_LAUNCH_CHECK();
+    if (cam_cell) FB_CUDA(cudaMemcpyAsync(cam_cell, a.cam_cell, 8, cudaMemcpyDeviceToDevice, st));
+    return FB_OK;
+}
+
+int fb_count_vs_mask(int N, const float* means3D, const float* logit_opacities, const float* w2c, const float* intr,
+                     const uint8_t* mask, int width, int height, float opacity_thresh, uint8_t* code, int* counts,
+                     void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (N < 0 || !counts || width <= 0 || height <= 0) return FB_E_INVALID;
+    FB_CUDA(cudaMemsetAsync(counts, 0, 3 * sizeof(int), st));
+    if (N == 0) return FB_OK;
+    if (!means3D || !logit_opacities || !w2c || !intr || !mask || !code) return FB_E_INVALID;
+    { FB_PROF(FB_K_VISIBLE); k_count_vs_mask<<<(N + 255) / 256, 256, 0, st>>>(N, means3D, logit_opacities, w2c, intr, mask,
+                                                                            width, height, opacity_thresh, code, counts); }
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
 }  // extern "C"

@@ -346,6 +346,31 @@ int fb_unproject_append(int width, int height, int downsample,
                         float* log_scales, int log_scale_cols, float* mean3_sq_dist,
                         void* stream);
 
+/* ---- occupancy grid and masked visibility (planning/astar.py, models/SLAM/gaussian_object.py) ---- */
+
+/* AstarPlanner.update_occ_map (planning/astar.py:202-303) on the device, without its host loop:
+ * occ_map [3,gz,gx] (unknown, occupied, free) is updated in place from one depth image [height,width]:
+ * the 3x3 block around the camera cell is set to 1e3 on the free channel; 10 samples along every pixel's ray
+ * (planes[0..9] * depth) are counted as free and the depth point (planes[10] = 1) as occupied, after the
+ * height filter, per grid cell (what torch.unique(..., return_counts=True) returns); one 8-connected line per
+ * occupied cell to the camera cell marks free space (cv2.line, thickness 1); the three channels are normalised
+ * and added.  c2w (16), intr {fx,fy,cx,cy}, planes (11), map_center (2): device pointers, so the pose never
+ * visits the host.  cam_cell (optional, 2 ints, device): the camera's (x, z) cell, the reference's cam_pos. */
+size_t fb_occ_workspace_bytes(int gx, int gz);
+int fb_occ_update(float* occ_map, int gx, int gz,
+                  const float* depth, int width, int height, int downsample,
+                  const float* c2w, const float* intr, const float* planes, const float* map_center,
+                  float cell_size, float height_lower, float height_upper, float far_distance,
+                  int* cam_cell, void* workspace, size_t workspace_bytes, void* stream);
+
+/* count_gaussians_vs_mask (models/SLAM/gaussian_object.py:359-428): code[i] = 0 if sigmoid(logit_i) < thresh,
+ * 1 if the Gaussian projects inside the mask, 2 if it projects into the image but outside the mask, 3 if it is
+ * active but behind the camera or outside the image; counts = {in, out (codes 2 and 3), active}.
+ * mask: u8 [height,width]; w2c: 16 floats row-major; intr {fx,fy,cx,cy}: device pointers. */
+int fb_count_vs_mask(int N, const float* means3D, const float* logit_opacities,
+                     const float* w2c, const float* intr, const uint8_t* mask, int width, int height,
+                     float opacity_thresh, uint8_t* code, int* counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

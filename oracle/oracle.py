@@ -377,3 +377,106 @@ def initialize_new_params(new_pt_cld, mean3_sq_dist, isotropic=False):
             "unnorm_rotations": np.tile(np.array([1, 0, 0, 0], np.float32), (n, 1)),
             "logit_opacities": np.zeros((n, 1), np.float32),
             "log_scales": np.tile(ls[:, None], (1, 1 if isotropic else 3))}
+
+
+# ---- occupancy update and masked visibility counter (numpy restatements, TEST INFRASTRUCTURE) ----
+def _r32(x):
+    return np.asarray(x, dtype=np.float32)
+
+
+def _affine_f32(m, x, y, z):
+    """fma(m2, z, fma(m1, y, m0 * x)) + m3 in float32: the k-sequential order the CUDA path fixes for `c2w @ p`
+    (float64 evaluation of each fma, rounded once, is the correctly rounded float32 fma for float32 inputs)."""
+    m = np.asarray(m, dtype=np.float32)
+    t = _r32(np.float64(m[0]) * np.float64(x))
+    t = _r32(np.float64(m[1]) * np.float64(y) + np.float64(t))
+    t = _r32(np.float64(m[2]) * np.float64(z) + np.float64(t))
+    return _r32(t + m[3])
+
+
+def cv_line_8(x1, y1, x2, y2):
+    """Pixels of cv2.line(img, (x1, y1), (x2, y2), color, thickness=1, lineType=LINE_8): OpenCV's LineIterator, 8-connected,
+    leftToRight (imgproc/src/drawing.cpp: Line() -> LineIterator(img, pt1, pt2, 8, true)).  OpenCV is not in this image:
+    parity of this part is UNPINNED; the algorithm is restated from the published source."""
+    if x2 < x1:
+        x1, y1, x2, y2 = x2, y2, x1, y1
+    dx, dy = x2 - x1, y2 - y1
+    ystep = -1 if dy < 0 else 1
+    dy = abs(dy)
+    steep = dy > dx
+    major, minor = (dy, dx) if steep else (dx, dy)
+    err, plus, minus = major - 2 * minor, 2 * major, -2 * minor
+    x, y, out = x1, y1, []
+    for _ in range(major + 1):
+        out.append((x, y))
+        m = err < 0
+        err += minus + (plus if m else 0)
+        if steep:
+            y += ystep
+            x += 1 if m else 0
+        else:
+            x += 1
+            y += ystep if m else 0
+    return out
+
+
+def update_occ_map(occ_map, depth, c2w, intr, cell_size, map_center, height_lower, height_upper, far, planes, downsample=1):
+    """AstarPlanner.update_occ_map (planning/astar.py:202-303) on numpy arrays, float32 operation by operation.
+    occ_map [3,gz,gx] is updated in place; returns the camera cell (x, z)."""
+    occ_map_in = occ_map
+    gz, gx = occ_map.shape[1], occ_map.shape[2]
+    c2w = _r32(c2w); mc = _r32(map_center); cell = np.float32(cell_size)
+    fx, fy, cx, cy = (np.float32(v) for v in intr)
+    cam_x = int(_r32(_r32(_r32(c2w[0, 3] - mc[0]) / cell) + np.float32(gx // 2)))
+    cam_z = int(_r32(_r32(_r32(c2w[2, 3] - mc[1]) / cell) + np.float32(gz // 2)))
+    occ_map_in[2, cam_z - 1:cam_z + 2, cam_x - 1:cam_x + 2] = 1e3                      # :214
+    d = _r32(depth).reshape(depth.shape[-2], depth.shape[-1])[::downsample, ::downsample]
+    ys, xs = np.meshgrid(np.arange(0, depth.shape[-2], downsample, dtype=np.float32),
+                         np.arange(0, depth.shape[-1], downsample, dtype=np.float32), indexing="ij")
+    xx, yy = _r32((xs - cx) / fx), _r32((ys - cy) / fy)
+    cnt = np.zeros((2, gz, gx), np.int64)                                               # [free, occupied]
+    for k in range(11):
+        dz = _r32(np.float32(planes[k]) * d)
+        m = (dz > 0) & (dz < np.float32(far))
+        x, y = _r32(xx * dz), _r32(yy * dz)
+        wx = _affine_f32(c2w[0], x, y, dz); wy = _affine_f32(c2w[1], x, y, dz); wz = _affine_f32(c2w[2], x, y, dz)
+        m &= (wy >= np.float32(height_lower)) & (wy <= np.float32(height_upper))
+        bx = _r32(np.floor(_r32(_r32(wx - mc[0]) / cell)) + np.float32((gx - 1) / 2.0)).astype(np.int32).clip(0, gx - 1)
+        bz = _r32(np.floor(_r32(_r32(wz - mc[1]) / cell)) + np.float32((gz - 1) / 2.0)).astype(np.int32).clip(0, gz - 1)
+        np.add.at(cnt[0 if k < 10 else 1], (bz[m], bx[m]), 1)
+    tmp = np.zeros((3, gz, gx), np.float32)
+    tmp[2] = np.where(cnt[0] > 0, _r32(np.float32(0.01) * _r32(cnt[0].astype(np.float32) + np.float32(1e-5))), np.float32(0))
+    tmp[1] = np.where(cnt[1] > 0, _r32(_r32(cnt[1].astype(np.float32) + np.float32(1e-5)) * np.float32(100)), np.float32(0))
+    canvas = np.zeros((gz, gx), bool)
+    cxx, czz = min(gx - 1, max(0, cam_x)), min(gz - 1, max(0, cam_z))
+    for z, x in zip(*np.nonzero(cnt[1])):
+        for (px, pz) in cv_line_8(int(x), int(z), cxx, czz):
+            canvas[pz, px] = True
+    tmp[2][canvas] = 1.0
+    den = _r32(_r32(_r32(tmp[0] + tmp[1]) + tmp[2]) + np.float32(1e-5))
+    occ_map_in += _r32(tmp / den)
+    return cam_x, cam_z
+
+
+def count_gaussians_vs_mask(means3D, logit_opacities, w2c, intr, mask, opacity_thresh=0.01):
+    """models/SLAM/gaussian_object.py:359-428 on numpy arrays (float32, one rounding per torch op).
+    Returns dict(in, out, active, idx_in, idx_out) with the reference's index order."""
+    H, W = mask.shape[-2], mask.shape[-1]
+    lo = _r32(logit_opacities).reshape(-1)
+    alpha = _r32(np.float32(1) / _r32(np.float32(1) + np.exp(-lo, dtype=np.float32)))
+    active = alpha >= np.float32(opacity_thresh)
+    idx_active = np.nonzero(active)[0]
+    X = _r32(means3D)[active]
+    w2c = _r32(w2c)
+    xc = _affine_f32(w2c[0], X[:, 0], X[:, 1], X[:, 2]); yc = _affine_f32(w2c[1], X[:, 0], X[:, 1], X[:, 2])
+    zc = _affine_f32(w2c[2], X[:, 0], X[:, 1], X[:, 2])
+    zz = np.maximum(zc, np.float32(1e-6))
+    fx, fy, cx, cy = (np.float32(v) for v in intr)
+    u = _r32(_r32(fx * _r32(xc / zz)) + cx); v = _r32(_r32(fy * _r32(yc / zz)) + cy)
+    ok = (zc > 0) & (u >= 0) & (u < W) & (v >= 0) & (v < H)
+    iu = np.rint(u[ok]).astype(np.int64).clip(0, W - 1); iv = np.rint(v[ok]).astype(np.int64).clip(0, H - 1)
+    inm = np.asarray(mask, bool).reshape(H, W)[iv, iu]
+    idx_ok = idx_active[ok]
+    idx_in = idx_ok[inm]
+    idx_out = np.concatenate([idx_ok[~inm], idx_active[~ok]])
+    return {"in": int(idx_in.size), "out": int(idx_out.size), "active": int(active.sum()), "idx_in": idx_in, "idx_out": idx_out}

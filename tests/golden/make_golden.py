@@ -10,6 +10,8 @@
   python tests/golden/make_golden.py pointcloud  # in the build container: the reference's get_pointcloud /
                                            # initialize_new_params bodies (models/SLAM/gaussian.py, by AST) on CPU
                                            # torch (`.cuda()` made a no-op) on seeded RGB-D frames
+  python tests/golden/make_golden.py maskcount  # in the build container: the reference's count_gaussians_vs_mask body
+                                           # (models/SLAM/gaussian_object.py:359-428, by AST) on CPU torch
   python tests/golden/make_golden.py cpu   # in the build container: executes the reference's own numpy
                                            # count_visible_points, taken from /root/reference/tester_navigator.py
                                            # by AST (the module itself imports habitat and cannot be imported)
@@ -225,9 +227,39 @@ def pointcloud(out_dir):
         print(name, cld.shape, cld_all.shape, float(msd.min()), float(msd.max()))
 
 
+def mask_inputs(N, H, W, seed):
+    """Seeded Gaussians (means, opacity logits), a pose, intrinsics and an object mask (shared with the tests)."""
+    from tests import common
+    rng = np.random.default_rng(seed)
+    means = np.c_[rng.uniform(-3, 3, N), rng.uniform(-2, 2, N), rng.uniform(-1.0, 6.0, N)].astype(np.float32)
+    logit = rng.normal(-2.0, 3.0, size=(N, 1)).astype(np.float32)
+    w2c = common.look_at_w2c((0.3, -0.1, -0.5), (0.1, 0.0, 2.5))
+    K = np.array([[0.8 * W, 0, W / 2.0], [0, 0.8 * W, H / 2.0], [0, 0, 1]], np.float32)
+    yy, xx = np.mgrid[0:H, 0:W]
+    mask = ((xx - 0.55 * W) ** 2 + (yy - 0.45 * H) ** 2 < (0.3 * H) ** 2) | (rng.random((H, W)) < 0.05)
+    return means, logit, w2c, K, mask
+
+
+MASK_CASES = [("mask_a", 20000, 48, 64, 401), ("mask_b", 7, 16, 16, 402)]
+
+
+def maskcount(out_dir):
+    import torch
+    fn, = _reference_methods(["count_gaussians_vs_mask"])
+    for name, N, H, W, seed in MASK_CASES:
+        means, logit, w2c, K, mask = mask_inputs(N, H, W, seed)
+        params = {"means3D": torch.from_numpy(means), "logit_opacities": torch.from_numpy(logit)}
+        r = fn(params, torch.from_numpy(w2c), torch.from_numpy(K), torch.from_numpy(mask), 0.01)
+        np.savez_compressed(os.path.join(out_dir, name + ".npz"), n_in=r["in"], n_out=r["out"], active=r["active"],
+                            idx_in=r["idx_in"].numpy(), idx_out=r["idx_out"].numpy(), N=N, H=H, W=W, seed=seed)
+        print(name, r["in"], r["out"], r["active"])
+
+
 if __name__ == "__main__":
     mode = sys.argv[1]
-    if mode == "pointcloud":
+    if mode == "maskcount":
+        maskcount(HERE)
+    elif mode == "pointcloud":
         pointcloud(HERE)
     elif mode == "blocks":
         blocks(HERE)

@@ -269,3 +269,50 @@ def test_get_pointcloud_matches_reference_golden(oracle, name):
     for k, v in new.items():
         assert v.shape == g["new_" + k].shape, k
         np.testing.assert_allclose(v, g["new_" + k], rtol=2e-6, atol=2e-6, err_msg=k)
+
+
+def test_count_gaussians_vs_mask_oracle_matches_reference_body():
+    """oracle.count_gaussians_vs_mask against fixtures produced by the reference's own function body
+    (models/SLAM/gaussian_object.py:359-428, executed on CPU torch by tests/golden/make_golden.py maskcount)."""
+    from oracle import oracle as O
+    from tests.golden import make_golden as G
+    for name, N, H, W, seed in G.MASK_CASES:
+        means, logit, w2c, K, mask = G.mask_inputs(N, H, W, seed)
+        z = np.load(os.path.join(os.path.dirname(G.__file__), name + ".npz"))
+        r = O.count_gaussians_vs_mask(means, logit, w2c, (K[0, 0], K[1, 1], K[0, 2], K[1, 2]), mask, 0.01)
+        assert (r["in"], r["out"], r["active"]) == (int(z["n_in"]), int(z["n_out"]), int(z["active"]))
+        np.testing.assert_array_equal(r["idx_in"], z["idx_in"])
+        np.testing.assert_array_equal(r["idx_out"], z["idx_out"])
+
+
+def test_cv_line_restatement_properties():
+    """The 8-connected Bresenham restated from OpenCV's LineIterator (parity unpinned: no OpenCV in this image):
+    max(|dx|, |dy|) + 1 pixels, both endpoints, 8-connected, one pixel per major-axis step, and -- because Line()
+    iterates left to right -- the same pixel set whichever endpoint comes first."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(5)
+    for _ in range(200):
+        x1, y1, x2, y2 = (int(v) for v in rng.integers(0, 40, 4))
+        a, b = O.cv_line_8(x1, y1, x2, y2), O.cv_line_8(x2, y2, x1, y1)
+        assert len(a) == max(abs(x2 - x1), abs(y2 - y1)) + 1
+        assert (x1, y1) in a and (x2, y2) in a and set(a) == set(b)
+        for (p, q) in zip(a[:-1], a[1:]):
+            assert max(abs(p[0] - q[0]), abs(p[1] - q[1])) == 1
+    assert O.cv_line_8(0, 0, 5, 2) == [(0, 0), (1, 0), (2, 1), (3, 1), (4, 2), (5, 2)]
+
+
+def test_update_occ_map_oracle_basic():
+    """A wall 2 m in front of the camera: the wall's cells become occupied, the cells between camera and wall free,
+    cells behind the wall stay unknown; the three channels of an updated cell add up to 1 (+ what was there)."""
+    from oracle import oracle as O
+    g = 64
+    occ = np.zeros((3, g, g), np.float32); occ[0] = 1
+    depth = np.full((1, 32, 32), 2.0, np.float32)
+    planes = np.linspace(1e-3, 0.95, 11, dtype=np.float32); planes[-1] = 1.0
+    cam = O.update_occ_map(occ, depth, np.eye(4, dtype=np.float32), (32.0, 32.0, 16.0, 16.0), 0.1, (0.0, 0.0), -0.5, 0.5,
+                           5.0, planes)
+    assert cam == (32, 32)
+    wall_z = int(np.floor(2.0 / 0.1) + 31.5)
+    assert occ[1, wall_z, 32] > 0.9 and occ[2, wall_z - 5, 32] > 0.9 and occ[1, wall_z - 5, 32] == 0
+    assert occ[0, wall_z + 3, 32] == 1 and occ[1, wall_z + 3, 32] == 0 and occ[2, wall_z + 3, 32] == 0
+    assert occ[2, 32, 32] >= 1e3

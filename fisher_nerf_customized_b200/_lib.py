@@ -50,6 +50,10 @@ SIGNATURES = {
                                       ci, vp, vp, vp]),
     "fb_raster_backward": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, vp, sz, vp, sz, vp, sz, vp, sz, ci,
                                 vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "fb_raster_forward_render2": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, vp, sz, vp, sz, vp, sz, vp, sz,
+                                       ci, vp, vp, vp, vp]),
+    "fb_raster_backward2": (ci, [C.POINTER(fb_camera), C.POINTER(fb_gaussians), vp, vp, vp, sz, vp, sz, vp, sz, vp, sz, ci,
+                                 vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "fb_mark_visible": (ci, [ci, vp, C.POINTER(cf), C.POINTER(cf), vp, vp]),
     "fb_debug_export": (ci, [C.POINTER(fb_camera), ci, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "fb_score_workspace_bytes": (sz, [ci, ci, ci, ci, ll, ll]),

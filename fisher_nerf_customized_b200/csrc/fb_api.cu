@@ -178,9 +178,18 @@ int fb_raster_forward_bin(const fb_camera* c, const fb_gaussians* g, void* geom,
 int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* geom, size_t geom_bytes, void* image,
                              size_t image_bytes, void* inst, size_t inst_bytes, void* scratch, size_t scratch_bytes,
                              int num_rendered, float* out_color, float* out_depth, void* stream_) {
+    return fb_raster_forward_render2(c, g, nullptr, geom, geom_bytes, image, image_bytes, inst, inst_bytes, scratch,
+                                     scratch_bytes, num_rendered, out_color, nullptr, out_depth, stream_);
+}
+
+int fb_raster_forward_render2(const fb_camera* c, const fb_gaussians* g, const float* extra_colors, void* geom,
+                              size_t geom_bytes, void* image, size_t image_bytes, void* inst, size_t inst_bytes,
+                              void* scratch, size_t scratch_bytes, int num_rendered, float* out_color, float* out_extra,
+                              float* out_depth, void* stream_) {
     (void)scratch; (void)scratch_bytes; (void)geom_bytes; (void)image_bytes;
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !g || !out_color || !out_depth || num_rendered < 0) return FB_E_INVALID;
+    if ((extra_colors == nullptr) != (out_extra == nullptr)) return FB_E_INVALID;
     const int P = g->P;
     if (P == 0) return FB_OK;
     if (!geom || !image || !inst) return FB_E_INVALID;
@@ -204,9 +213,14 @@ int fb_raster_forward_render(const fb_camera* c, const fb_gaussians* g, void* ge
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);
 #if FB_DROPIN_WARP
-    { FB_PROF(FB_K_RENDER); k_render_warp<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
-        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
+    if (extra_colors)
+        { FB_PROF(FB_K_RENDER); k_render_warp<1><<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
+            b, cam, feat, extra_colors, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_extra, out_depth); }
+    else
+        { FB_PROF(FB_K_RENDER); k_render_warp<0><<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
+            b, cam, feat, nullptr, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, nullptr, out_depth); }
 #else
+    if (extra_colors) return FB_E_INVALID;
     b.tile_order = nullptr;
     { FB_PROF(FB_K_RENDER); k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
         b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
@@ -220,9 +234,22 @@ int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* rad
                        size_t scratch_bytes, int num_rendered, const float* dL_dpix, int power, float* dL_dmeans2D,
                        float* dL_dconic, float* dL_dopacity, float* dL_dcolors, float* dL_dmeans3D, float* dL_dcov3D,
                        float* dL_dsh, float* dL_dscales, float* dL_drotations, void* stream_) {
+    return fb_raster_backward2(c, g, nullptr, radii, geom, geom_bytes, image, image_bytes, inst, inst_bytes, scratch,
+                               scratch_bytes, num_rendered, dL_dpix, nullptr, power, dL_dmeans2D, dL_dconic, dL_dopacity,
+                               dL_dcolors, nullptr, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, stream_);
+}
+
+int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* extra_colors, const int* radii,
+                        const void* geom, size_t geom_bytes, const void* image, size_t image_bytes, const void* inst,
+                        size_t inst_bytes, void* scratch, size_t scratch_bytes, int num_rendered, const float* dL_dpix,
+                        const float* dL_dextra, int power, float* dL_dmeans2D, float* dL_dconic, float* dL_dopacity,
+                        float* dL_dcolors, float* dL_dextra_colors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                        float* dL_dscales, float* dL_drotations, void* stream_) {
     (void)geom_bytes; (void)image_bytes; (void)inst_bytes; (void)dL_dsh;
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !dL_dpix) return FB_E_INVALID;
+    if ((extra_colors == nullptr) != (dL_dextra == nullptr)) return FB_E_INVALID;
+    if (extra_colors && (power != 1 || !FB_DROPIN_WARP)) return FB_E_INVALID;   // the two renders' gradients add only for power 1
     int rc = check_gauss(g);
     if (rc) return rc;
     const int P = g->P;
@@ -246,10 +273,10 @@ int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* rad
     b.tile_order = nullptr;
     dim3 grid(cam.tiles_x, cam.tiles_y);
 #endif
-    GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations};
+    GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations, dL_dextra_colors};
     if (power == 2) {
 #if FB_DROPIN_WARP
-        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<true><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<true, 0><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, nullptr, fT, nc, dL_dpix, nullptr, mom); }
 #else
         { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
 #endif
@@ -257,7 +284,14 @@ int fb_raster_backward(const fb_camera* c, const fb_gaussians* g, const int* rad
         { FB_PROF(FB_K_EXPAND); k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     } else {
 #if FB_DROPIN_WARP
-        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
+        if (extra_colors) {
+            { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false, 1><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, extra_colors, fT, nc, dL_dpix, dL_dextra, mom); }
+            FB_LAUNCH_CHECK();
+            { FB_PROF(FB_K_EXPAND); k_expand_grads<false, true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
+            FB_LAUNCH_CHECK();
+            return FB_OK;
+        }
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false, 0><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, nullptr, fT, nc, dL_dpix, nullptr, mom); }
 #else
         { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
 #endif

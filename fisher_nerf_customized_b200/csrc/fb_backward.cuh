@@ -67,10 +67,13 @@ struct GradOut {
     float* dcov3D;     // [P,6]
     float* dscales;    // [P,3]
     float* drots;      // [P,4]
+    float* dextra;     // [P,3]  fused second render only: gradient of the extra colour triple
 };
 
 // One thread per Gaussian.  Outputs are caller-zeroed, so invisible Gaussians are skipped.
-template <bool P2>
+// MULTI (fused colour + extra render, power 1): dmeans2D is the colour render's own (moment slots 6-7), everything
+// else is the sum of the two renders, dextra comes from slots 8-10 (see k_bwd_warp).
+template <bool P2, bool MULTI = false>
 __global__ void __launch_bounds__(128) k_expand_grads(int P, GaussIn g, Cam cam, const GRec* __restrict__ recs,
                                                      const int* __restrict__ radii, const float* __restrict__ mom,
                                                      GradOut out) {
@@ -111,6 +114,10 @@ __global__ void __launch_bounds__(128) k_expand_grads(int P, GaussIn g, Cam cam,
         if (has_sr) chain_scale_rot(sr, co.cov3D, res + 9, res + 12);
         con[0] = u[0]; con[1] = u[1]; con[2] = u[2];
         m2d[0] = u[3]; m2d[1] = u[4];
+        if (MULTI) {
+            m2d[0] = -(A * acc[6] + B * acc[7]) * halfW;
+            m2d[1] = -(C * acc[7] + B * acc[6]) * halfH;
+        }
         dop = acc[0] / op;
     } else {
         float col[5][16];
@@ -149,6 +156,7 @@ __global__ void __launch_bounds__(128) k_expand_grads(int P, GaussIn g, Cam cam,
     if (out.dconic) { out.dconic[4 * idx] = con[0]; out.dconic[4 * idx + 1] = con[1]; out.dconic[4 * idx + 3] = con[2]; }
     if (out.dopacity) out.dopacity[idx] = dop;
     if (out.dcolors) { out.dcolors[3 * idx] = acc[13]; out.dcolors[3 * idx + 1] = acc[14]; out.dcolors[3 * idx + 2] = acc[15]; }
+    if (MULTI && out.dextra) { out.dextra[3 * idx] = acc[8]; out.dextra[3 * idx + 1] = acc[9]; out.dextra[3 * idx + 2] = acc[10]; }
     if (out.dmeans3D) { out.dmeans3D[3 * idx] = res[6]; out.dmeans3D[3 * idx + 1] = res[7]; out.dmeans3D[3 * idx + 2] = res[8]; }
     if (out.dcov3D) {
 #pragma unroll

@@ -37,9 +37,15 @@ __device__ __forceinline__ WarpGeom warp_geom(const Bins& bins, const Cam& cam, 
 }
 
 // ---- forward: out_color[3,H,W], out_depth[H,W], final_T, n_contrib ------------------------------------------
+// NX = 1: a second colour triple per Gaussian (`extra`, e.g. SplaTAM's [depth, 1, depth^2], slam_helpers.py:235-252)
+// is blended in the same sweep into out_extra[3,H,W]: the reference rasterises twice for it (gaussian.py:207,211),
+// binning and sorting the same geometry twice.
+template <int NX>
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_render_warp(Bins bins, Cam cam, const float* __restrict__ features,
+                                                                   const float* __restrict__ extra,
                                                                    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                                                                   float* __restrict__ out_color, float* __restrict__ out_depth) {
+                                                                   float* __restrict__ out_color, float* __restrict__ out_extra,
+                                                                   float* __restrict__ out_depth) {
     extern __shared__ float4 smem[];
     const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -53,6 +59,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_render_warp(Bins bins, Ca
 
     float T = 1.0f, D = 15.0f;
     float C[3] = {0.f, 0.f, 0.f};
+    float X[3] = {0.f, 0.f, 0.f};
     int last = 0;
     bool done = !wg.inside;
     if (n > 0 && !__all_sync(0xffffffffu, done)) {
@@ -83,6 +90,12 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_render_warp(Bins bins, Ca
                     float* dst = reinterpret_cast<float*>(&q.rb[0][slot]);
 #pragma unroll
                     for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst + k, c + k, 4);
+                    if (NX) {
+                        const float* c2 = extra + 3 * (size_t)gid;
+                        float* dst2 = reinterpret_cast<float*>(&q.rb[1][slot]);
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst2 + k, c2 + k, 4);
+                    }
                 }
                 __pipeline_commit();
                 qn += __popc(mask);
@@ -110,6 +123,13 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_render_warp(Bins bins, Ca
                     const float c1 = __fmaf_rn(T, __fmul_rn(alpha, f.y), C[1]);
                     const float c2 = __fmaf_rn(T, __fmul_rn(alpha, f.z), C[2]);
                     C[0] = upd ? c0 : C[0]; C[1] = upd ? c1 : C[1]; C[2] = upd ? c2 : C[2];
+                    if (NX) {
+                        const float4 f2 = q.rb[1][slot];
+                        const float x0 = __fmaf_rn(T, __fmul_rn(alpha, f2.x), X[0]);
+                        const float x1 = __fmaf_rn(T, __fmul_rn(alpha, f2.y), X[1]);
+                        const float x2 = __fmaf_rn(T, __fmul_rn(alpha, f2.z), X[2]);
+                        X[0] = upd ? x0 : X[0]; X[1] = upd ? x1 : X[1]; X[2] = upd ? x2 : X[2];
+                    }
                     D = (upd && T > 0.5f && (double)test_T < 0.5) ? a.w : D;       // median depth, forward.cu:367-371
                     T = upd ? test_T : T;
                     last = upd ? __float_as_int(a.z) + 1 : last;
@@ -129,17 +149,28 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_render_warp(Bins bins, Ca
         n_contrib[pix_id] = (uint32_t)last;
 #pragma unroll
         for (int ch = 0; ch < 3; ++ch) out_color[(size_t)ch * H * W + pix_id] = __fmaf_rn(T, cam.bg[ch], C[ch]);
+        if (NX) {
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) out_extra[(size_t)ch * H * W + pix_id] = __fmaf_rn(T, cam.bg[ch], X[ch]);
+        }
         out_depth[pix_id] = D;
     }
 }
 
 // ---- backward: per-Gaussian moment rows mom[P][16] (consumed by k_expand_grads) ------------------------------
 // P2: backward_power == 2 (13 monomial moments of s^2) or 1 (6 sums of s); colour sums in 13..15 either way.
-template <bool P2>
+// NX = 1 (power 1 only: gradients of the two renders ADD, squares would not): the second colour triple and its image
+// gradient dL_dextra ride along.  dL/dalpha sums over the six channels, so the six geometry sums (slots 0-5) are those of
+// both renders together; slots 6-7 keep sum(s_rgb dx), sum(s_rgb dy) of the colour render alone (the reference takes
+// the densification statistic means2D.grad from the colour render only, gaussian.py:208); slots 8-10 are the extra
+// colours' gradients, 13-15 the colours'.
+template <bool P2, int NX>
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_bwd_warp(Bins bins, Cam cam, const float* __restrict__ colors,
+                                                                const float* __restrict__ extra,
                                                                 const float* __restrict__ final_T,
                                                                 const uint32_t* __restrict__ n_contrib,
-                                                                const float* __restrict__ dL_dpix, float* __restrict__ mom) {
+                                                                const float* __restrict__ dL_dpix,
+                                                                const float* __restrict__ dL_dextra, float* __restrict__ mom) {
     extern __shared__ float4 smem[];
     const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -153,12 +184,17 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_bwd_warp(Bins bins, Cam c
     const int pix_id = cam.W * wg.py + wg.px;
     const float T_final = wg.inside ? final_T[pix_id] : 0.f;
     const int last = wg.inside ? (int)n_contrib[pix_id] : 0;
-    float dpix[3], bgdot = 0.f;
+    float dpix[3], dext[3] = {0.f, 0.f, 0.f}, bgdot = 0.f, bgdot_x = 0.f;
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
         dpix[ch] = wg.inside ? dL_dpix[(size_t)ch * cam.H * cam.W + pix_id] : 0.f;
         bgdot += cam.bg[ch] * dpix[ch];
+        if (NX) {
+            dext[ch] = wg.inside ? dL_dextra[(size_t)ch * cam.H * cam.W + pix_id] : 0.f;
+            bgdot_x += cam.bg[ch] * dext[ch];
+        }
     }
+    float accum_x[3] = {0.f, 0.f, 0.f}, last_x[3] = {0.f, 0.f, 0.f};
     const int warp_last = min(__reduce_max_sync(0xffffffffu, last), (int)(range.y - range.x));
     if (warp_last == 0) return;
     float T = T_final;
@@ -194,6 +230,12 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_bwd_warp(Bins bins, Cam c
                 float* dst = reinterpret_cast<float*>(&q.rb[0][slot]);
 #pragma unroll
                 for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst + k, c + k, 4);
+                if (NX) {
+                    const float* c2 = extra + 3 * (size_t)gid;
+                    float* dst2 = reinterpret_cast<float*>(&q.rb[1][slot]);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst2 + k, c2 + k, 4);
+                }
             }
             __pipeline_commit();
             qn += __popc(mask);
@@ -232,9 +274,25 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_bwd_warp(Bins bins, Cam c
                         v[13 + ch] = P2 ? cc * cc : cc;
                     }
                     dL_dalpha *= T;
+                    float dL_dalpha_x = 0.0f;
+                    if (NX) {
+                        const float4 f2 = q.rb[1][slot];
+                        const float colx[3] = {f2.x, f2.y, f2.z};
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch) {
+                            accum_x[ch] = last_alpha * last_x[ch] + (1.f - last_alpha) * accum_x[ch];
+                            last_x[ch] = colx[ch];
+                            dL_dalpha_x += (colx[ch] - accum_x[ch]) * dext[ch];
+                            v[8 + ch] = dchannel_dcolor * dext[ch];
+                        }
+                        dL_dalpha_x *= T;
+                        dL_dalpha_x += (-T_final / (1.f - alpha)) * bgdot_x;
+                    }
                     last_alpha = alpha;
                     dL_dalpha += (-T_final / (1.f - alpha)) * bgdot;
-                    const float s = G * (co.w * dL_dalpha);
+                    const float s_rgb = G * (co.w * dL_dalpha);
+                    const float s = NX ? s_rgb + G * (co.w * dL_dalpha_x) : s_rgb;
+                    if (NX) { v[6] = s_rgb * dx; v[7] = s_rgb * dy; }
                     if (P2) {
                         const float qq = s * s;
                         const float qx = qq * dx, qy = qq * dy;

@@ -143,3 +143,34 @@ def initialize_new_params(new_pt_cld, mean3_sq_dist, isotropic=False):
         "log_scales": torch.tile(torch.log(torch.sqrt(mean3_sq_dist))[..., None], (1, 3 if not isotropic else 1)),
     }
     return {k: torch.nn.Parameter(v.float().contiguous().requires_grad_(True)) for k, v in out.items()}
+
+
+# ---- map update, optimisation half: the renders of get_loss in one pass -------------------------
+def get_depth_and_silhouette(pts_3D, w2c):
+    """slam_helpers.py:235-252: per-Gaussian colours [depth_z, 1, depth_z^2] of the depth + silhouette render."""
+    pts4 = torch.cat((pts_3D, torch.ones_like(pts_3D[:, :1])), dim=-1)
+    pts_in_cam = (w2c @ pts4.transpose(0, 1)).transpose(0, 1)
+    depth_z = pts_in_cam[:, 2].unsqueeze(-1)
+    return torch.cat((depth_z, torch.ones_like(depth_z), torch.square(depth_z)), dim=-1)
+
+
+def render_rgb_depth_silhouette(params, cam, w2c, transformed_pts):
+    """The two renders of get_loss / add_new_gaussians (models/SLAM/gaussian.py:203-216, 325-341) as ONE operator call:
+        rendervar          = transformed_params2rendervar(params, transformed_pts)            (slam_helpers.py:178-188)
+        depth_sil_rendervar = transformed_params2depthplussilhouette(params, w2c, transformed_pts)   (:268-279)
+        im, radius, _ = Renderer(cam)(**rendervar);  depth_sil, _, _ = Renderer(cam)(**depth_sil_rendervar)
+    Preprocess, binning and sort run once, one sweep blends the six channels, one backward sweep returns the gradients
+    (differentiable through params and transformed_pts like the reference's two calls; means2D carries the colour
+    render's gradient only, as variables['means2D'] does in the reference).
+    Returns (im [3,H,W], radius [P], depth_sil [3,H,W], means2D [P,3] leaf whose .grad is the densification statistic)."""
+    from .rasterizer import GaussianRasterizerFused
+    import torch.nn.functional as F
+    log_scales = params['log_scales'] if params['log_scales'].shape[-1] == 3 else torch.tile(params['log_scales'], (1, 3))
+    means2D = torch.zeros_like(params['means3D'], requires_grad=True, device=params['means3D'].device) + 0
+    if means2D.requires_grad:
+        means2D.retain_grad()
+    im, radius, _, depth_sil = GaussianRasterizerFused(cam)(
+        means3D=transformed_pts, means2D=means2D, opacities=torch.sigmoid(params['logit_opacities']),
+        colors_precomp=params['rgb_colors'], extra_colors=get_depth_and_silhouette(transformed_pts, w2c),
+        scales=torch.exp(log_scales), rotations=F.normalize(params['unnorm_rotations']))
+    return im, radius, depth_sil, means2D

@@ -185,6 +185,72 @@ class _CModule:
 
     @staticmethod
     @_on_tensor_device
+    def rasterize_gaussians2(bg, means3D, colors, extra_colors, opacity, scales, rotations, scale_modifier, viewmatrix,
+                             projmatrix, tan_fovx, tan_fovy, image_height, image_width, campos, prefiltered):
+        """Colour render and a second render of `extra_colors` [P,3] over the same geometry in one pass:
+        returns (num_rendered, color, extra, radii, geomBuffer, binningBuffer, imgBuffer, depth)."""
+        if means3D.ndim != 2 or means3D.size(1) != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")
+        L = _lib.lib()
+        P, H, W = means3D.size(0), int(image_height), int(image_width)
+        means3D, colors, extra_colors, opacity, scales, rotations = map(
+            _f32c, (means3D, colors, extra_colors, opacity, scales, rotations))
+        dev = means3D.device
+        out_color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+        out_extra = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
+        out_depth = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
+        radii = torch.zeros((P,), dtype=torch.int32, device=dev)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        if P == 0:
+            e = torch.empty((0,), **u8)
+            return 0, out_color, out_extra, radii, e, e.clone(), e.clone(), out_depth
+        cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, 0, 0, campos, prefiltered)
+        g = _gauss(P, means3D, opacity, None, colors, scales, rotations, None)
+        geom = torch.empty((L.fb_geom_bytes(P),), **u8)
+        img = torch.empty((L.fb_image_bytes(W, H),), **u8)
+        n = C.c_int(0)
+        st = _stream()
+        _lib.check(L.fb_raster_forward_bin(C.byref(cam), C.byref(g), geom.data_ptr(), geom.numel(), img.data_ptr(),
+                                           img.numel(), None, 0, radii.data_ptr(), C.byref(n), st), "rasterize_gaussians2")
+        R = n.value
+        inst = torch.empty((L.fb_inst_bytes(R),), **u8)
+        _lib.check(L.fb_raster_forward_render2(C.byref(cam), C.byref(g), extra_colors.data_ptr(), geom.data_ptr(),
+                                               geom.numel(), img.data_ptr(), img.numel(), inst.data_ptr(), inst.numel(),
+                                               None, 0, R, out_color.data_ptr(), out_extra.data_ptr(),
+                                               out_depth.data_ptr(), st), "rasterize_gaussians2")
+        return R, out_color, out_extra, radii, geom, inst, img, out_depth
+
+    @staticmethod
+    @_on_tensor_device
+    def rasterize_gaussians_backward2(bg, means3D, radii, colors, extra_colors, scales, rotations, scale_modifier,
+                                      viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_extra, campos,
+                                      geomBuffer, R, binningBuffer, imageBuffer):
+        """Backward of rasterize_gaussians2 (power 1): (dL_dmeans2D of the colour render alone, dL_dcolors, dL_dextra,
+        dL_dopacity, dL_dmeans3D, dL_dscales, dL_drotations), the shared inputs' gradients summed over both renders."""
+        L = _lib.lib()
+        P, H, W = means3D.size(0), dL_dout_color.size(1), dL_dout_color.size(2)
+        o = dict(dtype=torch.float32, device=means3D.device)
+        dL_dmeans3D, dL_dmeans2D = torch.zeros((P, 3), **o), torch.zeros((P, 3), **o)
+        dL_dcolors, dL_dextra = torch.zeros((P, 3), **o), torch.zeros((P, 3), **o)
+        dL_dopacity = torch.zeros((P, 1), **o)
+        dL_dscales, dL_drotations = torch.zeros((P, 3), **o), torch.zeros((P, 4), **o)
+        if P != 0 and int(R) != 0:
+            means3D, colors, extra_colors, scales, rotations, dL_dout_color, dL_dout_extra = map(
+                _f32c, (means3D, colors, extra_colors, scales, rotations, dL_dout_color, dL_dout_extra))
+            cam = _camera(bg, scale_modifier, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, 0, 0, campos, False)
+            g = _gauss(P, means3D, means3D, None, colors, scales, rotations, None)
+            scratch = torch.empty((L.fb_backward_scratch_bytes(P, int(R), 1, 0),), dtype=torch.uint8, device=means3D.device)
+            _lib.check(L.fb_raster_backward2(
+                C.byref(cam), C.byref(g), extra_colors.data_ptr(), radii.data_ptr(), geomBuffer.data_ptr(),
+                geomBuffer.numel(), imageBuffer.data_ptr(), imageBuffer.numel(), _ptr(binningBuffer), binningBuffer.numel(),
+                scratch.data_ptr(), scratch.numel(), int(R), dL_dout_color.data_ptr(), dL_dout_extra.data_ptr(), 1,
+                dL_dmeans2D.data_ptr(), None, dL_dopacity.data_ptr(), dL_dcolors.data_ptr(), dL_dextra.data_ptr(),
+                dL_dmeans3D.data_ptr(), None, None, dL_dscales.data_ptr(), dL_drotations.data_ptr(), _stream()),
+                "rasterize_gaussians_backward2")
+        return dL_dmeans2D, dL_dcolors, dL_dextra, dL_dopacity, dL_dmeans3D, dL_dscales, dL_drotations
+
+    @staticmethod
+    @_on_tensor_device
     def mark_visible(means3D, viewmatrix, projmatrix):
         L = _lib.lib()
         P = means3D.size(0)
@@ -236,6 +302,54 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
                         raster_settings, backward_power):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings, backward_power)
+
+
+class _RasterizeGaussians2(torch.autograd.Function):
+    """Autograd bridge of the fused colour + extra render (inputs in the order of the reference's bridge, with the
+    second colour triple after the first)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, colors_precomp, extra_colors, opacities, scales, rotations, raster_settings):
+        rs = raster_settings
+        num_rendered, color, extra, radii, geomBuffer, binningBuffer, imgBuffer, depth = _C.rasterize_gaussians2(
+            rs.bg, means3D, colors_precomp, extra_colors, opacities, scales, rotations, rs.scale_modifier, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, rs.campos, rs.prefiltered)
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, extra_colors, means3D, scales, rotations, radii, geomBuffer, binningBuffer,
+                              imgBuffer)
+        ctx.mark_non_differentiable(radii, depth)
+        return color, radii, depth, extra
+
+    @staticmethod
+    def backward(ctx, grad_color, _grad_radii, _grad_depth, grad_extra):
+        rs = ctx.raster_settings
+        colors_precomp, extra_colors, means3D, scales, rotations, radii, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        H, W = rs.image_height, rs.image_width
+        if grad_color is None:
+            grad_color = torch.zeros((3, H, W), dtype=torch.float32, device=means3D.device)
+        if grad_extra is None:
+            grad_extra = torch.zeros((3, H, W), dtype=torch.float32, device=means3D.device)
+        g2d, gcol, gext, gop, g3d, gsc, grot = _C.rasterize_gaussians_backward2(
+            rs.bg, means3D, radii, colors_precomp, extra_colors, scales, rotations, rs.scale_modifier, rs.viewmatrix,
+            rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_extra, rs.campos, geomBuffer, ctx.num_rendered,
+            binningBuffer, imgBuffer)
+        return g3d, g2d, gcol, gext, gop, gsc, grot, None
+
+
+class GaussianRasterizerFused(nn.Module):
+    """Two renders of one geometry in one pass: `forward(...)` returns (color [3,H,W], radii, depth, extra [3,H,W]), the
+    results of `GaussianRasterizer(rs)(colors_precomp=colors)` and `GaussianRasterizer(rs)(colors_precomp=extra)[0]` --
+    what get_loss / add_new_gaussians do with two operator calls (models/SLAM/gaussian.py:207,211,325-341).
+    backward_power is 1 (the two renders' gradients add); means2D receives the colour render's gradient only."""
+
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def forward(self, means3D, means2D, opacities, colors_precomp, extra_colors, scales, rotations):
+        return _RasterizeGaussians2.apply(means3D, means2D, colors_precomp, extra_colors, opacities, scales, rotations,
+                                          self.raster_settings)
 
 
 class GaussianRasterizer(nn.Module):

@@ -171,6 +171,25 @@ int fb_raster_backward(const fb_camera* cam, const fb_gaussians* g,
                        float* dL_dsh, float* dL_dscales, float* dL_drotations,
                        void* stream);
 
+/* Fused second render.  SplaTAM-style mapping / tracking rasterises every iteration twice with the
+ * same geometry: colours, then colors_precomp = [depth, 1, depth^2] for depth + silhouette (models/SLAM/gaussian.py:
+ * 207,211; models/SLAM/utils/slam_helpers.py:235-252,268-279).  These take the second colour triple along:
+ * preprocess, binning and sort run once (fb_raster_forward_bin), one sweep blends six channels, one backward sweep
+ * (power 1 only: the two renders' gradients add) returns the summed gradients of the shared inputs, the gradients of
+ * both colour triples, and dL_dmeans2D of the COLOUR render alone (the densification statistic, gaussian.py:208).
+ * extra_colors [P,3], out_extra / dL_dextra [3,H,W]; NULL extra_colors = the plain calls above. */
+int fb_raster_forward_render2(const fb_camera* cam, const fb_gaussians* g, const float* extra_colors,
+                              void* geom, size_t geom_bytes, void* image, size_t image_bytes,
+                              void* inst, size_t inst_bytes, void* scratch, size_t scratch_bytes,
+                              int num_rendered, float* out_color, float* out_extra, float* out_depth, void* stream);
+int fb_raster_backward2(const fb_camera* cam, const fb_gaussians* g, const float* extra_colors, const int* radii,
+                        const void* geom, size_t geom_bytes, const void* image, size_t image_bytes,
+                        const void* inst, size_t inst_bytes, void* scratch, size_t scratch_bytes,
+                        int num_rendered, const float* dL_dpix, const float* dL_dextra, int power,
+                        float* dL_dmeans2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolors,
+                        float* dL_dextra_colors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                        float* dL_dscales, float* dL_drotations, void* stream);
+
 /* present[i] = (viewmatrix * p_i).z > 0.001  (rasterizer_impl.cu:54-66). */
 int fb_mark_visible(int P, const float* means3D, const float* viewmatrix,
                     const float* projmatrix, uint8_t* present, void* stream);

@@ -114,3 +114,77 @@ def test_argument_checks(cuda):
         cuda.get_pointcloud(tc.cpu(), td.cpu(), tK, tw)
     with pytest.raises(RuntimeError):
         cuda.get_pointcloud(tc, td, tK, tw, downsample=5)
+
+
+def test_fused_rgb_depth_silhouette_render_matches_two_reference_calls(cuda):
+    """SURVEY 8(f) N1, optimisation half: the two renders of get_loss (models/SLAM/gaussian.py:207,211) in ONE pass --
+    image, depth + silhouette image, radii and every parameter gradient (through params AND transformed_pts, including
+    the depth colours' dependence on the points) against two forward + two backward calls of the UNMODIFIED reference
+    extension; means2D.grad is the colour render's alone."""
+    import torch
+    import torch.nn.functional as F
+    from oracle import build_ref
+    from fisher_nerf_customized_b200 import synth
+    ref_C = build_ref.import_ref("ref_dgr")
+    if ref_C is None:
+        pytest.skip("oracle/_ref/ref_dgr not built")
+    W = H = 256
+    P = 200_000
+    raw = synth.make_scene(P, seed=21)
+    rs = cuda.setup_camera(W, H, synth.intrinsics(W, H), np.eye(4, dtype=np.float32))
+    w2c = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(1, seed=4))[0]).cuda()
+    g = torch.Generator(device="cuda").manual_seed(3)
+    w_im = torch.randn((3, H, W), generator=g, device="cuda") * 1e-2
+    w_ds = torch.randn((3, H, W), generator=g, device="cuda") * 1e-2
+    e = torch.Tensor([])
+
+    class RefRaster(torch.autograd.Function):        # the reference's autograd bridge (__init__.py:42-138), power 1
+        @staticmethod
+        def forward(ctx, tag, means3D, colors, opacities, scales, rotations):
+            R, color, radii, geom, binning, img, depth = ref_C.rasterize_gaussians(
+                rs.bg, means3D, colors, opacities, scales, rotations, 1.0, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                rs.tanfovy, H, W, e, 0, rs.campos, False)
+            ctx.R, ctx.tag = R, tag
+            ctx.save_for_backward(means3D, colors, scales, rotations, radii, geom, binning, img)
+            return color, radii
+
+        @staticmethod
+        def backward(ctx, gc, _gr):
+            means3D, colors, scales, rotations, radii, geom, binning, img = ctx.saved_tensors
+            g2d, gcol, gop, g3d, gcov, gsh, gsc, grot = ref_C.rasterize_gaussians_backward(
+                rs.bg, means3D, radii, colors, scales, rotations, 1.0, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                rs.tanfovy, gc.contiguous(), e, 0, rs.campos, geom, ctx.R, binning, img, 1)
+            RefRaster.means2D[ctx.tag] = g2d
+            return None, g3d, gcol, gop, gsc, grot
+
+    def leaves():
+        p = {k: torch.from_numpy(np.asarray(v, np.float32)).cuda().requires_grad_(True) for k, v in raw.items()}
+        pts4 = torch.cat((p["means3D"], torch.ones(P, 1, device="cuda")), dim=1)
+        return p, (w2c @ pts4.T).T[:, :3].contiguous()
+
+    # reference: two renders
+    p, tp = leaves()
+    rot, op, sc = F.normalize(p["unnorm_rotations"]), torch.sigmoid(p["logit_opacities"]), torch.exp(p["log_scales"])
+    RefRaster.means2D = {}
+    im_r, radii_r = RefRaster.apply("rgb", tp, p["rgb_colors"], op, sc, rot)
+    ds_r, _ = RefRaster.apply("ds", tp, cuda.get_depth_and_silhouette(tp, torch.eye(4, device="cuda")), op, sc, rot)
+    ((im_r * w_im).sum() + (ds_r * w_ds).sum()).backward()
+    m2d_r = RefRaster.means2D["rgb"]
+    want = {k: v.grad.clone() for k, v in p.items()}
+    # fused
+    p2, tp2 = leaves()
+    im, radius, depth_sil, means2D = cuda.render_rgb_depth_silhouette(p2, rs, torch.eye(4, device="cuda"), tp2)
+    ((im * w_im).sum() + (depth_sil * w_ds).sum()).backward()
+    assert torch.equal(radius, radii_r)
+    assert torch.equal(im, im_r)                                  # same sweep arithmetic as the drop-in: bit-identical
+    torch.testing.assert_close(depth_sil, ds_r, rtol=1e-5, atol=1e-6)
+    vis = radius > 0
+    for k in want:
+        got, ref = p2[k].grad, want[k]
+        scale = ref.abs().amax()
+        bad = (got - ref).abs() > 1e-3 * ref.abs() + 1e-5 * scale
+        assert bad[vis].float().mean().item() < 1e-3, (k, int(bad.sum()))
+        assert not got[~vis].any()
+    scale = m2d_r.abs().amax()
+    bad = (means2D.grad - m2d_r).abs() > 1e-3 * m2d_r.abs() + 1e-5 * scale
+    assert bad.float().mean().item() < 1e-3

@@ -342,7 +342,7 @@ def test_plan_best_path_vs_reference_extension_loop(cuda):
     rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
     t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
     gmap = _gmap(cuda, torch, sc)
-    lengths = [14, 9, 4, 11, 19, 5]                      # 2, 1, 0, 2, 3, 1 accumulation levels
+    lengths = [14, 9, 3, 11, 19, 5]                      # 3, 2, 0, 2, 4, 1 accumulation levels (steps 4, 9, 14, 19)
     all_poses = synth.w2c_from_c2w(synth.make_poses(sum(lengths) + 3, seed=17))
     kf, rest = all_poses[:3], all_poses[3:]
     paths, o = [], 0
@@ -384,7 +384,7 @@ def test_plan_best_path_vs_reference_extension_loop(cuda):
     got, best, point = scorer.plan_best_path(gmap, paths, final_EIGs, H_train, lam, acc, pose_w, point_w, end_w)
     np.testing.assert_allclose(np.array(got), np.array(want), rtol=1e-3, atol=1e-5)
     assert best == int(np.argmax(want))
-    assert int(torch.isfinite(point).sum()) == 2 + 1 + 0 + 2 + 3 + 1
+    assert int(torch.isfinite(point).sum()) == sum(sum(1 for i in range(1, L + 1) if (i + 1) % acc == 0) for L in lengths) == 12
     # the object variant drops the point term (:1929, :1936) and only the end term decides
     got_o, best_o, _ = scorer.plan_best_path(gmap, paths, final_EIGs, H_train, lam, acc, pose_w, point_w, end_w,
                                              object_variant=True)

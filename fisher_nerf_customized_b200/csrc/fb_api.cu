@@ -94,7 +94,11 @@ size_t fb_image_bytes(int w, int h) { return image_layout(w, h).total; }
 // sorted keys + an equally sized ping-pong area for tile lists longer than the shared-memory sort capacity
 size_t fb_inst_bytes(int R) { return 2 * align_up((size_t)(R > 0 ? R : 1) * 8, 256); }
 size_t fb_forward_scratch_bytes(int, int, int, int) { return 256; }
-size_t fb_backward_scratch_bytes(int P, int, int, int) { return align_up((size_t)(P > 0 ? P : 1) * FB_NACC * 4, 256); }
+// moment rows (power 1 / 2, precomputed colours) or the per-pair fallback's chain rows (any other power, SH colours)
+size_t fb_backward_scratch_bytes(int P, int, int power, int sh) {
+    const size_t per = (power == 1 || power == 2) && !sh ? (size_t)FB_NACC * 4 : (size_t)FB_ROW_FLOATS * 4;
+    return align_up((size_t)(P > 0 ? P : 1) * per, 256);
+}
 
 }  // extern "C"
 
@@ -245,7 +249,7 @@ int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* 
                         const float* dL_dextra, int power, float* dL_dmeans2D, float* dL_dconic, float* dL_dopacity,
                         float* dL_dcolors, float* dL_dextra_colors, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                         float* dL_dscales, float* dL_drotations, void* stream_) {
-    (void)geom_bytes; (void)image_bytes; (void)inst_bytes; (void)dL_dsh;
+    (void)geom_bytes; (void)image_bytes; (void)inst_bytes;
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !dL_dpix) return FB_E_INVALID;
     if ((extra_colors == nullptr) != (dL_dextra == nullptr)) return FB_E_INVALID;
@@ -255,13 +259,31 @@ int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* 
     const int P = g->P;
     if (P == 0 || num_rendered == 0) return FB_OK;
     if (!geom || !image || !inst || !radii || !scratch) return FB_E_INVALID;
-    if (power != 1 && power != 2) return FB_E_INVALID;              // see DESIGN.md: other powers unsupported
-    if (g->shs && c->sh_degree > 0) return FB_E_INVALID;            // SH backward (degree>0) unsupported, DESIGN.md
-    if (scratch_bytes < fb_backward_scratch_bytes(P, num_rendered, power, 0)) return FB_E_WORKSPACE;
+    const bool pairwise = (power != 1 && power != 2) || (g->shs && c->sh_degree > 0);
+    if (pairwise && (extra_colors || !FB_DROPIN_WARP)) return FB_E_INVALID;
+    if (scratch_bytes < fb_backward_scratch_bytes(P, num_rendered, power, pairwise ? 1 : 0)) return FB_E_WORKSPACE;
     Cam cam = make_cam(c);
     Bins b = single_bins(P, cam, (void*)geom, (void*)image, (void*)inst, (long long)num_rendered);
     GeomLayout GL = geom_layout(P);
     ImageLayout IL = image_layout(cam.W, cam.H);
+    if (pairwise) {
+        // any integer power / SH degree > 0: the reference's per-pair definition (fb_backward.cuh: k_bwd_pairs)
+        float* rows = (float*)scratch;
+        const float* featp = g->colors_precomp ? g->colors_precomp : (const float*)((const char*)geom + GL.rgb);
+        ShArgs sh{g->shs, (const bool*)((const char*)geom + GL.clamped), c->sh_degree, c->sh_coeffs, nullptr};
+        // campos lives in the camera struct; k_chain_rows reads it from device-visible kernel parameters
+        Cam* cam_ptr = nullptr; (void)cam_ptr;
+        static_assert(sizeof(Cam) < 4000, "Cam travels as a kernel parameter");
+        { FB_PROF(FB_K_EXPAND); k_chain_rows<<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, sh, rows); }
+        FB_LAUNCH_CHECK();
+        PairOut po{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations,
+                   (g->shs && c->sh_degree > 0) ? dL_dsh : nullptr};
+        { FB_PROF(FB_K_BWD_TILES); k_bwd_pairs<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
+            b, cam, featp, (const float*)((const char*)image + IL.final_T), (const uint32_t*)((const char*)image + IL.n_contrib),
+            dL_dpix, rows, power, c->sh_coeffs, g->shs ? c->sh_degree : 0, (g->scales && g->rotations) ? 1 : 0, po); }
+        FB_LAUNCH_CHECK();
+        return FB_OK;
+    }
     float* mom = (float*)scratch;
     FB_CUDA(cudaMemsetAsync(mom, 0, (size_t)P * FB_NACC * 4, st));
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((const char*)geom + GL.rgb);

@@ -69,6 +69,7 @@ SIGNATURES = {
     "fb_block_outer_accumulate": (ci, [ci, vp, vp, vp, vp, vp, cf, vp, vp]),
     "fb_unproject_append": (ci, [ci, ci, ci, vp, vp, vp, vp, vp, ll, vp, ci, vp, ci, vp, vp, vp, ci,
                                 vp, vp]),
+    "fb_morton_codes": (ci, [ci, vp, vp, vp, vp, vp]),
     "fb_occ_workspace_bytes": (sz, [ci, ci]),
     "fb_occ_update": (ci, [vp, ci, ci, vp, ci, ci, ci, vp, vp, vp, vp, cf, cf, cf, cf, vp, vp, sz, vp]),
     "fb_count_vs_mask": (ci, [ci, vp, vp, vp, vp, vp, ci, ci, cf, vp, vp, vp]),

@@ -478,6 +478,17 @@ int fb_unproject_append(int width, int height, int downsample, const float* colo
     return FB_OK;
 }
 
+int fb_morton_codes(int P, const float* means3D, const float* lo, const float* ext, int* codes, void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (P < 0) return FB_E_INVALID;
+    if (P == 0) return FB_OK;
+    if (!means3D || !lo || !ext || !codes) return FB_E_INVALID;
+    { FB_PROF(FB_K_MAPUPDATE); k_morton30<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, lo, ext, codes); }
+    FB_LAUNCH_CHECK();
+    return FB_OK;
+}
+
 size_t fb_occ_workspace_bytes(int gx, int gz) {
     const size_t n = (size_t)(gx > 0 ? gx : 1) * (gz > 0 ? gz : 1);
     return fb::align_up(n * 4, 256) * 2 + fb::align_up(n, 256) + 256;

@@ -66,4 +66,27 @@ __global__ void __launch_bounds__(256) k_unproject_append(UnprojectArgs a) {
     }
 }
 
+// 30-bit Morton code of each mean inside the bounding box [lo, lo + ext] (10 bits per axis): the key the resident map
+// is sorted by (one kernel instead of ~35 elementwise launches; the sort itself is a library radix sort).
+__device__ __forceinline__ unsigned spread10(unsigned v) {
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__global__ void __launch_bounds__(256) k_morton30(int P, const float* __restrict__ means, const float* __restrict__ lo,
+                                                  const float* __restrict__ ext, int* __restrict__ codes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    unsigned q[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float e = fmaxf(ext[a], 1e-12f);
+        const float t = (means[3 * (size_t)i + a] - lo[a]) / e * 1023.0f;
+        q[a] = (unsigned)min(1023, max(0, (int)t));                      // NaN -> 0
+    }
+    codes[i] = (int)(spread10(q[0]) | (spread10(q[1]) << 1) | (spread10(q[2]) << 2));
+}
+
 }  // namespace fb

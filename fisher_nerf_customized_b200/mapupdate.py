@@ -94,6 +94,19 @@ class ResidentParams:
         self.buf = {k: torch.zeros((self.capacity, (1 if (k == "log_scales" and isotropic) else c)), dtype=torch.float32,
                                    device=device) for k, c in self.KEYS}
         self.timestep = torch.zeros((self.capacity,), dtype=torch.float32, device=device)
+        self._maps = []
+
+    def attach(self, gmap):
+        """Keep a GaussianMap (the activated, Morton-ordered replica the scorer reads) in step with this store: every
+        append activates and appends the new rows there too (O(new rows)), so the map cannot be scored stale."""
+        if gmap.P != self.n:
+            raise RuntimeError(f"attach: the map holds {gmap.P} Gaussians, the store {self.n}")
+        self._maps.append(gmap)
+        return gmap
+
+    def _notify(self, r0, n):
+        for m in self._maps:
+            m.append_rows(self.params(), r0, n)
 
     def params(self):
         return {k: v[:self.n] for k, v in self.buf.items()}
@@ -124,6 +137,7 @@ class ResidentParams:
                 ls_cols=1 if self.isotropic else 3)
         self.timestep[r0:r0 + n] = float(time_idx)
         self.n += n
+        self._notify(r0, n)
         return r0, n
 
 

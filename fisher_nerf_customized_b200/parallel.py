@@ -73,6 +73,8 @@ class ShardedScorer:
                 store.timestep[r0:r0 + n] = pack[:, o]
         if self.rank != src:
             store.n = r0 + n
+            if hasattr(store, "_notify"):
+                store._notify(r0, n)                      # attached GaussianMaps follow (the owner's did in append_from_frame)
         return r0, n
 
     def compute_H_train(self, gmap, keyframe_w2c):

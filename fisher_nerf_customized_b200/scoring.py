@@ -48,18 +48,20 @@ def read_npz_params(path, device="cuda"):
 
 
 def morton_order(means3D, bits=10):
-    """Permutation that sorts points by the 3*bits-bit Morton code of their position in the map's bounding
-    box (device-side torch ops, no host sync): Gaussians that are close in space become close in memory, so
-    the 32 Gaussians of a warp land in a handful of tiles (warp-aggregated counters) and a tile's list
+    """Permutation that sorts points by the 30-bit Morton code of their position in the map's bounding
+    box (one kernel for the codes + one device radix sort, no host sync): Gaussians that are close in space become close
+    in memory, so the 32 Gaussians of a warp land in a handful of tiles (warp-aggregated counters) and a tile's list
     gathers neighbouring records."""
-    lo = means3D.amin(dim=0, keepdim=True)
-    ext = (means3D.amax(dim=0, keepdim=True) - lo).clamp_min(1e-12)
-    q = ((means3D - lo) / ext * (2 ** bits - 1)).to(torch.int64).clamp_(0, 2 ** bits - 1)
-    code = torch.zeros((means3D.shape[0],), dtype=torch.int64, device=means3D.device)
-    for b in range(bits):
-        for axis in range(3):
-            code |= ((q[:, axis] >> b) & 1) << (3 * b + axis)
-    return torch.argsort(code, stable=True)
+    assert bits == 10
+    means3D = _f32c(means3D)
+    P = means3D.shape[0]
+    lo = means3D.amin(dim=0).contiguous()
+    ext = (means3D.amax(dim=0) - lo).contiguous()
+    codes = torch.empty((P,), dtype=torch.int32, device=means3D.device)
+    with torch.cuda.device(means3D.device):
+        _lib.check(_lib.lib().fb_morton_codes(P, means3D.data_ptr(), lo.data_ptr(), ext.data_ptr(), codes.data_ptr(),
+                                              _stream()), "fb_morton_codes")
+    return torch.argsort(codes, stable=True)
 
 
 class GaussianMap:
@@ -69,27 +71,52 @@ class GaussianMap:
     HBM layout: with `spatial_order=True` (default) the replica is stored in Morton order of the means
     (`perm[i]` = caller's index of the Gaussian stored at row i).  Everything that crosses the API in per-Gaussian
     form (H_train, H_train_inv, compute_Hessian) stays in the CALLER's order; FisherScorer permutes at the
-    boundary (one 4*C_H*P-byte gather per call).  Scores are sums over Gaussians and do not depend on the order."""
+    boundary (one 4*C_H*P-byte gather per call).  Scores are sums over Gaussians and do not depend on the order.
 
-    def __init__(self, means3D, rgb_colors, rotations, opacities, scales, spatial_order=True):
+    The arrays have CAPACITY: `append_rows` activates only the rows a densification step added and writes them behind
+    the live rows (unsorted tail: the order is a layout, not a result); when the tail outgrows `resort_fraction` of the
+    map the whole replica is re-sorted once.  `ResidentParams.attach(map)` keeps an attached map in step with the raw
+    parameter store, so a map can never be scored stale."""
+
+    NAMES = ("means3D", "colors", "rotations", "opacities", "scales")
+
+    def __init__(self, means3D, rgb_colors, rotations, opacities, scales, spatial_order=True, capacity=None,
+                 resort_fraction=0.05):
         scales = scales if scales.shape[-1] == 3 else scales.repeat(1, 3)   # isotropic: gaussian.py:1532-1533
+        self.spatial_order = bool(spatial_order)
+        self.resort_fraction = float(resort_fraction)
         self.perm = None
-        if spatial_order and means3D.shape[0] > 1:
-            with torch.no_grad():
+        self._inv_perm = None
+        self.tail = 0                                                        # rows appended since the last sort
+        with torch.no_grad():
+            if self.spatial_order and means3D.shape[0] > 1:
                 self.perm = morton_order(means3D.detach().float())
-            pick = lambda t: t.detach().index_select(0, self.perm)
-            means3D, rgb_colors, rotations = pick(means3D), pick(rgb_colors), pick(rotations)
-            opacities, scales = pick(opacities.reshape(-1)), pick(scales)
-        self.means3D = _f32c(means3D)
-        self.colors = _f32c(rgb_colors)
-        self.rotations = _f32c(rotations)
-        self.opacities = _f32c(opacities.reshape(-1))
-        self.scales = _f32c(scales)
-        self.P = self.means3D.shape[0]
+                pick = lambda t: t.detach().index_select(0, self.perm)
+                means3D, rgb_colors, rotations = pick(means3D), pick(rgb_colors), pick(rotations)
+                opacities, scales = pick(opacities.reshape(-1)), pick(scales)
+            rows = dict(means3D=_f32c(means3D.detach()), colors=_f32c(rgb_colors.detach()), rotations=_f32c(rotations.detach()),
+                        opacities=_f32c(opacities.detach().reshape(-1)), scales=_f32c(scales.detach()))
+            self.P = rows["means3D"].shape[0]
+            self.capacity = max(int(capacity or 0), self.P)
+            self._buf = {}
+            for k, v in rows.items():
+                if self.capacity > self.P:
+                    b = torch.empty((self.capacity,) + tuple(v.shape[1:]), dtype=torch.float32, device=v.device)
+                    b[:self.P] = v
+                else:
+                    b = v
+                self._buf[k] = b
+
+    # live rows under the names the kernels' fb_map uses
+    means3D = property(lambda self: self._buf["means3D"][:self.P])
+    colors = property(lambda self: self._buf["colors"][:self.P])
+    rotations = property(lambda self: self._buf["rotations"][:self.P])
+    opacities = property(lambda self: self._buf["opacities"][:self.P])
+    scales = property(lambda self: self._buf["scales"][:self.P])
 
     def inverse_perm(self):
         """inverse_perm()[c] = resident row of the caller's Gaussian c (built once, on first use)."""
-        if getattr(self, "_inv_perm", None) is None:
+        if self._inv_perm is None:
             inv = torch.empty_like(self.perm)
             inv[self.perm] = torch.arange(self.P, device=self.perm.device)
             self._inv_perm = inv
@@ -106,14 +133,64 @@ class GaussianMap:
         out.index_copy_(0, self.perm, per_gaussian)
         return out
 
+    @torch.no_grad()
+    def append_rows(self, params, r0, n):
+        """Rows [r0, r0 + n) of the reference's raw parameter dict were appended behind the caller's existing P rows
+        (r0 == P): activate them (gaussian.py:1529-1533) and write them behind the live rows.  O(n), not O(P)."""
+        r0, n = int(r0), int(n)
+        if r0 != self.P:
+            raise RuntimeError(f"append_rows: the map holds {self.P} Gaussians, the new rows start at {r0}")
+        if n == 0:
+            return
+        sl = slice(r0, r0 + n)
+        ls = params["log_scales"][sl]
+        new = dict(means3D=params["means3D"][sl], colors=params["rgb_colors"][sl],
+                   rotations=torch.nn.functional.normalize(params["unnorm_rotations"][sl]),
+                   opacities=torch.sigmoid(params["logit_opacities"][sl]).reshape(-1),
+                   scales=torch.exp(ls if ls.shape[-1] == 3 else ls.repeat(1, 3)))
+        need = self.P + n
+        if need > self.capacity:
+            cap = max(need, int(self.capacity * 1.5) + 1)
+            for k, b in self._buf.items():
+                nb = torch.empty((cap,) + tuple(b.shape[1:]), dtype=torch.float32, device=b.device)
+                nb[:self.P] = b[:self.P]
+                self._buf[k] = nb
+            self.capacity = cap
+        for k, v in new.items():
+            self._buf[k][self.P:need] = v.detach().float()
+        if self.perm is not None:
+            self.perm = torch.cat([self.perm, torch.arange(r0, r0 + n, device=self.perm.device, dtype=self.perm.dtype)])
+        elif self.spatial_order and need > 1:
+            self.perm = torch.arange(need, device=self._buf["means3D"].device)
+        self._inv_perm = None
+        self.P = need
+        self.tail += n
+        if self.spatial_order and self.tail > max(4096, int(self.resort_fraction * self.P)):
+            self.resort()
+
+    @torch.no_grad()
+    def resort(self):
+        """Re-establish the Morton order of the whole replica (after enough appended rows): one code kernel, one sort,
+        five gathers; the caller-order bookkeeping (`perm`) follows."""
+        if not self.spatial_order or self.P < 2:
+            return
+        order = morton_order(self.means3D)
+        for k, b in self._buf.items():
+            nb = torch.empty_like(b)
+            nb[:self.P] = b[:self.P].index_select(0, order)
+            self._buf[k] = nb
+        self.perm = order if self.perm is None else self.perm.index_select(0, order)
+        self._inv_perm = None
+        self.tail = 0
+
     @classmethod
-    def from_params(cls, params, spatial_order=True):
+    def from_params(cls, params, spatial_order=True, capacity=None):
         """From the reference's raw parameter dict (gaussian.py:156-168)."""
         with torch.no_grad():
             return cls(params["means3D"], params["rgb_colors"],
                        torch.nn.functional.normalize(params["unnorm_rotations"]),
                        torch.sigmoid(params["logit_opacities"]), torch.exp(params["log_scales"]),
-                       spatial_order=spatial_order)
+                       spatial_order=spatial_order, capacity=capacity)
 
     @classmethod
     def from_npz(cls, path, device="cuda", spatial_order=True):
@@ -123,8 +200,9 @@ class GaussianMap:
     def c_struct(self):
         m = _lib.fb_map()
         m.P = self.P
-        m.means3D, m.opacities = self.means3D.data_ptr(), self.opacities.data_ptr()
-        m.scales, m.rotations, m.colors = self.scales.data_ptr(), self.rotations.data_ptr(), self.colors.data_ptr()
+        b = self._buf
+        m.means3D, m.opacities = b["means3D"].data_ptr(), b["opacities"].data_ptr()
+        m.scales, m.rotations, m.colors = b["scales"].data_ptr(), b["rotations"].data_ptr(), b["colors"].data_ptr()
         return m
 
     def tensors(self):

@@ -365,6 +365,10 @@ int fb_unproject_append(int width, int height, int downsample,
                         float* log_scales, int log_scale_cols, float* mean3_sq_dist,
                         void* stream);
 
+/* codes[i] = 30-bit Morton code (10 bits per axis, x lowest) of means3D[i] quantised in the box [lo, lo + ext]
+ * (lo, ext: 3 floats each, device): the order the resident map is kept in (see fb_score_workspace_bytes). */
+int fb_morton_codes(int P, const float* means3D, const float* lo, const float* ext, int* codes, void* stream);
+
 /* ---- occupancy grid and masked visibility (planning/astar.py, models/SLAM/gaussian_object.py) ---- */
 
 /* AstarPlanner.update_occ_map (planning/astar.py:202-303) on the device, without its host loop:

@@ -390,3 +390,46 @@ def test_plan_best_path_vs_reference_extension_loop(cuda):
                                              object_variant=True)
     np.testing.assert_allclose(np.array(got_o), np.array(final_EIGs), rtol=1e-6)
     assert best_o == 1
+
+
+def test_morton_order_and_incremental_map(cuda):
+    """The Morton permutation (one code kernel + one sort) groups neighbours; a map grown by `append_rows` (activated
+    tail rows, lazy re-sort) scores exactly like a map rebuilt from the full parameter set; a ResidentParams store keeps
+    an attached map in step."""
+    import torch
+    from fisher_nerf_customized_b200.scoring import morton_order
+    pts = torch.from_numpy(synth.make_points(20000, seed=3)).cuda()
+    perm = morton_order(pts)
+    assert sorted(perm.tolist()) == list(range(20000))
+    s = pts[perm]
+    d_sorted = (s[1:] - s[:-1]).norm(dim=1).median()
+    d_plain = (pts[1:] - pts[:-1]).norm(dim=1).median()
+    assert float(d_sorted) < 0.1 * float(d_plain)
+    assert morton_order(pts[:1]).tolist() == [0]
+    assert sorted(morton_order(torch.zeros((5, 3), device="cuda")).tolist()) == [0, 1, 2, 3, 4]
+    flat = pts.clone(); flat[:, 1] = 0.25
+    assert sorted(morton_order(flat).tolist()) == list(range(20000))
+    # incremental growth == rebuild
+    W = H = 64
+    P0, steps, n_new = 6000, 5, 900
+    raw = synth.make_scene(P0 + steps * n_new, seed=41, box=(6.0, 3.0, 6.0), focal=32.0, mean_depth=2.0)
+    params = {k: torch.from_numpy(np.asarray(v, np.float32)).cuda() for k, v in raw.items()}
+    head = {k: v[:P0] for k, v in params.items()}
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), np.eye(4, dtype=np.float32))
+    poses = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(5, seed=6, box=(6.0, 3.0, 6.0)))).cuda()
+    grown = cuda.GaussianMap.from_params(head, capacity=P0 + 2 * n_new)        # capacity forces one regrow too
+    grown.resort_fraction = 0.2                                                # and one lazy re-sort on the way
+    for i in range(steps):
+        r0 = P0 + i * n_new
+        grown.append_rows({k: v[:r0 + n_new] for k, v in params.items()}, r0, n_new)
+    full = cuda.GaussianMap.from_params(params)
+    assert grown.P == full.P == P0 + steps * n_new and sorted(grown.perm.tolist()) == list(range(grown.P))
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=4)
+    H_a, H_b = scorer.compute_H_train(grown, poses[:2]), scorer.compute_H_train(full, poses[:2])
+    scale = H_b.abs().amax(dim=0, keepdim=True)
+    assert bool(((H_a - H_b).abs() <= 1e-4 * H_b.abs() + 1e-6 * scale).float().mean() > 0.999)
+    w = torch.reciprocal(H_b + 0.1)
+    np.testing.assert_allclose(scorer.score_candidates(grown, poses[2:], w).cpu().numpy(),
+                               scorer.score_candidates(full, poses[2:], w).cpu().numpy(), rtol=1e-4)
+    with pytest.raises(RuntimeError):
+        grown.append_rows(params, 5, 1)                                        # rows must start behind the live ones

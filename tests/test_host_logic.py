@@ -1,10 +1,10 @@
-"""Host-side logic that needs no GPU: checkpoint reading and the Morton layout permutation."""
+"""Host-side logic that needs no GPU: checkpoint reading; the resident map refuses CPU tensors."""
 import numpy as np
 import pytest
 import torch
 
 from fisher_nerf_customized_b200 import synth
-from fisher_nerf_customized_b200.scoring import GaussianMap, morton_order, read_npz_params
+from fisher_nerf_customized_b200.scoring import GaussianMap, read_npz_params
 
 
 def test_read_npz_params_reads_the_reference_checkpoint_format(tmp_path):
@@ -29,19 +29,3 @@ def test_gaussian_map_refuses_cpu_tensors():
     z = torch.zeros((4, 3))
     with pytest.raises(RuntimeError):
         GaussianMap(z, z, torch.zeros((4, 4)), torch.zeros((4, 1)), z, spatial_order=False)
-
-
-def test_morton_order_is_a_permutation_and_groups_neighbours():
-    pts = torch.from_numpy(synth.make_points(20000, seed=3))
-    perm = morton_order(pts)
-    assert sorted(perm.tolist()) == list(range(20000))
-    s = pts[perm]
-    # consecutive points of the ordered map are much closer than consecutive points of the shuffled one
-    d_sorted = (s[1:] - s[:-1]).norm(dim=1).median()
-    d_plain = (pts[1:] - pts[:-1]).norm(dim=1).median()
-    assert float(d_sorted) < 0.1 * float(d_plain)
-    # degenerate inputs: one point, coincident points, a flat axis
-    assert morton_order(pts[:1]).tolist() == [0]
-    assert sorted(morton_order(torch.zeros((5, 3))).tolist()) == [0, 1, 2, 3, 4]
-    flat = pts.clone(); flat[:, 1] = 0.25
-    assert sorted(morton_order(flat).tolist()) == list(range(20000))

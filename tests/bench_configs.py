@@ -216,7 +216,7 @@ def cfg5(steps):
     if rank == 0:
         for f in range(nf):
             masks[f, torch.from_numpy(rng.choice(H * W, size=add, replace=False)).to(dev)] = True
-    cand = c2w_all[steps:steps + 256]
+    cand = torch.from_numpy(synth.make_poses(256, seed=78)).to(dev)     # the same candidates whatever `steps` is
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     picks, vis_last = [], None
     if world > 1:
@@ -310,7 +310,7 @@ def cfg5_reference(steps):
         _ = int((radii > 0).sum().item())
         return torch.cat([g[3], g[2].reshape(-1, 1)], dim=1)
 
-    cand = torch.from_numpy(poses[steps:steps + 256]).to(dev)
+    cand = torch.from_numpy(synth.make_poses(256, seed=78)).to(dev)
     picks = []
     torch.cuda.synchronize()
     t0 = time.perf_counter()

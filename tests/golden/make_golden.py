@@ -55,6 +55,46 @@ def _img_state(img, HW):
     return accum.cpu().numpy(), ncon.cpu().numpy().view(np.uint32), ranges.cpu().numpy().view(np.uint32)
 
 
+def _walk(buf):
+    """obtain() of rasterizer_impl.h:21-28: consecutive arrays, each aligned to 128 bytes of ABSOLUTE address."""
+    base = buf.data_ptr()
+    state = {"p": base}
+
+    def take(nbytes):
+        o = (state["p"] + 127) // 128 * 128 - base
+        state["p"] = base + o + nbytes
+        return buf[o:o + nbytes]
+    return take
+
+
+def _geom_state(geom, P):
+    """GeometryState::fromChunk (rasterizer_impl.cu:155-170): depths f32[P], clamped bool[3P], internal_radii i32[P],
+    means2D float2[P], cov3D f32[6P], conic_opacity float4[P], rgb f32[3P], tiles_touched u32[P], ..."""
+    import torch
+    take = _walk(geom)
+    depths = take(4 * P).view(torch.float32)
+    take(3 * P)
+    take(4 * P)
+    means2D = take(8 * P).view(torch.float32).reshape(P, 2)
+    cov3D = take(24 * P).view(torch.float32).reshape(P, 6)
+    conic_opacity = take(16 * P).view(torch.float32).reshape(P, 4)
+    take(12 * P)
+    tiles_touched = take(4 * P).view(torch.int32)
+    return (depths.cpu().numpy(), means2D.cpu().numpy(), cov3D.cpu().numpy(), conic_opacity.cpu().numpy(),
+            tiles_touched.cpu().numpy().view(np.uint32))
+
+
+def _binning_state(binning, R):
+    """BinningState::fromChunk (rasterizer_impl.cu:181-194): point_list u32[R], point_list_unsorted u32[R],
+    point_list_keys u64[R], point_list_keys_unsorted u64[R], ..."""
+    import torch
+    take = _walk(binning)
+    point_list = take(4 * R).view(torch.int32)
+    take(4 * R)
+    keys = take(8 * R).view(torch.int64)
+    return point_list.cpu().numpy().view(np.uint32), keys.cpu().numpy().view(np.uint64)
+
+
 def gpu(out_dir):
     import torch
     from oracle import build_ref, oracle as O
@@ -81,6 +121,13 @@ def gpu(out_dir):
         out = dict(P=P, W=W, H=H, seed=seed, ident=ident, num_rendered=R, color=color.cpu().numpy(),
                    radii=radii.cpu().numpy(), depth=depth.cpu().numpy(), final_T=final_T, n_contrib=n_contrib,
                    ranges=ranges[:2 * tiles].reshape(tiles, 2))
+        # the reference's own geometry and binning state (only rows of Gaussians with radii > 0 are ever written)
+        vis = (radii > 0).cpu().numpy()
+        depths, means2D, cov3D, conic_opacity, tiles_touched = _geom_state(geom, P)
+        point_list, point_keys = _binning_state(binning, R)
+        out.update(point_list=point_list, point_list_keys=point_keys, tiles_touched=np.where(vis, tiles_touched, 0),
+                   depths=np.where(vis, depths, 0), means2D=np.where(vis[:, None], means2D, 0),
+                   conic_opacity=np.where(vis[:, None], conic_opacity, 0))
         rng = np.random.default_rng(seed)
         dpix1 = (rng.normal(size=(3, H, W)) * 1e-3).astype(np.float32)
         for power, dpix in ((1, dpix1), (2, np.full((3, H, W), 1e-3, np.float32))):

@@ -151,6 +151,18 @@ def test_forward_backward_match_reference_extension(cuda, P, W, H, seed, ident):
         tiles = got["ranges"].shape[0]
         np.testing.assert_array_equal(got["ranges"], ref_ranges[:2 * tiles].reshape(tiles, 2))
         np.testing.assert_array_equal(got["n_contrib"], ref_nc)
+        # the reference's own GeometryState / BinningState (rasterizer_impl.cu:155-194): the sorted instance list and
+        # its (tile | depth) keys, tiles_touched and the per-Gaussian projection, bit for bit
+        from tests.golden.make_golden import _geom_state, _binning_state
+        r_depths, r_means2D, _, r_conic_op, r_tiles = _geom_state(geom, P)
+        r_list, r_keys = _binning_state(binning, R)
+        vis = radii.cpu().numpy() > 0
+        np.testing.assert_array_equal(got["point_list"], r_list)
+        np.testing.assert_array_equal(got["point_keys"].view(np.uint64), r_keys)
+        np.testing.assert_array_equal(got["tiles_touched"][vis], r_tiles[vis])
+        np.testing.assert_array_equal(got["depths"][vis], r_depths[vis])
+        np.testing.assert_array_equal(got["means2D"][vis], r_means2D[vis])
+        np.testing.assert_array_equal(got["conic_opacity"][vis], r_conic_op[vis])
         np.testing.assert_allclose(got["final_T"], ref_T, rtol=1e-5, atol=1e-8)
         np.testing.assert_allclose(got["color"], color.cpu().numpy(), rtol=IMG_RTOL, atol=IMG_ATOL)
         np.testing.assert_array_equal(got["depth"], depth.cpu().numpy())

@@ -45,6 +45,16 @@ def test_forward_matches_reference_golden(oracle, name):
     ok = np.abs(f.final_T - g["final_T"]) <= 1e-7 + 1e-4 * np.abs(g["final_T"])
     assert ok.mean() > 1 - 2e-3
     assert (f.depth == g["depth"]).mean() > 1 - 2e-3
+    # the reference's own GeometryState / BinningState (rasterizer_impl.cu:155-194): sorted instance list, its
+    # (tile | depth) keys and the per-Gaussian projection, bit for bit
+    assert "point_list" in g.files, "fixture predates the geometry / binning state dump: regenerate (make_golden.py gpu)"
+    np.testing.assert_array_equal(f.point_list, g["point_list"])
+    np.testing.assert_array_equal(f.keys, g["point_list_keys"])
+    np.testing.assert_array_equal(f.tiles_touched, g["tiles_touched"])
+    vis = g["radii"] > 0
+    np.testing.assert_array_equal(f.depths[vis], g["depths"][vis])
+    np.testing.assert_array_equal(f.means2D[vis], g["means2D"][vis])
+    np.testing.assert_array_equal(f.conic_opacity[vis], g["conic_opacity"][vis])
 
 
 @pytest.mark.parametrize("name", ["raster_a", "raster_b"])

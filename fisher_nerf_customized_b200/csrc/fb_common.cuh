@@ -70,6 +70,7 @@ struct Cam {
     float campos[3];
     float view[16];
     float proj[16];
+    float cull_k;       // bound on ||W J||^2 z^2 (see maybe_on_screen), 0 = no early cull
 };
 
 __host__ inline Cam make_cam(const fb_camera* c) {
@@ -85,6 +86,21 @@ __host__ inline Cam make_cam(const fb_camera* c) {
     k.sh_degree = c->sh_degree; k.sh_coeffs = c->sh_coeffs; k.prefiltered = c->prefiltered;
     for (int i = 0; i < 3; ++i) { k.bg[i] = c->bg[i]; k.campos[i] = c->campos[i]; }
     for (int i = 0; i < 16; ++i) { k.view[i] = c->viewmatrix[i]; k.proj[i] = c->projmatrix[i]; }
+    // ||W||_2^2 of the view's 3x3 block: 1 for a rigid transform (checked), its Frobenius norm otherwise
+    double wtw[3][3], fro = 0.0; bool rigid = true;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            double s = 0.0;
+            for (int r = 0; r < 3; ++r) s += (double)k.view[4 * i + r] * (double)k.view[4 * j + r];
+            wtw[i][j] = s;
+            if (fabs(s - (i == j ? 1.0 : 0.0)) > 1e-5) rigid = false;
+            if (i == j) fro += s;
+        }
+    (void)wtw;
+    const double lx = 1.3 * k.tanfovx, ly = 1.3 * k.tanfovy;
+    const double jb = (double)k.focal_x * k.focal_x * (1.0 + lx * lx) + (double)k.focal_y * k.focal_y * (1.0 + ly * ly);
+    const double ck = (rigid ? 1.0 : fro) * jb * 1.02;
+    k.cull_k = (ck == ck && ck < 1e30) ? (float)ck : 0.f;
     return k;
 }
 
@@ -226,6 +242,26 @@ __device__ __forceinline__ int project_splat(const float3& p_orig, const float* 
     if ((s.x1 - s.x0) * (s.y1 - s.y0) == 0) return 0;
     s.depth = p_view.z;
     return 1;
+}
+
+// Conservative early test of stage 1: false only if project_splat would certainly return 0 (behind the near plane, or
+// the 3-sigma tile rectangle certainly empty), so skipping the projection for such a Gaussian changes nothing.
+// lambda_max(cov2D) <= ||W J||_F^2 tr(Sigma) + 0.3 with ||J||_F^2 <= (fx^2 (1 + lx^2) + fy^2 (1 + ly^2)) / z^2 (the
+// Jacobian's t.x/t.z, t.y/t.z are clamped to lx, ly = 1.3 tan(fov/2), forward.cu:82-87); the reference's radius is
+// ceil(3 sqrt(lambda)) with lambda <= lambda_max + sqrt(0.1) (its max(0.1, .) under the root, forward.cu:229-232).
+// The rectangle is empty iff px + radius < 1 or (px - radius) / 16 >= tiles_x (auxiliary.h:46-56), same in y.
+__device__ __forceinline__ bool maybe_on_screen(const float3& p_orig, float tr_sigma, const Cam& cam) {
+    const float3 p_view = xform4x3(p_orig, cam.view);
+    if (p_view.z <= 0.001f) return false;                                   // the reference's own near cull
+    if (cam.cull_k == 0.f) return true;
+    const float4 p_hom = xform4x4(p_orig, cam.proj);
+    const float p_w = 1.0f / __fadd_rn(p_hom.w, 0.0000001f);
+    const float px = ndc_to_pix_exact(__fmul_rn(p_hom.x, p_w), cam.W), py = ndc_to_pix_exact(__fmul_rn(p_hom.y, p_w), cam.H);
+    const float lam = cam.cull_k * tr_sigma / (p_view.z * p_view.z) + 0.65f;
+    const float rb = 3.0f * sqrtf(lam) * 1.001f + 1.5f;
+    const bool off = (px + rb < 0.f) || (px - rb > (float)(cam.tiles_x * FB_TILE_X) + 1.f) ||
+                     (py + rb < 0.f) || (py - rb > (float)(cam.tiles_y * FB_TILE_Y) + 1.f);
+    return !off;                                                            // NaN anywhere: not culled
 }
 
 // Exponent of a (pixel, Gaussian) pair, forward.cu:341 / backward.cu:968:

@@ -282,7 +282,10 @@ __device__ __forceinline__ void f2_acc(f32x2& acc, f32x2 a, f32x2 b) { acc = f2_
 #define FB_S2_LIST 1              // 1: surviving ring slots are compacted into a byte list (no BREV/FLO in the loop)
 #endif
 struct WarpQ2 { WarpQ q; unsigned char list[32]; unsigned char pad[96]; };
-#define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ2) * FB_S2_WPC)
+#ifndef FB_S2_SMEM_EXTRA
+#define FB_S2_SMEM_EXTRA 0        // extra dynamic shared memory per CTA: caps the resident CTAs per SM so that the other chunk
+#endif                            // lane's latency-bound kernels (scatter, sort) find registers and warp slots beside the sweep
+#define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ2) * FB_S2_WPC + FB_S2_SMEM_EXTRA)
 
 __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins bins, Cam cam, float grad_scale,
                                                                  float* __restrict__ partial) {

@@ -9,7 +9,8 @@ sc = synth.activate(synth.make_scene(P))
 t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
 gmap = fb.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"])
 rs = fb.setup_camera(256, 256, synth.intrinsics(256, 256), np.eye(4, dtype=np.float32))
-scorer = fb.FisherScorer(rs, C_H=4, views_per_chunk=64)
+scorer = fb.FisherScorer(rs, C_H=4, views_per_chunk=64, chunk_lanes=int(os.environ.get("FB_CHUNK_LANES", "2")))
+print("chunk_lanes", scorer.chunk_lanes)
 sh = fb.ShardedScorer(scorer)
 kf_all = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(32, seed=synth.SEED_POSES + 1))).cuda()
 c2w_all = torch.from_numpy(synth.make_poses(256, seed=synth.SEED_POSES)).cuda()

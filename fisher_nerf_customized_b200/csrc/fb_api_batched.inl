@@ -205,8 +205,7 @@ static DevState* dev_state() {
 // pair sweep issue-bound; scan, scatter and sort latency-bound).
 // When the caller's workspace holds two chunks (>= 2 x fb_score_workspace_bytes), consecutive chunks alternate between
 // the caller's stream and a library-owned stream, each in its own half of the workspace, so the latency-bound kernels
-// of one chunk run under the issue-bound kernels of the other.  A single chunk (K <= views_per_chunk) is split in two
-// half chunks so that small candidate sets use both lanes too.  Results are unchanged (each view's arithmetic is its
+// of one chunk run under the issue-bound kernels of the other.  Results are unchanged (each view's arithmetic is its
 // own); the caller's stream waits for the second lane before fb_score_candidates' work is complete on it.
 // While per-kernel profiling is enabled the chunks stay on one stream so that the event pairs time kernels alone.
 static int g_lanes_enabled = 1;
@@ -247,9 +246,10 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
         ds->score_attr = true; ds->sort_attr = true;
     }
     cudaStream_t st0 = st;
-    const int lanes = (g_lanes_enabled && !g_prof_on && K > 1 && workspace_bytes >= 2 * L.total) ? 2 : 1;
-    // chunk size: V views, or half the candidates when they all fit in one chunk and there are two lanes
-    const int Vstep = (lanes == 2 && K <= V) ? (K + 1) / 2 : V;
+    // (splitting a single small chunk over the two lanes was measured and dropped: 4 keyframes + 32 candidates per
+    //  planning step take 2.75 ms as two half chunks against 2.63 ms as one: launches that small are latency-bound)
+    const int lanes = (g_lanes_enabled && !g_prof_on && K > V && workspace_bytes >= 2 * L.total) ? 2 : 1;
+    const int Vstep = V;
     char* ws = (char*)workspace;
     FB_CUDA(cudaMemsetAsync(status_dev, 0, 8 * sizeof(int), st0));
     const size_t tc_bytes = (size_t)V * cam.tiles_x * cam.tiles_y * 4 * FB_TC_STRIDE;

@@ -174,20 +174,24 @@ struct Cov2D {
     M3     T;
     float  a, b, c;
 };
+// FAST: approximate divisions (div.approx, 2 ulp).  Only for values that never decide an integer: the scoring path's
+// coefficient phase (its conic and polynomial feed the pair sweep alone, held to rtol 1e-3 on the scores).
+template <bool FAST> __device__ __forceinline__ float fdiv(float a, float b) { return FAST ? __fdividef(a, b) : a / b; }
+template <bool FAST = false>
 __device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const float* cov6) {
     Cov2D o;
     float3 t = xform4x3(mean, cam.view);
     const float limx = 1.3f * cam.tanfovx;
     const float limy = 1.3f * cam.tanfovy;
-    o.txtz = t.x / t.z;
-    o.tytz = t.y / t.z;
+    o.txtz = fdiv<FAST>(t.x, t.z);
+    o.tytz = fdiv<FAST>(t.y, t.z);
     t.x = __fmul_rn(fminf(limx, fmaxf(-limx, o.txtz)), t.z);
     t.y = __fmul_rn(fminf(limy, fmaxf(-limy, o.tytz)), t.z);
     o.t = t;
     M3 J;
     const float tzz = __fmul_rn(t.z, t.z);
-    J.c[0][0] = cam.focal_x / t.z; J.c[0][1] = 0.f; J.c[0][2] = -__fmul_rn(cam.focal_x, t.x) / tzz;
-    J.c[1][0] = 0.f; J.c[1][1] = cam.focal_y / t.z; J.c[1][2] = -__fmul_rn(cam.focal_y, t.y) / tzz;
+    J.c[0][0] = fdiv<FAST>(cam.focal_x, t.z); J.c[0][1] = 0.f; J.c[0][2] = fdiv<FAST>(-__fmul_rn(cam.focal_x, t.x), tzz);
+    J.c[1][0] = 0.f; J.c[1][1] = fdiv<FAST>(cam.focal_y, t.z); J.c[1][2] = fdiv<FAST>(-__fmul_rn(cam.focal_y, t.y), tzz);
     J.c[2][0] = 0.f; J.c[2][1] = 0.f; J.c[2][2] = 0.f;
     M3 Wm;
     Wm.c[0][0] = cam.view[0]; Wm.c[0][1] = cam.view[4]; Wm.c[0][2] = cam.view[8];

@@ -38,20 +38,21 @@ struct GCtx {
     float m_w, mul1, mul2;
 };
 
+template <bool FAST = false>
 __device__ __forceinline__ GCtx make_ctx(const float3& mean, const float* cov6, const Cam& cam) {
     GCtx g;
-    g.c2 = cov2d(mean, cam, cov6);
+    g.c2 = cov2d<FAST>(mean, cam, cov6);
     const float limx = 1.3f * cam.tanfovx, limy = 1.3f * cam.tanfovy;
     g.xmul = (g.c2.txtz < -limx || g.c2.txtz > limx) ? 0.f : 1.f;
     g.ymul = (g.c2.tytz < -limy || g.c2.tytz > limy) ? 0.f : 1.f;
     const float a = g.c2.a, b = g.c2.b, c = g.c2.c;
     g.denom = a * c - b * b;
-    g.d2i = 1.0f / ((g.denom * g.denom) + 0.0000001f);
+    g.d2i = fdiv<FAST>(1.0f, (g.denom * g.denom) + 0.0000001f);
 #pragma unroll
     for (int i = 0; i < 6; ++i) g.V[i] = cov6[i];
     g.m = mean;
     float4 mh = xform4x4(mean, cam.proj);
-    g.m_w = 1.0f / (mh.w + 0.0000001f);
+    g.m_w = fdiv<FAST>(1.0f, mh.w + 0.0000001f);
     g.mul1 = (cam.proj[0] * mean.x + cam.proj[4] * mean.y + cam.proj[8] * mean.z + cam.proj[12]) * g.m_w * g.m_w;
     g.mul2 = (cam.proj[1] * mean.x + cam.proj[5] * mean.y + cam.proj[9] * mean.z + cam.proj[13]) * g.m_w * g.m_w;
     return g;
@@ -230,6 +231,7 @@ __device__ __forceinline__ int reduce16_slot(int lane) { return ((lane >> 4) & 1
 // instead of five passes through chain_geom with unit vectors (the compiler may not fold x*0, so each pass costs the
 // whole chain): K = d(cov2D a,b,c)/d(conic) with the -1/2 of phi_to_u folded in, D = d(t)/d(a,b,c) through
 // T = W J (backward.cu:333-407), the view rotation, and the projection path for the two mean2D columns (:566-574).
+template <bool FAST = false>
 __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam, float A, float B, float C,
                                                   float halfW, float halfH, float M[3][5]) {
     const float a = g.c2.a, b = g.c2.b, c = g.c2.c, denom = g.denom;
@@ -249,7 +251,7 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
     const float p10 = vw[1] * r0[0] + vw[5] * r0[1] + vw[9] * r0[2], p11 = vw[1] * r1[0] + vw[5] * r1[1] + vw[9] * r1[2];
     const float p20 = vw[2] * r0[0] + vw[6] * r0[1] + vw[10] * r0[2], p21 = vw[2] * r1[0] + vw[6] * r1[1] + vw[10] * r1[2];
     const float3 t = g.c2.t;
-    const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float tz = fdiv<FAST>(1.f, t.z), tz2 = tz * tz, tz3 = tz2 * tz;
     const float fx2 = -cam.focal_x * tz2, fy2 = -cam.focal_y * tz2;
     const float kx = g.xmul * fx2, ky = g.ymul * fy2;
     const float cx3 = 2.f * cam.focal_x * t.x * tz3, cy3 = 2.f * cam.focal_y * t.y * tz3;
@@ -273,7 +275,7 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
     }
 }
 
-template <int CH>
+template <int CH, bool FAST = false>
 __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, const SRCtx& sr, float A, float B, float C,
                                             float op, const float* __restrict__ w, float* coef) {
     constexpr int NOUT = (CH == 11) ? 10 : 3;
@@ -281,7 +283,7 @@ __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, con
     const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
     if (CH == 4) {
         float M[3][5];
-        mean_chain_matrix(ctx, cam, A, B, C, halfW, halfH, M);
+        mean_chain_matrix<FAST>(ctx, cam, A, B, C, halfW, halfH, M);
 #pragma unroll
         for (int i = 0; i < 5; ++i) { col[i][0] = M[0][i]; col[i][1] = M[1][i]; col[i][2] = M[2][i]; }
     } else
@@ -308,7 +310,7 @@ __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, con
     }
 #pragma unroll
     for (int m = 0; m < 13; ++m) coef[m] = 0.f;
-    coef[0] = w[3] / (op * op);
+    coef[0] = fdiv<FAST>(w[3], op * op);
     const int tab[5][5] = {{8, 9, 10, 4, 5}, {9, 10, 11, 5, 6}, {10, 11, 12, 6, 7}, {4, 5, 6, 1, 2}, {5, 6, 7, 2, 3}};
 #pragma unroll
     for (int i = 0; i < 5; ++i)

@@ -272,6 +272,9 @@ __device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int t
 #define FB_PS_VG 16
 #endif
 #define FB_PS_THREADS 256
+#ifndef FB_PS_FAST_COEF
+#define FB_PS_FAST_COEF 1      // approximate divisions in the coefficient phase (phase 2) of k_preprocess_score
+#endif
 #ifndef FB_PS_EARLY_CULL
 #define FB_PS_EARLY_CULL 1     // conservative per-warp visibility test before the projection (fb_common.cuh: maybe_on_screen)
 #endif
@@ -408,10 +411,11 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
             float c6[6];
 #pragma unroll
             for (int k = 0; k < 6; ++k) c6[k] = S.cov6[k][gi];
-            const GCtx ctx = make_ctx(pc, c6, cam);
-            // conic exactly as project_splat builds it
+            // nothing this phase produces decides an integer any more (its conic is read by the pair sweep only), so
+            // its divisions are approximate (FB_PS_FAST_COEF; the visible list, radii and keys come from phase 1)
+            const GCtx ctx = make_ctx<FB_PS_FAST_COEF != 0>(pc, c6, cam);
             const float det = __fmaf_rn(ctx.c2.a, ctx.c2.c, -__fmul_rn(ctx.c2.b, ctx.c2.b));
-            const float det_inv = 1.f / det;
+            const float det_inv = fdiv<FB_PS_FAST_COEF != 0>(1.f, det);
             const float ca = __fmul_rn(ctx.c2.c, det_inv), cb = __fmul_rn(-ctx.c2.b, det_inv), cc = __fmul_rn(ctx.c2.a, det_inv);
             const SRCtx sr = make_sr(make_float3(S.sc[0][gi], S.sc[1][gi], S.sc[2][gi]), cam.scale_modifier,
                                      make_float4(S.q[0][gi], S.q[1][gi], S.q[2][gi], S.q[3][gi]));
@@ -425,7 +429,7 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
                 for (int k = 0; k < CH; ++k) wv[k] = wsrc[k];
             }
             float coef[13];
-            score_coefs<CH>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
+            score_coefs<CH, FB_PS_FAST_COEF != 0>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
             float4* rb = bins.recB + ((size_t)(v0 + vv) * vcap + slot) * 5;
             // the scoring kernel evaluates G = ex2(dx (A dx + B dy) + C dy^2): conic pre-multiplied by
             // -log2(e)/2, -log2(e), -log2(e)/2 (the sign of the exponent is kept); r+g+b is the one colour

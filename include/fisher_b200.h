@@ -232,10 +232,10 @@ size_t fb_score_workspace_bytes(int P, int width, int height, int views_per_chun
 size_t fb_hessian_workspace_bytes(int P, int width, int height, int views_per_chunk,
                                   long long inst_capacity);
 
-/* Chunk lanes.  If `workspace_bytes` >= 2 * fb_score_workspace_bytes(...) and K > 1,
+/* Chunk lanes.  If `workspace_bytes` >= 2 * fb_score_workspace_bytes(...) and K > views_per_chunk,
  * fb_score_candidates alternates consecutive chunks between the caller's stream and a library-owned
  * stream, each in its own half of the workspace (the latency-bound binning kernels of one chunk run
- * under the issue-bound kernels of the other; K <= views_per_chunk is split into two half chunks); the
+ * under the issue-bound kernels of the other); the
  * caller's stream waits for both before the call's work is complete on it.  Results do not change.
  * fb_score_set_lanes(0) keeps every chunk on the caller's stream; so does fb_profile_enable(1), so that
  * its event pairs time kernels alone.  Library state (the second stream, function attributes) is kept per

@@ -6,6 +6,14 @@
 #ifndef FB_DROPIN_WARP
 #define FB_DROPIN_WARP 1
 #endif
+// FB_SCATTER_CTA (default): keys are scattered by k_scatter_keys_cta (shared-memory aggregation: one returning global
+// atomic per (CTA, tile)) whenever the view has <= 1024 tiles; 0 keeps the warp-aggregated k_scatter_keys everywhere.
+#ifndef FB_SCATTER_CTA
+#define FB_SCATTER_CTA 1
+#endif
+#ifndef FB_SC_GRID
+#define FB_SC_GRID 2              // CTAs per SM and view in the grid of k_scatter_keys_cta
+#endif
 #include "fb_backward.cuh"
 #include "fb_stage5.cuh"
 #include "fb_blocks.cuh"
@@ -204,6 +212,10 @@ int fb_raster_forward_render2(const fb_camera* c, const fb_gaussians* g, const f
     ImageLayout IL = image_layout(cam.W, cam.H);
     if (num_rendered > 0) {
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 8) sblocks = 148 * 8;
+#if FB_SCATTER_CTA
+        if (b.tiles <= FB_SC_MAX_TILES) { FB_PROF(FB_K_SCATTER); k_scatter_keys_cta<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
+        else
+#endif
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, 1), 256, 0, st>>>(b, cam); }
         FB_LAUNCH_CHECK();
         static bool attr_set = false;

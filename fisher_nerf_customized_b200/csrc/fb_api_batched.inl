@@ -284,8 +284,16 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<Vc, 1024, 0, st>>>(b); }
         FB_LAUNCH_CHECK();
         ++g_launches; k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
-        int sblocks = (int)((b.vis_stride + 255) / 256); if (sblocks > 148 * 2) sblocks = 148 * 2;
-        { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
+#if FB_SCATTER_CTA
+        if (b.tiles <= FB_SC_MAX_TILES) {
+            int sblocks = (int)((b.vis_stride + 256 * FB_SC_EPT - 1) / (256 * FB_SC_EPT)); if (sblocks > 148 * FB_SC_GRID) sblocks = 148 * FB_SC_GRID;
+            { FB_PROF(FB_K_SCATTER); k_scatter_keys_cta<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
+        } else
+#endif
+        {
+            int sblocks = (int)((b.vis_stride + 255) / 256); if (sblocks > 148 * 2) sblocks = 148 * 2;
+            { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
+        }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
@@ -348,6 +356,10 @@ int fb_accumulate_hessian_sets(const fb_camera* c, const fb_map* map, const floa
         { FB_PROF(FB_K_SCAN); k_scan_tiles<<<Vc, 1024, 0, st>>>(b); }
         ++g_launches; k_status_update<<<1, 32, 0, st>>>(b.total, b.vis_count, b.V, status_dev);
         int sblocks = (P + 255) / 256; if (sblocks > 148 * 2) sblocks = 148 * 2;
+#if FB_SCATTER_CTA
+        if (b.tiles <= FB_SC_MAX_TILES) { FB_PROF(FB_K_SCATTER); k_scatter_keys_cta<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
+        else
+#endif
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();

@@ -577,6 +577,63 @@ __global__ void __launch_bounds__(256) k_scatter_keys(Bins bins, Cam cam) {
     }
 }
 
+// CTA-aggregated form of the scatter (tiles <= FB_SC_MAX_TILES): a CTA takes FB_SC_EPT * 256 consecutive entries of a
+// view's visible list, counts their instances per tile with SHARED-memory atomics, claims each touched tile's room
+// with ONE global atomicSub per (CTA, tile) -- the warp-aggregated form above issues one per (warp, tile), ~13x as many
+// returning L2 atomics, and is bound by their latency -- and writes the keys at ranks handed out again in shared memory.
+// The order inside a segment is arbitrary either way; k_sort_tiles establishes it.
+#define FB_SC_MAX_TILES 1024
+#ifndef FB_SC_EPT
+#define FB_SC_EPT 1
+#endif
+__global__ void __launch_bounds__(256) k_scatter_keys_cta(Bins bins, Cam cam) {
+    __shared__ unsigned cnt[FB_SC_MAX_TILES];
+    __shared__ unsigned base[FB_SC_MAX_TILES];
+    const int v = blockIdx.y, tid = threadIdx.x, tiles = bins.tiles;
+    uint32_t* tc = bins.tile_count + (size_t)v * tiles * FB_TC_STRIDE;
+    if (bins.total[1]) {
+        if (blockIdx.x == 0)
+            for (int i = tid; i < tiles; i += blockDim.x) tc[i * FB_TC_STRIDE] = 0u;
+        return;
+    }
+    const unsigned nvis = bins.vis_count[v];
+    const uint2* tr = bins.tile_range + (size_t)v * tiles;
+    const unsigned per_cta = 256u * FB_SC_EPT;
+    for (unsigned start = blockIdx.x * per_cta; start < nvis; start += gridDim.x * per_cta) {
+        for (int t = tid; t < tiles; t += 256) cnt[t] = 0u;
+        __syncthreads();
+        uint4 e[FB_SC_EPT];
+#pragma unroll
+        for (int k = 0; k < FB_SC_EPT; ++k) {
+            const unsigned i = start + k * 256u + tid;
+            e[k] = make_uint4(0u, 0u, 0u, 0u);
+            if (i < nvis) e[k] = bins.vis_list[(size_t)v * bins.vis_stride + i];
+            const int x0 = e[k].z & 0xff, y0 = (e[k].z >> 8) & 0xff, x1 = (e[k].z >> 16) & 0xff, y1 = e[k].z >> 24;
+            for (int y = y0; y < y1; ++y)
+                for (int x = x0; x < x1; ++x) atomicAdd(&cnt[y * cam.tiles_x + x], 1u);
+        }
+        __syncthreads();
+        for (int t = tid; t < tiles; t += 256) {
+            const unsigned c = cnt[t];
+            if (c) base[t] = tr[t].x + atomicSub(&tc[t * FB_TC_STRIDE], c) - 1u;      // position of this CTA's rank 0
+            cnt[t] = 0u;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < FB_SC_EPT; ++k) {
+            const unsigned i = start + k * 256u + tid;
+            const int x0 = e[k].z & 0xff, y0 = (e[k].z >> 8) & 0xff, x1 = (e[k].z >> 16) & 0xff, y1 = e[k].z >> 24;
+            const u64 key = ((u64)e[k].y << 32) | (u64)(bins.key_is_slot ? i : e[k].x);
+            for (int y = y0; y < y1; ++y)
+                for (int x = x0; x < x1; ++x) {
+                    const int t = y * cam.tiles_x + x;
+                    bins.keys[base[t] - atomicAdd(&cnt[t], 1u)] = key;
+                }
+        }
+        __syncthreads();
+    }
+}
+
 // ---- stage 2c: in-CTA sort of one tile segment ----------------------------------------------
 // Stable LSD radix sort of the 8-byte keys (depth_bits<<32 | gaussian_id) on the 32 DEPTH bits only
 // (four 8-bit passes; a pass whose digit is the same for every key is skipped), followed by a

@@ -71,6 +71,7 @@ struct Cam {
     float view[16];
     float proj[16];
     float cull_k;       // bound on ||W J||^2 z^2 (see maybe_on_screen), 0 = no early cull
+    int   view_ident;   // the view matrix is exactly the identity
 };
 
 __host__ inline Cam make_cam(const fb_camera* c) {
@@ -101,6 +102,8 @@ __host__ inline Cam make_cam(const fb_camera* c) {
     const double jb = (double)k.focal_x * k.focal_x * (1.0 + lx * lx) + (double)k.focal_y * k.focal_y * (1.0 + ly * ly);
     const double ck = (rigid ? 1.0 : fro) * jb * 1.02;
     k.cull_k = (ck == ck && ck < 1e30) ? (float)ck : 0.f;
+    k.view_ident = 1;
+    for (int i = 0; i < 16; ++i) if (k.view[i] != ((i % 5 == 0) ? 1.0f : 0.0f)) k.view_ident = 0;
     return k;
 }
 
@@ -177,10 +180,13 @@ struct Cov2D {
 // FAST: approximate divisions (div.approx, 2 ulp).  Only for values that never decide an integer: the scoring path's
 // coefficient phase (its conic and polynomial feed the pair sweep alone, held to rtol 1e-3 on the scores).
 template <bool FAST> __device__ __forceinline__ float fdiv(float a, float b) { return FAST ? __fdividef(a, b) : a / b; }
-template <bool FAST = false>
+// IDENT: the view matrix is exactly the identity (the scoring path: the caller's camera is set up with w2c = I and the
+// candidate pose is applied to the means, gaussian.py:1523-1527), so t = mean and T = W J = J; the products with 0 and 1
+// are written out.  Only used together with FAST (values that decide no integer).
+template <bool FAST = false, bool IDENT = false>
 __device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const float* cov6) {
     Cov2D o;
-    float3 t = xform4x3(mean, cam.view);
+    float3 t = IDENT ? mean : xform4x3(mean, cam.view);
     const float limx = 1.3f * cam.tanfovx;
     const float limy = 1.3f * cam.tanfovy;
     o.txtz = fdiv<FAST>(t.x, t.z);
@@ -193,6 +199,17 @@ __device__ __forceinline__ Cov2D cov2d(const float3& mean, const Cam& cam, const
     J.c[0][0] = fdiv<FAST>(cam.focal_x, t.z); J.c[0][1] = 0.f; J.c[0][2] = fdiv<FAST>(-__fmul_rn(cam.focal_x, t.x), tzz);
     J.c[1][0] = 0.f; J.c[1][1] = fdiv<FAST>(cam.focal_y, t.z); J.c[1][2] = fdiv<FAST>(-__fmul_rn(cam.focal_y, t.y), tzz);
     J.c[2][0] = 0.f; J.c[2][1] = 0.f; J.c[2][2] = 0.f;
+    if (IDENT) {
+        o.T = J;
+        const float j00 = J.c[0][0], j02 = J.c[0][2], j11 = J.c[1][1], j12 = J.c[1][2];
+        const float u0 = j00 * cov6[0] + j02 * cov6[2], u2 = j00 * cov6[2] + j02 * cov6[5];       // (J row 0) V, x and z parts
+        const float u1 = j00 * cov6[1] + j02 * cov6[4];
+        const float w1 = j11 * cov6[3] + j12 * cov6[4], w2 = j11 * cov6[4] + j12 * cov6[5];
+        o.a = (u0 * j00 + u2 * j02) + 0.3f;
+        o.b = u1 * j11 + u2 * j12;
+        o.c = (w1 * j11 + w2 * j12) + 0.3f;
+        return o;
+    }
     M3 Wm;
     Wm.c[0][0] = cam.view[0]; Wm.c[0][1] = cam.view[4]; Wm.c[0][2] = cam.view[8];
     Wm.c[1][0] = cam.view[1]; Wm.c[1][1] = cam.view[5]; Wm.c[1][2] = cam.view[9];

@@ -38,10 +38,10 @@ struct GCtx {
     float m_w, mul1, mul2;
 };
 
-template <bool FAST = false>
+template <bool FAST = false, bool IDENT = false>
 __device__ __forceinline__ GCtx make_ctx(const float3& mean, const float* cov6, const Cam& cam) {
     GCtx g;
-    g.c2 = cov2d<FAST>(mean, cam, cov6);
+    g.c2 = cov2d<FAST, IDENT>(mean, cam, cov6);
     const float limx = 1.3f * cam.tanfovx, limy = 1.3f * cam.tanfovy;
     g.xmul = (g.c2.txtz < -limx || g.c2.txtz > limx) ? 0.f : 1.f;
     g.ymul = (g.c2.tytz < -limy || g.c2.tytz > limy) ? 0.f : 1.f;
@@ -231,7 +231,7 @@ __device__ __forceinline__ int reduce16_slot(int lane) { return ((lane >> 4) & 1
 // instead of five passes through chain_geom with unit vectors (the compiler may not fold x*0, so each pass costs the
 // whole chain): K = d(cov2D a,b,c)/d(conic) with the -1/2 of phi_to_u folded in, D = d(t)/d(a,b,c) through
 // T = W J (backward.cu:333-407), the view rotation, and the projection path for the two mean2D columns (:566-574).
-template <bool FAST = false>
+template <bool FAST = false, bool IDENT = false>
 __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam, float A, float B, float C,
                                                   float halfW, float halfH, float M[3][5]) {
     const float a = g.c2.a, b = g.c2.b, c = g.c2.c, denom = g.denom;
@@ -242,14 +242,20 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
     K[1][0] = 2.f * h * (b * c);   K[1][1] = -2.f * h * (denom + 2.f * b * b);  K[1][2] = 2.f * h * (a * b);
     K[2][0] = h * dmac;            K[2][1] = h * (2.f * a * b);                 K[2][2] = h * (-a * a);
     const float V00 = g.V[0], V01 = g.V[1], V02 = g.V[2], V11 = g.V[3], V12 = g.V[4], V22 = g.V[5];
-    const float r0[3] = {T.c[0][0] * V00 + T.c[0][1] * V01 + T.c[0][2] * V02, T.c[0][0] * V01 + T.c[0][1] * V11 + T.c[0][2] * V12,
-                         T.c[0][0] * V02 + T.c[0][1] * V12 + T.c[0][2] * V22};
-    const float r1[3] = {T.c[1][0] * V00 + T.c[1][1] * V01 + T.c[1][2] * V02, T.c[1][0] * V01 + T.c[1][1] * V11 + T.c[1][2] * V12,
-                         T.c[1][0] * V02 + T.c[1][1] * V12 + T.c[1][2] * V22};
+    float r0[3], r1[3];
+    if (IDENT) {            // T = J: T.c[0][1] = T.c[1][0] = 0
+        r0[0] = T.c[0][0] * V00 + T.c[0][2] * V02; r0[1] = T.c[0][0] * V01 + T.c[0][2] * V12; r0[2] = T.c[0][0] * V02 + T.c[0][2] * V22;
+        r1[0] = T.c[1][1] * V01 + T.c[1][2] * V02; r1[1] = T.c[1][1] * V11 + T.c[1][2] * V12; r1[2] = T.c[1][1] * V12 + T.c[1][2] * V22;
+    } else {
+        r0[0] = T.c[0][0] * V00 + T.c[0][1] * V01 + T.c[0][2] * V02; r0[1] = T.c[0][0] * V01 + T.c[0][1] * V11 + T.c[0][2] * V12;
+        r0[2] = T.c[0][0] * V02 + T.c[0][1] * V12 + T.c[0][2] * V22;
+        r1[0] = T.c[1][0] * V00 + T.c[1][1] * V01 + T.c[1][2] * V02; r1[1] = T.c[1][0] * V01 + T.c[1][1] * V11 + T.c[1][2] * V12;
+        r1[2] = T.c[1][0] * V02 + T.c[1][1] * V12 + T.c[1][2] * V22;
+    }
     const float* vw = cam.view;
-    const float p00 = vw[0] * r0[0] + vw[4] * r0[1] + vw[8] * r0[2], p01 = vw[0] * r1[0] + vw[4] * r1[1] + vw[8] * r1[2];
-    const float p10 = vw[1] * r0[0] + vw[5] * r0[1] + vw[9] * r0[2], p11 = vw[1] * r1[0] + vw[5] * r1[1] + vw[9] * r1[2];
-    const float p20 = vw[2] * r0[0] + vw[6] * r0[1] + vw[10] * r0[2], p21 = vw[2] * r1[0] + vw[6] * r1[1] + vw[10] * r1[2];
+    const float p00 = IDENT ? r0[0] : vw[0] * r0[0] + vw[4] * r0[1] + vw[8] * r0[2], p01 = IDENT ? r1[0] : vw[0] * r1[0] + vw[4] * r1[1] + vw[8] * r1[2];
+    const float p10 = IDENT ? r0[1] : vw[1] * r0[0] + vw[5] * r0[1] + vw[9] * r0[2], p11 = IDENT ? r1[1] : vw[1] * r1[0] + vw[5] * r1[1] + vw[9] * r1[2];
+    const float p20 = IDENT ? r0[2] : vw[2] * r0[0] + vw[6] * r0[1] + vw[10] * r0[2], p21 = IDENT ? r1[2] : vw[2] * r1[0] + vw[6] * r1[1] + vw[10] * r1[2];
     const float3 t = g.c2.t;
     const float tz = fdiv<FAST>(1.f, t.z), tz2 = tz * tz, tz3 = tz2 * tz;
     const float fx2 = -cam.focal_x * tz2, fy2 = -cam.focal_y * tz2;
@@ -268,14 +274,14 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
 #pragma unroll
-        for (int j = 0; j < 3; ++j) M[i][j] = vw[4 * i] * E[0][j] + vw[4 * i + 1] * E[1][j] + vw[4 * i + 2] * E[2][j];
+        for (int j = 0; j < 3; ++j) M[i][j] = IDENT ? E[i][j] : vw[4 * i] * E[0][j] + vw[4 * i + 1] * E[1][j] + vw[4 * i + 2] * E[2][j];
         const float px = pr[4 * i] * g.m_w - pr[4 * i + 3] * g.mul1, py = pr[4 * i + 1] * g.m_w - pr[4 * i + 3] * g.mul2;
         M[i][3] = -(px * (A * halfW) + py * (B * halfH));
         M[i][4] = -(px * (B * halfW) + py * (C * halfH));
     }
 }
 
-template <int CH, bool FAST = false>
+template <int CH, bool FAST = false, bool IDENT = false>
 __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, const SRCtx& sr, float A, float B, float C,
                                             float op, const float* __restrict__ w, float* coef) {
     constexpr int NOUT = (CH == 11) ? 10 : 3;
@@ -283,7 +289,7 @@ __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, con
     const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
     if (CH == 4) {
         float M[3][5];
-        mean_chain_matrix<FAST>(ctx, cam, A, B, C, halfW, halfH, M);
+        mean_chain_matrix<FAST, IDENT>(ctx, cam, A, B, C, halfW, halfH, M);
 #pragma unroll
         for (int i = 0; i < 5; ++i) { col[i][0] = M[0][i]; col[i][1] = M[1][i]; col[i][2] = M[2][i]; }
     } else
@@ -312,13 +318,22 @@ __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, con
     for (int m = 0; m < 13; ++m) coef[m] = 0.f;
     coef[0] = fdiv<FAST>(w[3], op * op);
     const int tab[5][5] = {{8, 9, 10, 4, 5}, {9, 10, 11, 5, 6}, {10, 11, 12, 6, 7}, {4, 5, 6, 1, 2}, {5, 6, 7, 2, 3}};
+    // C_H = 4: the columns are pre-multiplied by the weights (45 FMAs for the 15 products instead of 135 operations);
+    // C_H = 11 keeps the three-factor form (a second 5x10 array would not fit the register budget)
+    float colw[5][CH == 4 ? NOUT : 1];
+    if (CH == 4) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i)
+#pragma unroll
+            for (int k = 0; k < NOUT; ++k) colw[i][k] = wk[k] * col[i][k];
+    }
 #pragma unroll
     for (int i = 0; i < 5; ++i)
 #pragma unroll
         for (int j = i; j < 5; ++j) {
             float b = 0.f;
 #pragma unroll
-            for (int k = 0; k < NOUT; ++k) b += wk[k] * col[i][k] * col[j][k];
+            for (int k = 0; k < NOUT; ++k) b += (CH == 4) ? colw[i][CH == 4 ? k : 0] * col[j][k] : wk[k] * col[i][k] * col[j][k];
             coef[tab[i][j]] += (i == j) ? b : 2.f * b;
         }
 }

@@ -18,6 +18,7 @@
 #include "fb_layout.cuh"
 #include "fb_fisher.cuh"
 #include <cuda_fp16.h>
+#include <type_traits>
 
 namespace fb {
 
@@ -272,6 +273,9 @@ __device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int t
 #define FB_PS_VG 16
 #endif
 #define FB_PS_THREADS 256
+#ifndef FB_PS_IDENT
+#define FB_PS_IDENT 1         // written-out products for an identity view matrix in the coefficient phase
+#endif
 #ifndef FB_PS_FAST_COEF
 #define FB_PS_FAST_COEF 1      // approximate divisions in the coefficient phase (phase 2) of k_preprocess_score
 #endif
@@ -281,6 +285,17 @@ __device__ __forceinline__ void warp_tiles(int x0, int y0, int x1, int y1, int t
 #ifndef FB_PS_SPLIT
 #define FB_PS_SPLIT 4          // view groups of one Gaussian group go to up to this many blocks (grid.y)
 #endif
+// conic (as project_splat forms it) and the 13 scoring coefficients of one visible (Gaussian, view) pair
+template <int CH, bool FC, bool ID>
+__device__ __forceinline__ void build_coefs(const float3& pc, const float* c6, const Cam& cam, const SRCtx& sr, float op,
+                                            const float* wv, float* coef, float& ca, float& cb, float& cc) {
+    const GCtx ctx = make_ctx<FC, ID>(pc, c6, cam);
+    const float det = __fmaf_rn(ctx.c2.a, ctx.c2.c, -__fmul_rn(ctx.c2.b, ctx.c2.b));
+    const float det_inv = fdiv<FC>(1.f, det);
+    ca = __fmul_rn(ctx.c2.c, det_inv); cb = __fmul_rn(-ctx.c2.b, det_inv); cc = __fmul_rn(ctx.c2.a, det_inv);
+    score_coefs<CH, FC, ID>(ctx, cam, sr, ca, cb, cc, op, wv, coef);
+}
+
 template <int CH> struct PSmem {
     float p[3][FB_PS_THREADS], cov6[6][FB_PS_THREADS], op[FB_PS_THREADS], sc[3][FB_PS_THREADS], q[4][FB_PS_THREADS],
         col[3][FB_PS_THREADS], w[CH][FB_PS_THREADS];
@@ -412,11 +427,8 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
 #pragma unroll
             for (int k = 0; k < 6; ++k) c6[k] = S.cov6[k][gi];
             // nothing this phase produces decides an integer any more (its conic is read by the pair sweep only), so
-            // its divisions are approximate (FB_PS_FAST_COEF; the visible list, radii and keys come from phase 1)
-            const GCtx ctx = make_ctx<FB_PS_FAST_COEF != 0>(pc, c6, cam);
-            const float det = __fmaf_rn(ctx.c2.a, ctx.c2.c, -__fmul_rn(ctx.c2.b, ctx.c2.b));
-            const float det_inv = fdiv<FB_PS_FAST_COEF != 0>(1.f, det);
-            const float ca = __fmul_rn(ctx.c2.c, det_inv), cb = __fmul_rn(-ctx.c2.b, det_inv), cc = __fmul_rn(ctx.c2.a, det_inv);
+            // its divisions are approximate (FB_PS_FAST_COEF; the visible list, radii and keys come from phase 1) and an
+            // identity view matrix (the scoring path's usual camera) takes the written-out products
             const SRCtx sr = make_sr(make_float3(S.sc[0][gi], S.sc[1][gi], S.sc[2][gi]), cam.scale_modifier,
                                      make_float4(S.q[0][gi], S.q[1][gi], S.q[2][gi], S.q[3][gi]));
             float wv[CH];
@@ -428,8 +440,14 @@ __global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(
 #pragma unroll
                 for (int k = 0; k < CH; ++k) wv[k] = wsrc[k];
             }
-            float coef[13];
-            score_coefs<CH, FB_PS_FAST_COEF != 0>(ctx, cam, sr, ca, cb, cc, S.op[gi], wv, coef);
+            float coef[13], ca, cb, cc;
+            constexpr bool FC = FB_PS_FAST_COEF != 0;
+            if constexpr (CH == 4 && FC && FB_PS_IDENT) {
+                if (cam.view_ident) build_coefs<CH, FC, true>(pc, c6, cam, sr, S.op[gi], wv, coef, ca, cb, cc);
+                else build_coefs<CH, FC, false>(pc, c6, cam, sr, S.op[gi], wv, coef, ca, cb, cc);
+            } else {
+                build_coefs<CH, FC, false>(pc, c6, cam, sr, S.op[gi], wv, coef, ca, cb, cc);
+            }
             float4* rb = bins.recB + ((size_t)(v0 + vv) * vcap + slot) * 5;
             // the scoring kernel evaluates G = ex2(dx (A dx + B dy) + C dy^2): conic pre-multiplied by
             // -log2(e)/2, -log2(e), -log2(e)/2 (the sign of the exponent is kept); r+g+b is the one colour

@@ -18,6 +18,6 @@ CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
 timeout 600 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_ -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
 echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_tile_score|k_preprocess|k_scatter_keys|k_sort_tiles' -s ${NCU_SKIP:-100} -c 8 -o gpurun_out/${TAG}_prof $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_tile_score|k_preprocess|k_scatter_keys|k_sort_tiles' -s ${NCU_SKIP:-40} -c 8 -o gpurun_out/${TAG}_prof $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out | tail -20

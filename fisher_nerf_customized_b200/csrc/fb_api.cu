@@ -1,11 +1,6 @@
 // fb_api.cu -- the C ABI (include/fisher_b200.h) over the sm_100a kernels.  No torch types here.
 #include "fb_score.cuh"
 #include "fb_render_warp.cuh"
-// FB_DROPIN_WARP (default): the single-view drop-in renders with k_render_warp / k_bwd_warp; 0 selects the
-// block-synchronous kernels k_render_fwd / k_bwd_tiles (same results, kept for A/B runs).
-#ifndef FB_DROPIN_WARP
-#define FB_DROPIN_WARP 1
-#endif
 // FB_SCATTER_CTA (default): keys are scattered by k_scatter_keys_cta (shared-memory aggregation: one returning global
 // atomic per (CTA, tile)) whenever the view has <= 1024 tiles; 0 keeps the warp-aggregated k_scatter_keys everywhere.
 #ifndef FB_SCATTER_CTA
@@ -228,19 +223,12 @@ int fb_raster_forward_render2(const fb_camera* c, const fb_gaussians* g, const f
         FB_LAUNCH_CHECK();
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);
-#if FB_DROPIN_WARP
     if (extra_colors)
         { FB_PROF(FB_K_RENDER); k_render_warp<1><<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
             b, cam, feat, extra_colors, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_extra, out_depth); }
     else
         { FB_PROF(FB_K_RENDER); k_render_warp<0><<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
             b, cam, feat, nullptr, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, nullptr, out_depth); }
-#else
-    if (extra_colors) return FB_E_INVALID;
-    b.tile_order = nullptr;
-    { FB_PROF(FB_K_RENDER); k_render_fwd<<<dim3(cam.tiles_x, cam.tiles_y), FB_TILE_PIX, 0, st>>>(
-        b, cam, feat, (float*)((char*)image + IL.final_T), (uint32_t*)((char*)image + IL.n_contrib), out_color, out_depth); }
-#endif
     FB_LAUNCH_CHECK();
     return FB_OK;
 }
@@ -265,14 +253,14 @@ int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* 
     cudaStream_t st = (cudaStream_t)stream_;
     if (!c || !dL_dpix) return FB_E_INVALID;
     if ((extra_colors == nullptr) != (dL_dextra == nullptr)) return FB_E_INVALID;
-    if (extra_colors && (power != 1 || !FB_DROPIN_WARP)) return FB_E_INVALID;   // the two renders' gradients add only for power 1
+    if (extra_colors && power != 1) return FB_E_INVALID;   // the two renders' gradients add only for power 1
     int rc = check_gauss(g);
     if (rc) return rc;
     const int P = g->P;
     if (P == 0 || num_rendered == 0) return FB_OK;
     if (!geom || !image || !inst || !radii || !scratch) return FB_E_INVALID;
     const bool pairwise = (power != 1 && power != 2) || (g->shs && c->sh_degree > 0);
-    if (pairwise && (extra_colors || !FB_DROPIN_WARP)) return FB_E_INVALID;
+    if (pairwise && extra_colors) return FB_E_INVALID;
     if (scratch_bytes < fb_backward_scratch_bytes(P, num_rendered, power, pairwise ? 1 : 0)) return FB_E_WORKSPACE;
     Cam cam = make_cam(c);
     Bins b = single_bins(P, cam, (void*)geom, (void*)image, (void*)inst, (long long)num_rendered);
@@ -301,23 +289,13 @@ int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* 
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((const char*)geom + GL.rgb);
     const float* fT = (const float*)((const char*)image + IL.final_T);
     const uint32_t* nc = (const uint32_t*)((const char*)image + IL.n_contrib);
-#if FB_DROPIN_WARP
     dim3 grid(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), 1);
-#else
-    b.tile_order = nullptr;
-    dim3 grid(cam.tiles_x, cam.tiles_y);
-#endif
     GradOut o{dL_dmeans2D, dL_dconic, dL_dopacity, dL_dcolors, dL_dmeans3D, dL_dcov3D, dL_dscales, dL_drotations, dL_dextra_colors};
     if (power == 2) {
-#if FB_DROPIN_WARP
         { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<true, 0><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, nullptr, fT, nc, dL_dpix, nullptr, mom); }
-#else
-        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<true, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
-#endif
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_EXPAND); k_expand_grads<true><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     } else {
-#if FB_DROPIN_WARP
         if (extra_colors) {
             { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false, 1><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, extra_colors, fT, nc, dL_dpix, dL_dextra, mom); }
             FB_LAUNCH_CHECK();
@@ -326,9 +304,6 @@ int fb_raster_backward2(const fb_camera* c, const fb_gaussians* g, const float* 
             return FB_OK;
         }
         { FB_PROF(FB_K_BWD_TILES); k_bwd_warp<false, 0><<<grid, 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(b, cam, feat, nullptr, fT, nc, dL_dpix, nullptr, mom); }
-#else
-        { FB_PROF(FB_K_BWD_TILES); k_bwd_tiles<false, true><<<grid, FB_TILE_PIX, 0, st>>>(b, cam, feat, fT, nc, dL_dpix, mom); }
-#endif
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_EXPAND); k_expand_grads<false><<<(P + 127) / 128, 128, 0, st>>>(P, to_in(g), cam, b.recs, radii, mom, o); }
     }

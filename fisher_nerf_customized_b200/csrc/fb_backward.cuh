@@ -1,61 +1,9 @@
-// fb_backward.cuh -- drop-in backward: tile walk -> per-Gaussian moment rows -> expansion into the
-// reference's nine gradient tensors (RasterizeGaussiansBackwardCUDA, DGR/rasterize_points.cu:117-196).
+// fb_backward.cuh -- drop-in backward: per-Gaussian moment rows (k_bwd_warp, fb_render_warp.cuh) -> expansion into the
+// reference's nine gradient tensors; the per-pair fallback for other powers / SH colours (RasterizeGaussiansBackwardCUDA, DGR/rasterize_points.cu:117-196).
 #pragma once
-#include "fb_fisher_tile.cuh"
+#include "fb_fisher.cuh"
 
 namespace fb {
-
-struct MomFlush {
-    float* mom;  // [P][16]
-    __device__ __forceinline__ void operator()(int, int gid, const float* row) const {
-        float4* dst = reinterpret_cast<float4*>(mom + (size_t)gid * FB_NACC);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            float4 v = *reinterpret_cast<const float4*>(row + 4 * k);
-            if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) atomicAdd(dst + k, v);  // red.global.add.v4.f32
-        }
-    }
-};
-
-template <bool P2, bool COLOR>
-__global__ void __launch_bounds__(FB_TILE_PIX) k_bwd_tiles(Bins bins, Cam cam, const float* __restrict__ colors,
-                                                          const float* __restrict__ final_T,
-                                                          const uint32_t* __restrict__ n_contrib,
-                                                          const float* __restrict__ dL_dpix, float* __restrict__ mom) {
-    __shared__ BwdSmem sm;
-    // blockIdx.z = view of a batch: per-view records, ranges, pixel state and moment rows; dL_dpix is shared
-    int tx = blockIdx.x, ty = blockIdx.y, v = blockIdx.z;
-    if (bins.tile_order) {            // batched: heaviest (view, tile) slots first
-        const unsigned slot = bins.tile_order[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x];
-        v = (int)(slot / (unsigned)bins.tiles);
-        const int t = (int)(slot % (unsigned)bins.tiles);
-        tx = t % cam.tiles_x; ty = t / cam.tiles_x;
-    }
-    {
-        const size_t HWv = (size_t)cam.W * cam.H * v;
-        final_T += HWv; n_contrib += HWv;
-        bins.recs += (size_t)v * bins.P;
-        bins.tile_range += (size_t)v * bins.tiles;
-        mom += (size_t)v * bins.P * FB_NACC;
-    }
-    const int px = tx * FB_TILE_X + threadIdx.x % FB_TILE_X, py = ty * FB_TILE_Y + threadIdx.x / FB_TILE_X;
-    const bool inside = px < cam.W && py < cam.H;
-    const int pix_id = cam.W * py + px;
-    if (bins.total[1]) return;
-    uint2 range = bins.tile_range[ty * cam.tiles_x + tx];
-    PixState ps;
-    ps.T_final = inside ? final_T[pix_id] : 0.f;
-    ps.last = inside ? (int)n_contrib[pix_id] : 0;
-    ps.bgdot = 0.f;
-#pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        ps.dpix[ch] = inside ? dL_dpix[(size_t)ch * cam.H * cam.W + pix_id] : 0.f;
-        ps.bgdot += cam.bg[ch] * ps.dpix[ch];
-    }
-    MomFlush fl{mom};
-    tile_backward<P2, COLOR>(sm, bins.keys + range.x, (int)(range.y - range.x), bins.recs, colors, ps, (float)px, (float)py,
-                            0.5f * cam.W, 0.5f * cam.H, fl);
-}
 
 // Outputs in the reference's shapes; any pointer may be null (skipped).
 struct GradOut {

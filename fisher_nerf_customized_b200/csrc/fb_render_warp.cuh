@@ -1,8 +1,8 @@
 // fb_render_warp.cuh -- the drop-in single-view forward render and moment backward in warp-autonomous form.
 //
 // Same per-pixel arithmetic, in the same order, as renderCUDA<3> (DGR/cuda_rasterizer/forward.cu:261-393) and the
-// pair loop of renderCUDAFused<3> (backward.cu:939-1038); what changes is who visits what.  The reference (and
-// k_render_fwd / k_bwd_tiles, kept as the block-synchronous form) lets each of a tile's 256 pixels test every
+// pair loop of renderCUDAFused<3> (backward.cu:939-1038); what changes is who visits what.  The reference
+// lets each of a tile's 256 pixels test every
 // instance binned to the tile, with a block barrier per 256 instances.  Here a warp owns an 8x4 pixel block,
 // walks the tile's sorted list on its own, 32 entries per step, drops the entries whose alpha >= 1/255 footprint
 // box misses the block (pairs the reference's own alpha test skips; skipped pairs change no state, so every
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_bwd_warp(Bins bins, Cam c
 #pragma unroll
                 for (int k = 0; k < FB_NACC; ++k) v[k] = 0.f;
                 if (ok) {
-                    // backward.cu:978-1038, the statements of tile_backward in the same order
+                    // backward.cu:978-1038, the reference's statements in the same order
                     T = T / (1.f - alpha);
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;

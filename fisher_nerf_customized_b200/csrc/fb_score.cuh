@@ -476,10 +476,10 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
 // ---- per-Gaussian Hessian moments (compute_H_train), warp-autonomous form ----------------------------------
 // Same traversal as k_tile_score (two sweeps, the reference's arithmetic: expf, IEEE division, the recurrences of
 // backward.cu:978-1017 with r+g+b as the one colour channel), but what a contributing pair produces is the 13
-// monomial moments  s^2 * dx^i dy^j  of fb_fisher_tile.cuh (power = 2).  They are summed over the 32 pixels of the
+// monomial moments  s^2 * dx^i dy^j  of fb_fisher.cuh (power = 2).  They are summed over the 32 pixels of the
 // block with the halving butterfly (16 SHFL), four neighbouring sums are gathered into one lane and added to the
 // Gaussian's 16-float row with ONE red.global.add.v4.f32 per quad: 4 vector atomics per (Gaussian, pixel block).
-// k_expand_H turns the rows into H columns.  Replaces k_render_fwd + k_bwd_tiles on the batched H_train path (every
+// k_expand_H turns the rows into H columns.  Replaces a per-view render + block-synchronous tile backward on the batched H_train path (every
 // pixel tests every instance, block barriers per 256 instances): 170 -> ~60 us per keyframe at 500k Gaussians.
 __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, Cam cam, const float* __restrict__ colors,
                                                                     float grad_scale, float* __restrict__ mom_all) {

@@ -92,3 +92,27 @@ def test_count_visible_boundary_points(cuda, oracle):
                     [np.nextafter(np.float32(z), 0), 0, z]], dtype=np.float32)
     counts = cuda.count_visible_batch(torch.from_numpy(pts).cuda(), c2w[None], Kmat, 256).cpu().numpy()
     assert counts[0] == len(oracle.count_visible_points(pts, c2w, Kmat, 256))
+
+
+@pytest.mark.timeout(120)
+def test_distCUDA2_terminates_on_non_finite_points(cuda, oracle):
+    """A diverged map (inf / NaN means) must not hang the grid set-up (its coarsening loop is bounded and non-finite
+    coordinates stay out of the bounding box); the finite points away from the bad ones keep their exact result."""
+    import torch
+    for P, bad in ((5000, [(7, np.inf)]), (300, [(1, np.nan), (2, -np.inf)]), (4, [(0, np.inf)])):
+        pts = synth.make_points(P, seed=9)
+        clean = oracle.distCUDA2(pts)
+        dirty = pts.copy()
+        for i, v in bad:
+            dirty[i, i % 3] = v
+        got = cuda.distCUDA2(torch.from_numpy(dirty).cuda())
+        torch.cuda.synchronize()                                  # the call returned: no endless loop on the device
+        got = got.cpu().numpy()
+        assert got.shape == (P,)
+        if P >= 1000:
+            # a finite point whose three nearest neighbours are finite and not the corrupted ones is unaffected
+            bad_idx = [i for i, _ in bad]
+            far = np.ones(P, bool)
+            for i in bad_idx:
+                far &= np.linalg.norm(pts - pts[i], axis=1) > 1.0
+            np.testing.assert_array_equal(got[far], clean[far])

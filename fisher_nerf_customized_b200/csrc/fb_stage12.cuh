@@ -768,7 +768,9 @@ __device__ __forceinline__ void fix_equal_depth_runs(u64* a, int n, const uint4*
 #ifndef FB_SORT_FINE
 #define FB_SORT_FINE 2048
 #endif
+#ifndef FB_SORT_MAX_BUCKET
 #define FB_SORT_MAX_BUCKET 64
+#endif
 
 __device__ __forceinline__ unsigned block_excl_scan_256(unsigned x, unsigned* warp_sums, unsigned* total) {
     // exclusive scan of one value per thread over a 256-thread block (all threads call; contains barriers)

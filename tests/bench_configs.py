@@ -110,6 +110,31 @@ def cfg2():
     return out
 
 
+def cfg3_variants():
+    """BASELINE cfg 3's other settings (bench.py is C_H = 4, lambda = 0.1): C_H = 11 and lambda = 1e-6, resident views/s."""
+    import torch
+    import fisher_nerf_customized_b200 as fb
+    from fisher_nerf_customized_b200 import synth
+    P, K, W, H = 500_000, 256, 256, 256
+    sc = synth.activate(synth.make_scene(P))
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    gmap = fb.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"])
+    rs = fb.setup_camera(W, H, synth.intrinsics(W, H), np.eye(4, dtype=np.float32))
+    kf = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(32, seed=synth.SEED_POSES + 1))).cuda()
+    w2c = torch.from_numpy(synth.w2c_from_c2w(synth.make_poses(K))).cuda()
+    out = {"config": "3 (variants): 500k Gaussians x 256 candidates at 256x256, resident"}
+    for C_H in (4, 11):
+        scorer = fb.FisherScorer(rs, C_H=C_H, views_per_chunk=64)
+        H_train = scorer.compute_H_train(gmap, kf)
+        out[f"C_H{C_H}_H_train_keyframes_per_s"] = 32 / (ev_time(lambda: scorer.compute_H_train(gmap, kf), 5, warm=2) * 1e-3)
+        for lam in (0.1, 1e-6):
+            H_inv = torch.reciprocal(H_train + lam)
+            ms = ev_time(lambda: scorer.score_candidates(gmap, w2c, H_inv), 5, warm=2)
+            out[f"C_H{C_H}_lambda{lam}_views_per_s"] = K / (ms * 1e-3)
+            out[f"C_H{C_H}_lambda{lam}_argmax"] = int(scorer.score_candidates(gmap, w2c, H_inv).argmax())
+    return out
+
+
 def cfg4():
     """HM3D-scale map: 3M Gaussians x 1024 candidates, plus distCUDA2 over the 3M means."""
     import torch
@@ -443,7 +468,7 @@ def main():
     args = ap.parse_args()
     from fisher_nerf_customized_b200 import _lib
     _lib.lib()
-    todo = {"1": cfg1, "2": cfg2, "4": cfg4, "5": lambda: cfg5(args.loop_steps), "5a": cfg5a,
+    todo = {"1": cfg1, "2": cfg2, "3": cfg3_variants, "4": cfg4, "5": lambda: cfg5(args.loop_steps), "5a": cfg5a,
             "5ref": lambda: cfg5_reference(args.ref_steps), "n1": cfg_n1}
     for k in args.only.split(","):
         r = todo[k.strip()]()

@@ -5,6 +5,10 @@
 #ifndef FB_SCORE_PX2
 #define FB_SCORE_PX2 1
 #endif
+// FB_SCORE_MIX (default, with FB_SCORE_PX2): k_tile_score_mix -- lists of >= FB_HEAVY_KEYS keys go to the 8x4 form.
+#ifndef FB_SCORE_MIX
+#define FB_SCORE_MIX FB_SCORE_PX2
+#endif
 #if FB_SCORE_PX2
 #define FB_SCORE_KERNEL k_tile_score2
 #define FB_SCORE_BLOCKS FB_S2_BLOCKS
@@ -241,6 +245,7 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
     if (!ds->score_attr) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(FB_SCORE_KERNEL, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_KSMEM));
+        FB_CUDA(cudaFuncSetAttribute(k_tile_score_mix, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MIX_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<4>)));
         FB_CUDA(cudaFuncSetAttribute(k_preprocess_score<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem<11>)));
         ds->score_attr = true; ds->sort_attr = true;
@@ -297,9 +302,19 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
         FB_LAUNCH_CHECK();
+#if FB_SCORE_MIX
+        {
+            const int heavy_tiles = (b.tiles < FB_HEAVY_RANKS ? b.tiles : FB_HEAVY_RANKS) * Vc;
+            FB_PROF(FB_K_TILE_SCORE);
+            k_tile_score_mix<<<heavy_tiles * 2 + b.tiles * Vc, 128, FB_MIX_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial), heavy_tiles);
+        }
+        FB_LAUNCH_CHECK();
+        { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }
+#else
         { FB_PROF(FB_K_TILE_SCORE); FB_SCORE_KERNEL<<<dim3(b.tiles * (FB_SCORE_BLOCKS / FB_SCORE_KWPC), Vc), 32 * FB_SCORE_KWPC, FB_SCORE_KSMEM, st>>>(b, cam, grad_scale, (float*)(ws + L.partial)); }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_SCORE_BLOCKS, scores + k0); }
+#endif
         FB_LAUNCH_CHECK();
     }
     if (lanes == 2) {

@@ -20,6 +20,9 @@
 
 namespace fb {
 
+#ifndef FB_S2_PFD
+#define FB_S2_PFD 1    // scan steps the record gather of the pair sweeps runs ahead of its use
+#endif
 #define FB_WB_X 8      // warp pixel block of the H_train moment kernel
 #define FB_WB_Y 4
 // pixel block of k_tile_score1 (32 pixels, one per lane: 8x4 default; 4x8 and 16x2 measured)
@@ -108,17 +111,12 @@ __device__ __forceinline__ float hess_div(float a, float b) {
 // Rounding: the three sums are of non-negative terms and the cancellation happens once per pixel; measured
 // against the reference extension the scores agree to ~1e-5 (tests/test_gpu_scoring.py, rtol 1e-3 required).
 
-// k_tile_score1: one pixel per lane, 8x4 block per warp (the round-1 kernel on the slot-indexed records; built with
-// -DFB_SCORE_PX2=0 as the independent form the parity tests can be run against).
-__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Cam cam, float grad_scale,
-                                                                   float* __restrict__ partial) {
-    extern __shared__ float4 smem[];
-    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;
-    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
-    const int tile_slot = (int)bins.tile_order[lin / CPT];
+// sweep_px1: one pixel per lane, 8x4 block per warp.  D = scan steps the record gather runs ahead of its use.
+template <int D>
+__device__ __forceinline__ void sweep_px1(const Bins& bins, const Cam& cam, float grad_scale, int tile_slot, int warp,
+                                          WarpQ& q, float* __restrict__ out) {
     const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
-    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
-    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;
+    const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
     constexpr int BPR = FB_TILE_X / FB_S1_WX;                       // pixel blocks per tile row
@@ -128,7 +126,6 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const float pxf = (float)px, pyf = (float)py;
     const float cx = (float)bx + 0.5f * (FB_S1_WX - 1), cy = (float)by + 0.5f * (FB_S1_WY - 1);
     const float ex = 0.5f * (FB_S1_WX - 1), ey = 0.5f * (FB_S1_WY - 1);
-    float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + warp;
     if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
     const uint2 range = bins.tile_range[tile_slot];
     const int n = (int)(range.y - range.x);
@@ -138,27 +135,33 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
     const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
     const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
-    WarpQ& q = reinterpret_cast<WarpQ*>(smem)[wq];
 
     float T = 1.0f, Cp = 0.f, Qaa = 0.f, Qab = 0.f, Qbb = 0.f;
     bool done = !inside;
     if (!__all_sync(0xffffffffu, done)) {
         int qn = 0, qh = 0;
         const int nsteps = (n + 31) >> 5;
-        bool v_nxt = lane < n;
-        unsigned gid_nxt = v_nxt ? sorted[2 * lane] : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
-        unsigned key2 = (32 + lane < n) ? sorted[2 * (32 + lane)] : 0u;
+        // the 16-byte {px, py, hx, hy} gathers run D scan steps ahead of their use, the keys one more
+        bool vq[D]; unsigned gq[D]; float4 aq[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            vq[d] = d * 32 + lane < n;
+            gq[d] = vq[d] ? sorted[2 * (d * 32 + lane)] : 0u;
+            aq[d] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (vq[d]) aq[d] = __ldg(reinterpret_cast<const float4*>(recA + (gq[d] << 4)));
+        }
+        unsigned key2 = (D * 32 + lane < n) ? sorted[2 * (D * 32 + lane)] : 0u;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < n;
-                gid_nxt = key2;
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
-                key2 = ((step + 2) * 32 + lane < n) ? sorted[2 * ((step + 2) * 32 + lane)] : 0u;
+                const float4 a = aq[0];
+                const unsigned gid = gq[0];
+                const bool valid = vq[0];
+#pragma unroll
+                for (int d = 0; d + 1 < D; ++d) { vq[d] = vq[d + 1]; gq[d] = gq[d + 1]; aq[d] = aq[d + 1]; }
+                vq[D - 1] = (step + D) * 32 + lane < n;
+                gq[D - 1] = key2;
+                if (vq[D - 1]) aq[D - 1] = __ldg(reinterpret_cast<const float4*>(recA + (key2 << 4)));
+                key2 = ((step + D + 1) * 32 + lane < n) ? sorted[2 * ((step + D + 1) * 32 + lane)] : 0u;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
@@ -229,6 +232,20 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Ca
     if (lane == 0) *out = score;
 }
 
+// k_tile_score1: the 8x4 form alone (the round-1 kernel on the slot-indexed records; built with -DFB_SCORE_PX2=0 as
+// the independent form the parity tests can be run against).
+__global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_score1(Bins bins, Cam cam, float grad_scale,
+                                                                   float* __restrict__ partial) {
+    extern __shared__ float4 smem[];
+    constexpr int CPT = FB_TILE_WARPS / FB_SCORE_WPC;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int wq = threadIdx.x >> 5;
+    const int warp = (int)(lin % CPT) * FB_SCORE_WPC + wq;
+    sweep_px1<FB_S2_PFD>(bins, cam, grad_scale, tile_slot, warp, reinterpret_cast<WarpQ*>(smem)[wq],
+                         partial + (size_t)tile_slot * FB_TILE_WARPS + warp);
+}
+
 // ---- k_tile_score2: two pixels per lane, packed FP32 ------------------------------------------------
 // The pair loop is bound by instruction issue, not by a pipe or by memory (round 1: 79 % of the issue slots, fma 42 %,
 // alu 42 %).  This form issues fewer instructions per (pixel, Gaussian) pair:
@@ -287,15 +304,11 @@ struct WarpQ2 { WarpQ q; unsigned char list[32]; unsigned char pad[96]; };
 #endif                            // lane's latency-bound kernels (scatter, sort) find registers and warp slots beside the sweep
 #define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ2) * FB_S2_WPC + FB_S2_SMEM_EXTRA)
 
-__global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins bins, Cam cam, float grad_scale,
-                                                                 float* __restrict__ partial) {
-    extern __shared__ float4 smem[];
-    constexpr int CPT = FB_S2_BLOCKS / FB_S2_WPC;
-    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
-    const int tile_slot = (int)bins.tile_order[lin / CPT];
+template <int D>
+__device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, float grad_scale, int tile_slot, int warp,
+                                          WarpQ2& q2, float* __restrict__ out) {
     const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
-    const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
-    const int warp = (int)(lin % CPT) * FB_S2_WPC + wq;            // 8x8 block of the tile, 0..3
+    const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
     const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
@@ -304,7 +317,6 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
     const float pxf = (float)px;
     const f32x2 npy = f2_pack(-(float)py0, -(float)py1);
     const float cx = (float)bx + 3.5f, cy = (float)by + 3.5f;
-    float* out = partial + (size_t)tile_slot * FB_S2_BLOCKS + warp;
     if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
     const uint2 range = bins.tile_range[tile_slot];
     const int n = (int)(range.y - range.x);
@@ -312,7 +324,6 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
     const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
     const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
     const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
-    WarpQ2& q2 = reinterpret_cast<WarpQ2*>(smem)[wq];
     WarpQ& q = q2.q;
 
     f32x2 T = f2_dup(1.0f), Cp = f2_dup(0.f), Qaa = f2_dup(0.f), Qab = f2_dup(0.f), Qbb = f2_dup(0.f);
@@ -323,20 +334,27 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
     if (__any_sync(0xffffffffu, in0 || in1)) {
         int qn = 0, qh = 0;
         const int nsteps = (n + 31) >> 5;
-        bool v_nxt = lane < n;
-        unsigned gid_nxt = v_nxt ? sorted[2 * lane] : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
-        unsigned key2 = (32 + lane < n) ? sorted[2 * (32 + lane)] : 0u;
+        // the 16-byte {px, py, hx, hy} gathers run D scan steps ahead of their use, the keys one more
+        bool vq[D]; unsigned gq[D]; float4 aq[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            vq[d] = d * 32 + lane < n;
+            gq[d] = vq[d] ? sorted[2 * (d * 32 + lane)] : 0u;
+            aq[d] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (vq[d]) aq[d] = __ldg(reinterpret_cast<const float4*>(recA + (gq[d] << 4)));
+        }
+        unsigned key2 = (D * 32 + lane < n) ? sorted[2 * (D * 32 + lane)] : 0u;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < n;
-                gid_nxt = key2;
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recA + (gid_nxt << 4)));
-                key2 = ((step + 2) * 32 + lane < n) ? sorted[2 * ((step + 2) * 32 + lane)] : 0u;
+                const float4 a = aq[0];
+                const unsigned gid = gq[0];
+                const bool valid = vq[0];
+#pragma unroll
+                for (int d = 0; d + 1 < D; ++d) { vq[d] = vq[d + 1]; gq[d] = gq[d + 1]; aq[d] = aq[d + 1]; }
+                vq[D - 1] = (step + D) * 32 + lane < n;
+                gq[D - 1] = key2;
+                if (vq[D - 1]) aq[D - 1] = __ldg(reinterpret_cast<const float4*>(recA + (key2 << 4)));
+                key2 = ((step + D + 1) * 32 + lane < n) ? sorted[2 * ((step + D + 1) * 32 + lane)] : 0u;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + 3.5f) && (fabsf(a.y - cy) <= a.w + 3.5f);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
 #if FB_S2_STATS == 1
@@ -471,6 +489,64 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
     if (lane == 0) *out = score;
+}
+
+__global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins bins, Cam cam, float grad_scale,
+                                                                 float* __restrict__ partial) {
+    extern __shared__ float4 smem[];
+    constexpr int CPT = FB_S2_BLOCKS / FB_S2_WPC;
+    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
+    const int tile_slot = (int)bins.tile_order[lin / CPT];
+    const int wq = threadIdx.x >> 5;
+    const int warp = (int)(lin % CPT) * FB_S2_WPC + wq;            // 8x8 block of the tile, 0..3
+    sweep_px2<FB_S2_PFD>(bins, cam, grad_scale, tile_slot, warp, reinterpret_cast<WarpQ2*>(smem)[wq],
+                         partial + (size_t)tile_slot * FB_S2_BLOCKS + warp);
+}
+
+// ---- k_tile_score_mix: one launch, two sweep forms ------------------------------------------------------
+// A warp walks its tile's list alone, so the longest list of the chunk bounds the kernel: a view along a 30 m floor
+// puts > 100 k tiny splats on each tile of the horizon row (cfg 4: ~30 tiles of a view hold 80 % of its instances) and
+// a lone 8x8 warp needs milliseconds for one of them while the rest of the GPU has drained (measured with clock64 at
+// 3M Gaussians: the longest warp of a view runs as long as the whole kernel; the sum of the warp times fills 7.6 of
+// the 32 resident warps per SM).  Lists of >= FB_HEAVY_KEYS keys therefore go to EIGHT warps of 8x4 pixels (sweep_px1:
+// twice the warps per tile, each with ~60 % of the hits and pixel blocks that saturate sooner) with the record gather
+// FB_HEAVY_PFD scan steps ahead; everything else stays on the 8x8 two-pixel form.
+// Grid: [2 CTAs per tile for the first FB_HEAVY_RANKS ranks of every view's tile order][1 CTA per tile].  A heavy CTA
+// whose tile is not heavy exits at once, and so does the ordinary CTA of a heavy tile.
+// partial: FB_TILE_WARPS floats per tile (the 8x8 form writes four and zeroes four).
+#ifndef FB_HEAVY_KEYS
+#define FB_HEAVY_KEYS 16384
+#endif
+#ifndef FB_HEAVY_RANKS
+#define FB_HEAVY_RANKS 64
+#endif
+#ifndef FB_HEAVY_PFD
+#define FB_HEAVY_PFD 1
+#endif
+#define FB_MIX_SMEM_BYTES ((int)sizeof(WarpQ2) * 4)
+__global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_score_mix(Bins bins, Cam cam, float grad_scale,
+                                                                    float* __restrict__ partial, int heavy_tiles) {
+    extern __shared__ float4 smem[];
+    const int wq = threadIdx.x >> 5;
+    const int heavy_ctas = heavy_tiles * 2;
+    if ((int)blockIdx.x < heavy_ctas) {
+        const int tile_slot = (int)bins.tile_order[blockIdx.x >> 1];
+        const uint2 r = bins.tile_range[tile_slot];
+        if ((int)(r.y - r.x) < FB_HEAVY_KEYS) return;
+        const int warp = (int)(blockIdx.x & 1) * 4 + wq;
+        sweep_px1<FB_HEAVY_PFD>(bins, cam, grad_scale, tile_slot, warp, reinterpret_cast<WarpQ2*>(smem)[wq].q,
+                                partial + (size_t)tile_slot * FB_TILE_WARPS + warp);
+    } else {
+        const int idx = (int)blockIdx.x - heavy_ctas;
+        const int tile_slot = (int)bins.tile_order[idx];
+        if (idx < heavy_tiles) {
+            const uint2 r = bins.tile_range[tile_slot];
+            if ((int)(r.y - r.x) >= FB_HEAVY_KEYS) return;
+        }
+        float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + wq;
+        if ((threadIdx.x & 31) == 0) out[4] = 0.f;
+        sweep_px2<FB_S2_PFD>(bins, cam, grad_scale, tile_slot, wq, reinterpret_cast<WarpQ2*>(smem)[wq], out);
+    }
 }
 
 // ---- per-Gaussian Hessian moments (compute_H_train), warp-autonomous form ----------------------------------

@@ -72,6 +72,7 @@ SIGNATURES = {
     "fb_morton_codes": (ci, [ci, vp, vp, vp, vp, vp]),
     "fb_occ_workspace_bytes": (sz, [ci, ci]),
     "fb_occ_update": (ci, [vp, ci, ci, vp, ci, ci, ci, vp, vp, vp, vp, cf, cf, cf, cf, vp, vp, sz, vp]),
+    "fb_occ_update_static": (ci, [vp, ci, ci, vp, ci, ci, ci, vp, vp, vp, vp, cf, cf, cf, cf, vp, vp]),
     "fb_count_vs_mask": (ci, [ci, vp, vp, vp, vp, vp, ci, ci, cf, vp, vp, vp]),
     "fb_block_opt_partials": (ci, [ci]),
     "fb_block_opt": (ci, [ci, ci, vp, vp, vp, vp, cf, ci, vp, vp, vp]),

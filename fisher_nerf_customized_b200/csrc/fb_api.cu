@@ -68,6 +68,7 @@ const char* fb_error_string(int s) {
         case FB_E_CUDA: return "CUDA error";
         case FB_E_CAPACITY: return "instance capacity exceeded";
         case FB_E_PREFILTERED: return "Point is filtered although prefiltered is set";
+        case FB_E_STATIC_LIMIT: return "size exceeds the static scratch of the no-allocation entry point (FB_OCC_STATIC_MAX_CELLS)";
         default: return "unknown";
     }
 }

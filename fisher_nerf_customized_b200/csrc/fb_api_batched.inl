@@ -550,6 +550,57 @@ int fb_occ_update(float* occ_map, int gx, int gz, const float* depth, int width,
     return FB_OK;
 }
 
+// ---- fb_occ_update_static: the occupancy update with its scratch in a file-scope device array ----------------------
+// For callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): same kernels
+// and arguments as fb_occ_update, but the counters / canvas / camera cell live in g_occ_static_scratch, which every GPU
+// that loads this library holds until exit.  No counterpart in the reference.
+// The array's name is only a host-side handle: its device address is looked up once per device (with that
+// device current) through cudaGetSymbolAddress and handed to the kernels.  Calls share the array and it keeps the last
+// call's contents: the used part is cleared on the stream first, and two calls that overlap on one GPU race.
+#define FB_OCC_STATIC_BYTES (2 * (size_t)FB_OCC_STATIC_MAX_CELLS * 4 + (size_t)FB_OCC_STATIC_MAX_CELLS + 256)
+static __device__ __align__(256) unsigned char g_occ_static_scratch[FB_OCC_STATIC_BYTES];
+static void* g_occ_static_ptr[64] = {nullptr};
+
+int fb_occ_update_static(float* occ_map, int gx, int gz, const float* depth, int width, int height, int downsample,
+                         const float* c2w, const float* intr, const float* planes, const float* map_center,
+                         float cell_size, float height_lower, float height_upper, float far_distance, int* cam_cell,
+                         void* stream_) {
+    using namespace fb;
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (!occ_map || gx <= 0 || gz <= 0 || !depth || width <= 0 || height <= 0 || downsample <= 0 || !c2w || !intr ||
+        !planes || !map_center || !(cell_size > 0.f)) return FB_E_INVALID;
+    if ((long long)gx * gz > (long long)FB_OCC_STATIC_MAX_CELLS) return FB_E_STATIC_LIMIT;
+    int dev = -1;
+    FB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return FB_E_INVALID;
+    if (!g_occ_static_ptr[dev]) {
+        void* p = nullptr;
+        FB_CUDA(cudaGetSymbolAddress(&p, g_occ_static_scratch));
+        if (!p) return FB_E_CUDA;
+        g_occ_static_ptr[dev] = p;
+    }
+    const size_t n = (size_t)gx * gz;
+    char* ws = (char*)g_occ_static_ptr[dev];
+    OccArgs a;
+    a.occ_map = occ_map; a.gx = gx; a.gz = gz; a.depth = depth; a.W = width; a.H = height; a.ds = downsample;
+    a.c2w = c2w; a.intr = intr; a.planes = planes; a.map_center = map_center;
+    a.cell = cell_size; a.h_lo = height_lower; a.h_hi = height_upper; a.far = far_distance;
+    a.cnt_free = (int*)ws; a.cnt_occ = (int*)(ws + align_up(n * 4, 256));
+    a.canvas = (unsigned char*)(ws + 2 * align_up(n * 4, 256));
+    a.cam_cell = (int*)(ws + 2 * align_up(n * 4, 256) + align_up(n, 256));
+    FB_CUDA(cudaMemsetAsync(ws, 0, 2 * align_up(n * 4, 256) + align_up(n, 256), st));
+    const long long pts = (long long)((width + downsample - 1) / downsample) * ((height + downsample - 1) / downsample) * 11;
+    // (no FB_PROF here: the profiling scope creates events when enabled; the launches are counted by hand)
+    k_occ_points<<<(unsigned)((pts + 255) / 256), 256, 0, st>>>(a);
+    FB_LAUNCH_CHECK();
+    k_occ_lines<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
+    k_occ_fuse<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a);
+    FB_LAUNCH_CHECK();
+    g_launches += 3;
+    if (cam_cell) FB_CUDA(cudaMemcpyAsync(cam_cell, a.cam_cell, 8, cudaMemcpyDeviceToDevice, st));
+    return FB_OK;
+}
+
 int fb_count_vs_mask(int N, const float* means3D, const float* logit_opacities, const float* w2c, const float* intr,
                      const uint8_t* mask, int width, int height, float opacity_thresh, uint8_t* code, int* counts,
                      void* stream_) {

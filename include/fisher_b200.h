@@ -60,6 +60,7 @@ extern "C" {
 #define FB_E_CUDA           (-3)  /* a CUDA runtime call or launch failed; see fb_last_cuda_error() */
 #define FB_E_CAPACITY       (-4)  /* device-side instance capacity exceeded; *needed tells how much */
 #define FB_E_PREFILTERED    (-5)  /* prefiltered=1 but a point was culled (reference: device __trap, auxiliary.h:156-160) */
+#define FB_E_STATIC_LIMIT   (-6)  /* fb_occ_update_static: gx * gz exceeds FB_OCC_STATIC_MAX_CELLS */
 
 /* Compile-time raster constants, identical to DGR/cuda_rasterizer/config.h:15-17. */
 #define FB_NUM_CHANNELS 3
@@ -385,6 +386,20 @@ int fb_occ_update(float* occ_map, int gx, int gz,
                   const float* c2w, const float* intr, const float* planes, const float* map_center,
                   float cell_size, float height_lower, float height_upper, float far_distance,
                   int* cam_cell, void* workspace, size_t workspace_bytes, void* stream);
+
+/* fb_occ_update without any allocation or caller workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops).  Same arguments and
+ * results as fb_occ_update; the scratch is a file-scope device array inside the library (9.0 MiB on every GPU that loads
+ * it, held until exit) sized for gx * gz <= FB_OCC_STATIC_MAX_CELLS cells (the reference's 768 x 768 grid fits);
+ * larger grids return FB_E_STATIC_LIMIT.  The call itself uses only cudaMemsetAsync, kernel launches and one
+ * device-to-device cudaMemcpyAsync on `stream`.  All calls on a GPU share the array: calls that overlap on the GPU
+ * (different streams, or different host threads) race; serialise them. */
+#define FB_OCC_STATIC_MAX_CELLS (1024 * 1024)
+int fb_occ_update_static(float* occ_map, int gx, int gz,
+                         const float* depth, int width, int height, int downsample,
+                         const float* c2w, const float* intr, const float* planes, const float* map_center,
+                         float cell_size, float height_lower, float height_upper, float far_distance,
+                         int* cam_cell, void* stream);
 
 /* count_gaussians_vs_mask (models/SLAM/gaussian_object.py:359-428): code[i] = 0 if sigmoid(logit_i) < thresh,
  * 1 if the Gaussian projects inside the mask, 2 if it projects into the image but outside the mask, 3 if it is

@@ -134,7 +134,7 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
     b.tile_order = (uint32_t*)(ib + IL.tile_order);
     b.total = (uint32_t*)(ib + IL.totals);
-    b.keys = (u64*)inst; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
+    b.keys = (u64*)inst; b.sub_list = nullptr; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
 
@@ -219,8 +219,8 @@ int fb_raster_forward_render2(const fb_camera* c, const fb_gaussians* g, const f
             FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
             attr_set = true;
         }
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, 1), 256, FB_SORT_SMEM_BYTES, st>>>(
-            b, (u64*)((char*)inst + align_up((size_t)num_rendered * 8, 256)), FB_SORT_SMEM_KEYS); }
+        { FB_PROF(FB_K_SORT); k_sort_tiles<<<b.tiles, 256, FB_SORT_SMEM_BYTES, st>>>(
+            b, (u64*)((char*)inst + align_up((size_t)num_rendered * 8, 256)), FB_SORT_SMEM_KEYS, b.tiles, 0); }
         FB_LAUNCH_CHECK();
     }
     const float* feat = g->colors_precomp ? g->colors_precomp : (const float*)((char*)geom + GL.rgb);

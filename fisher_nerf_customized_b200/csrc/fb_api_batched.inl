@@ -2,6 +2,17 @@
 // Included by fb_api.cu.
 
 // FB_SCORE_PX2 (default): the pair sweep is k_tile_score2 (two pixels per lane, packed FP32); 0 selects k_tile_score1.
+// FB_SORT_SPLIT: tile segments of >= FB_SPLIT_MIN keys (among the FB_SPLIT_RANKS heaviest tiles of a view) are partitioned by
+// depth and sorted piecewise by FB_SORT_SUB_CTAS CTAs (fb_stage12.cuh: split_segment).
+#ifndef FB_SORT_SPLIT
+#define FB_SORT_SPLIT 1
+#endif
+#ifndef FB_SPLIT_RANKS
+#define FB_SPLIT_RANKS 64
+#endif
+#ifndef FB_SORT_SUB_CTAS
+#define FB_SORT_SUB_CTAS (148 * 6)
+#endif
 #ifndef FB_SCORE_PX2
 #define FB_SCORE_PX2 1
 #endif
@@ -80,7 +91,7 @@ static CtrlPtrs ctrl_ptrs(char* base) { return CtrlPtrs{(uint32_t*)base, (uint32
 // Scoring workspace of one chunk lane.  Records live in the view's visible slot: [V][vis_cap] rows of 16 + 80 + 16
 // bytes (vis_cap = the caller's visible capacity, <= P), not [V][P] rows.
 struct ScoreLayout {
-    size_t recA, recB, vis_list, ctrl, tile_count, tile_range, tile_order, partial, keys, keys_alt, total;
+    size_t recA, recB, vis_list, ctrl, tile_count, tile_range, tile_order, partial, keys, keys_alt, sub_list, total;
 };
 static ScoreLayout score_layout(int P, int W, int H, int V, long long cap, long long vis_cap) {
     ScoreLayout L; size_t o = 0; size_t Vv = (size_t)(V > 0 ? V : 1);
@@ -96,6 +107,7 @@ static ScoreLayout score_layout(int P, int W, int H, int V, long long cap, long 
     L.partial = o;    o = align_up(o + Vv * tiles * 4 * FB_TILE_WARPS, 256);
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.sub_list = o;   o = align_up(o + sort_sub_capacity(cap > 0 ? cap : 1, (long long)Vv * FB_SPLIT_RANKS) * 16, 256);
     L.total = o;
     return L;
 }
@@ -109,14 +121,14 @@ static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& 
     b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.tile_order = (uint32_t*)(ws + L.tile_order);
-    b.keys = (u64*)(ws + L.keys);
+    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
 
 // H_train workspace (fb_accumulate_hessian): records and moment rows are indexed by Gaussian id, [V][P].
 struct HessLayout {
-    size_t recs, mom, vis_list, ctrl, tile_count, tile_range, tile_order, keys, keys_alt, total;
+    size_t recs, mom, vis_list, ctrl, tile_count, tile_range, tile_order, keys, keys_alt, sub_list, total;
 };
 static HessLayout hess_layout(int P, int W, int H, int V, long long cap) {
     HessLayout L; size_t o = 0; size_t Pp = (size_t)(P > 0 ? P : 1), Vv = (size_t)(V > 0 ? V : 1);
@@ -130,6 +142,7 @@ static HessLayout hess_layout(int P, int W, int H, int V, long long cap) {
     L.tile_order = o; o = align_up(o + Vv * tiles * 4, 256);
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
+    L.sub_list = o;   o = align_up(o + sort_sub_capacity(cap > 0 ? cap : 1, (long long)Vv * FB_SPLIT_RANKS) * 16, 256);
     L.total = o;
     return L;
 }
@@ -141,7 +154,7 @@ static Bins hess_bins(const HessLayout& L, char* ws, int P, int V, const Cam& ca
     b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.tile_order = (uint32_t*)(ws + L.tile_order);
-    b.keys = (u64*)(ws + L.keys);
+    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
@@ -300,7 +313,12 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
             { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
         }
         FB_LAUNCH_CHECK();
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
+        {
+            // long segments are cut into pieces by their CTA, the pieces sorted by the last FB_SORT_SUB_CTAS CTAs of the grid
+            const int split_slots = FB_SORT_SPLIT ? (b.tiles < FB_SPLIT_RANKS ? b.tiles : FB_SPLIT_RANKS) * Vc : 0;
+            const int sub_ctas = split_slots ? FB_SORT_SUB_CTAS : 0;
+            { FB_PROF(FB_K_SORT); k_sort_tiles<<<b.tiles * Vc + sub_ctas, 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS, b.tiles * Vc, split_slots); }
+        }
         FB_LAUNCH_CHECK();
 #if FB_SCORE_MIX
         {
@@ -376,7 +394,12 @@ int fb_accumulate_hessian_sets(const fb_camera* c, const fb_map* map, const floa
         else
 #endif
         { FB_PROF(FB_K_SCATTER); k_scatter_keys<<<dim3(sblocks, Vc), 256, 0, st>>>(b, cam); }
-        { FB_PROF(FB_K_SORT); k_sort_tiles<<<dim3(b.tiles, Vc), 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS); }
+        {
+            // long segments are cut into pieces by their CTA, the pieces sorted by the last FB_SORT_SUB_CTAS CTAs of the grid
+            const int split_slots = FB_SORT_SPLIT ? (b.tiles < FB_SPLIT_RANKS ? b.tiles : FB_SPLIT_RANKS) * Vc : 0;
+            const int sub_ctas = split_slots ? FB_SORT_SUB_CTAS : 0;
+            { FB_PROF(FB_K_SORT); k_sort_tiles<<<b.tiles * Vc + sub_ctas, 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS, b.tiles * Vc, split_slots); }
+        }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_BWD_TILES); k_tile_hessian<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
               b, cam, map->colors, grad_scale, mom); }

@@ -44,6 +44,7 @@ struct Bins {
     uint32_t* tile_order;  // [V*tiles]    scoring only (else null): tile slots by descending instance count
     uint32_t* total;       // [4]: total instances (lo), overflow flag, prefiltered-trap flag, max tile count
     u64*      keys;        // [capacity]
+    uint4*    sub_list;    // scoring / H_train paths (else null): pieces of the long segments (split_segment in k_sort_tiles); count in total[8], reports in total[9]
     long long capacity;
     int       P;
     int       V;

@@ -788,30 +788,38 @@ __device__ __forceinline__ unsigned block_excl_scan_256(unsigned x, unsigned* wa
     return base + inc - x;
 }
 
-__global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __restrict__ keys_alt, int smem_keys) {
-    extern __shared__ u64 s_keys[];
-    __shared__ unsigned work[FB_SORT_FINE > FB_RADIX_WARPS * 256 ? FB_SORT_FINE : FB_RADIX_WARPS * 256];   // fine-bucket cursors, or the radix histograms
-    __shared__ unsigned c_cnt[FB_SORT_COARSE], c_base[FB_SORT_COARSE], c_nf[FB_SORT_COARSE];
-    __shared__ unsigned wsums[FB_RADIX_WARPS];
-    __shared__ unsigned s_lo, s_hi, s_maxb;
+struct SortShared {
+    unsigned work[FB_SORT_FINE > FB_RADIX_WARPS * 256 ? FB_SORT_FINE : FB_RADIX_WARPS * 256];   // fine-bucket cursors, or the radix histograms
+    unsigned c_cnt[FB_SORT_COARSE], c_base[FB_SORT_COARSE], c_nf[FB_SORT_COARSE];
+    unsigned wsums[FB_RADIX_WARPS];
+    unsigned s_lo, s_hi, s_maxb;
+};
+
+// Sorts the n keys of one segment into `seg`.  `alt`: n keys of scratch in global memory; with in_alt the unsorted keys
+// are there (k_sort_split left them in bucket order), else in seg.  All threads of the 256-thread CTA call; the caller
+// puts a barrier between two calls.
+__device__ __forceinline__ void sort_segment(u64* seg, u64* alt, const int n, const bool in_alt,
+                                             const uint4* __restrict__ vis, const int smem_keys, u64* s_keys, SortShared& sh) {
+    unsigned* work = sh.work;
+    unsigned* c_cnt = sh.c_cnt; unsigned* c_base = sh.c_base; unsigned* c_nf = sh.c_nf;
+    unsigned* wsums = sh.wsums;
+    unsigned& s_lo = sh.s_lo; unsigned& s_hi = sh.s_hi; unsigned& s_maxb = sh.s_maxb;
     const int tid = threadIdx.x;
-    const unsigned lin = blockIdx.y * gridDim.x + blockIdx.x;
-    const unsigned slot = bins.tile_order ? bins.tile_order[lin] : lin;    // heaviest segments first
-    if (bins.total[1]) return;
-    const uint2 r = bins.tile_range[slot];
-    const int n = (int)(r.y - r.x);
-    if (n < 2) return;
-    u64* seg = bins.keys + r.x;
-    const uint4* __restrict__ vis = bins.key_is_slot ? bins.vis_list + (size_t)(slot / (unsigned)bins.tiles) * bins.vis_stride : nullptr;
+    if (n < 2) { if (in_alt && n == 1 && tid == 0) seg[0] = alt[0]; return; }
+    if (in_alt && n > smem_keys) {                            // (a pathological sub-segment: rare)
+        for (int i = tid; i < n; i += FB_TILE_PIX) seg[i] = alt[i];
+        __syncthreads();
+    }
+    const u64* src = (in_alt && n <= smem_keys) ? alt : seg;
     bool radix = false;
     {
         // Segments that fit: keys staged and scattered in shared memory, 2048 fine buckets in `work`.
         // Longer segments (a view close to a wall puts > 10k instances on a tile): same algorithm with the keys
-        // in global memory (seg -> keys_alt -> seg, L2-resident) and the dynamic shared memory used as the
+        // in global memory (seg -> alt -> seg, L2-resident) and the dynamic shared memory used as the
         // bucket array instead (16 KB per 4096 entries), so the buckets stay short.
         const bool big = n > smem_keys;
         const u64* s_in = big ? seg : s_keys;
-        u64* s_out = big ? keys_alt + r.x : s_keys + smem_keys;
+        u64* s_out = big ? alt : s_keys + smem_keys;
         unsigned* fine = big ? reinterpret_cast<unsigned*>(s_keys) : work;
 #define FB_FIDX(f) (f)
         const int NF = big ? min(smem_keys * 4, 32768) & ~255 : FB_SORT_FINE;   // u32 entries available; multiple of 256
@@ -822,7 +830,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
         unsigned lo = 0xffffffffu, hi = 0u;
 #pragma unroll 4
         for (int i = tid; i < n; i += FB_TILE_PIX) {
-            const u64 k = seg[i];
+            const u64 k = src[i];
             if (!big) s_keys[i] = k;
             const unsigned d = (unsigned)(k >> 32);
             lo = min(lo, d); hi = max(hi, d);
@@ -919,7 +927,8 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
     {
         unsigned (*hist)[256] = reinterpret_cast<unsigned (*)[256]>(work);
         u64* a = seg;
-        u64* b = keys_alt + r.x;
+        u64* b = alt;
+        if (in_alt && n <= smem_keys) { a = alt; b = seg; }     // a piece that was not copied: its keys are still in alt
 #pragma unroll 1
         for (int pass = 0; pass < 4; ++pass) {
             if (radix_pass_u64(a, b, n, 32 + 8 * pass, hist)) { u64* tmp = a; a = b; b = tmp; }
@@ -929,6 +938,144 @@ __global__ void __launch_bounds__(FB_TILE_PIX) k_sort_tiles(Bins bins, u64* __re
             for (int i = tid; i < n; i += blockDim.x) seg[i] = a[i];
         }
     }
+}
+
+// ---- long segments: split by depth first, sort the pieces with every SM ------------------------------------
+// One CTA per tile sorts a segment, and a segment longer than the shared staging goes through global memory at a
+// fraction of the speed: a view along a 30 m floor has tiles with > 100 k keys (cfg 4: the longest 272 k) and the
+// kernel waited milliseconds for the CTAs that own them.  A segment of >= FB_SPLIT_MIN keys (among the first
+// `split_slots` entries of the tile order) is instead PARTITIONED by its CTA into depth buckets
+// (keys -> keys_alt in bucket order), and the bucket sequence is cut into pieces of
+// ~FB_SPLIT_T keys.  A piece never cuts a bucket, so equal depths stay together and the sorted pieces, concatenated,
+// are the sorted segment.  The pieces go onto one list for the chunk (bins.sub_list, count in bins.total[8]); the LAST
+// `sub_ctas` CTAs of the grid wait until the first split_slots CTAs have reported (bins.total[9]) and sort the pieces
+// (keys_alt -> keys) in shared memory.  CTAs start in index order, so every CTA a waiting one depends on is resident
+// or done (the argument of the chained scan).
+#ifndef FB_SPLIT_MIN
+#define FB_SPLIT_MIN 16384
+#endif
+#ifndef FB_SPLIT_T
+#define FB_SPLIT_T 768
+#endif
+#define FB_SPLIT_FINE 4096        // fine buckets of the partition: the dynamic shared memory as unsigned[4096]
+#define FB_SPLIT_MAXJ 2048        // piece table: SortShared::work
+__host__ __device__ __forceinline__ bool sort_is_split(int n) { return n >= FB_SPLIT_MIN && n <= FB_SPLIT_MAXJ * FB_SPLIT_T; }
+// entries the piece list needs for `instances` keys over at most `slots` split segments (a hard bound)
+__host__ __device__ __forceinline__ size_t sort_sub_capacity(long long instances, long long slots) {
+    return (size_t)(instances / FB_SPLIT_T + slots + 1);
+}
+
+// The partition uses a FIXED monotone map depth -> bucket (no min / max and no equalisation passes: two reads of the
+// segment instead of four): 512 buckets per octave of depth over [0.125, 32) m, i.e. bits 14.. of the float above
+// 0.125f.  A tile whose depths cluster in a few buckets yields pieces longer than the staging; sort_segment takes
+// those through its global-memory path, as it would have taken the whole segment.
+__device__ __forceinline__ unsigned split_bucket(unsigned depth_bits) {
+    const unsigned x = depth_bits > 0x3E000000u ? depth_bits - 0x3E000000u : 0u;
+    return min(x >> 14, (unsigned)(FB_SPLIT_FINE - 1));
+}
+__device__ __forceinline__ void split_segment(const Bins& bins, const u64* __restrict__ seg, u64* __restrict__ alt, const int n,
+                                              const unsigned off, const unsigned view, unsigned* fine, SortShared& sh) {
+    unsigned* tab = sh.work;
+    const int tid = threadIdx.x, lane = tid & 31;
+    constexpr int NF = FB_SPLIT_FINE, NT = FB_TILE_PIX, U = 8;
+    for (int i = tid; i < NF; i += NT) fine[i] = 0u;
+    const int J = (n + FB_SPLIT_T - 1) / FB_SPLIT_T;
+    for (int i = tid; i < J; i += NT) tab[i] = 0xffffffffu;
+    __syncthreads();
+    // histogram: U loads in flight per thread
+    for (int i0 = 0; i0 < n; i0 += NT * U) {
+        unsigned d[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { const int i = i0 + u * NT + tid; d[u] = i < n ? (unsigned)(__ldcg(seg + i) >> 32) : 0u; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (i0 + u * NT + tid < n) atomicAdd(&fine[split_bucket(d[u])], 1u);
+    }
+    __syncthreads();
+    {
+        // exclusive scan of the counts: thread t owns buckets [16 t, 16 t + 16)
+        constexpr int PER = NF / NT;
+        unsigned sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) sum += fine[tid * PER + k];
+        unsigned start = block_excl_scan_256(sum, sh.wsums, nullptr);
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const unsigned c = fine[tid * PER + k];
+            fine[tid * PER + k] = start;
+            // piece j = the buckets whose first key position lies in [j T, (j + 1) T): its start is the smallest of them
+            if (c) atomicMin(&tab[start / FB_SPLIT_T], start);
+            start += c;
+        }
+    }
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += NT * U) {
+        u64 k[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { const int i = i0 + u * NT + tid; k[u] = i < n ? __ldcg(seg + i) : 0ull; }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (i0 + u * NT + tid < n) alt[atomicAdd(&fine[split_bucket((unsigned)(k[u] >> 32))], 1u)] = k[u];
+    }
+    // the pieces: one list entry each {first key, keys, view, -}; a warp reserves its entries with one atomic
+    for (int j0 = 0; j0 < J; j0 += NT) {
+        const int j = j0 + tid;
+        const unsigned st = j < J ? tab[j] : 0xffffffffu;
+        const bool has = st != 0xffffffffu;
+        unsigned en = (unsigned)n;
+        if (has) for (int k = j + 1; k < J; ++k) { const unsigned t = tab[k]; if (t != 0xffffffffu) { en = t; break; } }
+        const unsigned m = __ballot_sync(0xffffffffu, has);
+        unsigned base = 0;
+        if (lane == 0 && m) base = atomicAdd(&bins.total[8], (unsigned)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (has) bins.sub_list[base + __popc(m & ((1u << lane) - 1u))] = make_uint4(off + st, en - st, view, 0u);
+    }
+}
+
+// Sort every tile segment of every view of the chunk.  Dynamic shared memory: smem_keys keys (x2 if FB_SORT_STAGE).
+// Grid: [one CTA per (view, tile), heaviest first; the first split_slots may partition instead][sub_ctas piece sorters].
+#ifndef FB_SORT_MINB
+#define FB_SORT_MINB 6
+#endif
+__global__ void __launch_bounds__(FB_TILE_PIX, FB_SORT_MINB) k_sort_tiles(Bins bins, u64* __restrict__ keys_alt, int smem_keys, int tile_ctas,
+                                                               int split_slots) {
+    extern __shared__ u64 s_keys[];
+    __shared__ SortShared sh;
+    if (bins.total[1]) return;
+    const int tid = threadIdx.x;
+    if ((int)blockIdx.x >= tile_ctas) {
+        // piece sorter: wait for the partitions, then walk the list
+        if (tid == 0) {
+            volatile unsigned* done = bins.total + 9;
+            while (*done < (unsigned)split_slots) __nanosleep(200);
+            __threadfence();
+        }
+        __syncthreads();
+        const unsigned cnt = *(volatile unsigned*)(bins.total + 8);
+        const unsigned nsub = gridDim.x - (unsigned)tile_ctas;
+        for (unsigned i = blockIdx.x - (unsigned)tile_ctas; i < cnt; i += nsub) {
+            const uint4 d = __ldcg(bins.sub_list + i);
+            const uint4* vis = bins.key_is_slot ? bins.vis_list + (size_t)d.z * bins.vis_stride : nullptr;
+            sort_segment(bins.keys + d.x, keys_alt + d.x, (int)d.y, true, vis, smem_keys, s_keys, sh);
+            __syncthreads();
+        }
+        return;
+    }
+    const unsigned lin = blockIdx.x;
+    const unsigned slot = bins.tile_order ? bins.tile_order[lin] : lin;    // heaviest segments first
+    const uint2 r = bins.tile_range[slot];
+    const int n = (int)(r.y - r.x);
+    const bool reports = (int)lin < split_slots;
+    if (reports && sort_is_split(n)) {
+        split_segment(bins, bins.keys + r.x, keys_alt + r.x, n, r.x, slot / (unsigned)bins.tiles, reinterpret_cast<unsigned*>(s_keys), sh);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) atomicAdd(&bins.total[9], 1u);
+        return;
+    }
+    if (reports && tid == 0) atomicAdd(&bins.total[9], 1u);
+    if (n < 2) return;
+    const uint4* vis = bins.key_is_slot ? bins.vis_list + (size_t)(slot / (unsigned)bins.tiles) * bins.vis_stride : nullptr;
+    sort_segment(bins.keys + r.x, keys_alt + r.x, n, false, vis, smem_keys, s_keys, sh);
 }
 
 }  // namespace fb

@@ -134,7 +134,7 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
     b.tile_count = (uint32_t*)(ib + IL.tile_count); b.tile_range = (uint2*)(ib + IL.tile_range);
     b.tile_order = (uint32_t*)(ib + IL.tile_order);
     b.total = (uint32_t*)(ib + IL.totals);
-    b.keys = (u64*)inst; b.sub_list = nullptr; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
+    b.keys = (u64*)inst; b.sub_list = nullptr; b.seg_list = nullptr; b.seg_flags = nullptr; b.capacity = cap; b.P = P; b.V = 1; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
 

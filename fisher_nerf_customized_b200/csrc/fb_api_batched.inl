@@ -91,7 +91,7 @@ static CtrlPtrs ctrl_ptrs(char* base) { return CtrlPtrs{(uint32_t*)base, (uint32
 // Scoring workspace of one chunk lane.  Records live in the view's visible slot: [V][vis_cap] rows of 16 + 80 + 16
 // bytes (vis_cap = the caller's visible capacity, <= P), not [V][P] rows.
 struct ScoreLayout {
-    size_t recA, recB, vis_list, ctrl, tile_count, tile_range, tile_order, partial, keys, keys_alt, sub_list, total;
+    size_t recA, recB, vis_list, ctrl, tile_count, tile_range, tile_order, partial, keys, keys_alt, sub_list, seg_list, seg_zero, seg_state, seg_out, seg_items, total;
 };
 static ScoreLayout score_layout(int P, int W, int H, int V, long long cap, long long vis_cap) {
     ScoreLayout L; size_t o = 0; size_t Vv = (size_t)(V > 0 ? V : 1);
@@ -108,6 +108,11 @@ static ScoreLayout score_layout(int P, int W, int H, int V, long long cap, long 
     L.keys = o;       o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.keys_alt = o;   o = align_up(o + (size_t)(cap > 0 ? cap : 1) * 8, 256);
     L.sub_list = o;   o = align_up(o + sort_sub_capacity(cap > 0 ? cap : 1, (long long)Vv * FB_SPLIT_RANKS) * 16, 256);
+    L.seg_items = seg_item_capacity(cap > 0 ? cap : 1, (long long)Vv * FB_HEAVY_RANKS);
+    L.seg_list = o;   o = align_up(o + L.seg_items * 16, 256);
+    L.seg_zero = o;   o = align_up(o + L.seg_items * 32, 256);          // chain flags and completion counters: [items][8]
+    L.seg_state = o;  o = align_up(o + L.seg_items * 4 * 32 * 16, 256);
+    L.seg_out = o;    o = align_up(o + L.seg_items * 4 * 64 * 16, 256);
     L.total = o;
     return L;
 }
@@ -121,7 +126,7 @@ static Bins score_bins(const ScoreLayout& L, char* ws, int P, int V, const Cam& 
     b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.tile_order = (uint32_t*)(ws + L.tile_order);
-    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list);
+    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list); b.seg_list = FB_SCORE_MIX ? (uint4*)(ws + L.seg_list) : nullptr; b.seg_flags = (uint4*)(ws + L.seg_zero);
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
@@ -154,7 +159,7 @@ static Bins hess_bins(const HessLayout& L, char* ws, int P, int V, const Cam& ca
     b.vis_count = c.vis_count; b.total = c.total; b.view_total = c.view_total;
     b.tile_count = (uint32_t*)(ws + L.tile_count); b.tile_range = (uint2*)(ws + L.tile_range);
     b.tile_order = (uint32_t*)(ws + L.tile_order);
-    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list);
+    b.keys = (u64*)(ws + L.keys); b.sub_list = (uint4*)(ws + L.sub_list); b.seg_list = nullptr; b.seg_flags = nullptr;
     b.capacity = cap; b.P = P; b.V = V; b.tiles = cam.tiles_x * cam.tiles_y;
     return b;
 }
@@ -322,9 +327,11 @@ int fb_score_candidates_sets(const fb_camera* c, const fb_map* map, const float*
         FB_LAUNCH_CHECK();
 #if FB_SCORE_MIX
         {
-            const int heavy_tiles = (b.tiles < FB_HEAVY_RANKS ? b.tiles : FB_HEAVY_RANKS) * Vc;
+            SegWs sw;
+            sw.state = (float4*)(ws + L.seg_state); sw.out = (float4*)(ws + L.seg_out);
+            sw.flag = (unsigned*)(ws + L.seg_zero);
             FB_PROF(FB_K_TILE_SCORE);
-            k_tile_score_mix<<<heavy_tiles * 2 + b.tiles * Vc, 128, FB_MIX_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial), heavy_tiles);
+            k_tile_score_mix<<<FB_SEG_WORKERS + b.tiles * Vc, 128, FB_MIX_SMEM_BYTES, st>>>(b, cam, grad_scale, (float*)(ws + L.partial), sw, FB_SEG_WORKERS);
         }
         FB_LAUNCH_CHECK();
         { FB_PROF(FB_K_FINALIZE); k_score_finalize<<<Vc, 32, 0, st>>>((const float*)(ws + L.partial), b.tiles * FB_TILE_WARPS, scores + k0); }

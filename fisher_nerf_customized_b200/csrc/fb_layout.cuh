@@ -27,6 +27,22 @@ struct __align__(16) GRec {
 };
 
 // View-batched binning state.  All arrays are [V][...] with the given strides.
+// Tile lists of >= FB_HEAVY_KEYS keys (among the FB_HEAVY_RANKS heaviest tiles of a view) are swept in segments of
+// FB_SEG_KEYS keys by different warps (fb_score.cuh: sweep_px2_segment).
+#ifndef FB_HEAVY_KEYS
+#define FB_HEAVY_KEYS 16384
+#endif
+#ifndef FB_HEAVY_RANKS
+#define FB_HEAVY_RANKS 64
+#endif
+#ifndef FB_SEG_KEYS
+#define FB_SEG_KEYS 8192
+#endif
+// work items the segment list needs for `instances` keys over at most `slots` heavy tiles (a hard bound)
+static inline __host__ __device__ size_t seg_item_capacity(long long instances, long long slots) {
+    return (size_t)(instances / FB_SEG_KEYS + slots + 1);
+}
+
 struct Bins {
     GRec*     recs;        // [V][P]   drop-in and H_train paths: indexed by Gaussian id
     float4*   recsB;       // unused by the kernels (the H_train path keeps its moment rows in that region)
@@ -44,6 +60,9 @@ struct Bins {
     uint32_t* tile_order;  // [V*tiles]    scoring only (else null): tile slots by descending instance count
     uint32_t* total;       // [4]: total instances (lo), overflow flag, prefiltered-trap flag, max tile count
     u64*      keys;        // [capacity]
+    uint4*    seg_list;    // scoring path (else null): heavy tile lists {tile slot, segments, first item, -} (k_scan_tiles -> k_tile_score_mix);
+                           // total[10] items, [11] ticket counter, [12] lists, [13] longest list in segments
+    uint4*    seg_flags;   // [items][2]  chain flags and completion counters of the work items (fb_score.cuh: SegWs)
     uint4*    sub_list;    // scoring / H_train paths (else null): pieces of the long segments (split_segment in k_sort_tiles); count in total[8], reports in total[9]
     long long capacity;
     int       P;

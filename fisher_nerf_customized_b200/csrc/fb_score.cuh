@@ -304,34 +304,25 @@ struct WarpQ2 { WarpQ q; unsigned char list[32]; unsigned char pad[96]; };
 #endif                            // lane's latency-bound kernels (scatter, sort) find registers and warp slots beside the sweep
 #define FB_S2_SMEM_BYTES ((int)sizeof(WarpQ2) * FB_S2_WPC + FB_S2_SMEM_EXTRA)
 
-template <int D>
-__device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, float grad_scale, int tile_slot, int warp,
-                                          WarpQ2& q2, float* __restrict__ out) {
-    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+struct Px2State { f32x2 T, Cp, Qaa, Qab, Qbb; float athr0, athr1; };   // athr: 1/255 while the pixel is live, 2 once done / outside
+
+// The pair sweep of one 8x8 pixel block (corner bx, by) over n depth-sorted keys, continuing from the state S.
+// MODE 0: the scoring sweep (stop rule, three accumulators).  MODE 1: transmittance and colour only and WITHOUT the
+// stop rule -- the plain products a later segment of the same list needs as its starting state (sweep_px2_segment).
+template <int D, int MODE>
+__device__ __forceinline__ void sweep_px2_core(const char* __restrict__ recA, const char* __restrict__ recB,
+                                               const unsigned* __restrict__ sorted, const int n, const int bx, const int by,
+                                               WarpQ2& q2, Px2State& S, float& stat) {
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
-    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
-    const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
-    const int px = bx + (lane & 7), py0 = by + (lane >> 3), py1 = py0 + 4;
-    const bool in0 = px < cam.W && py0 < cam.H, in1 = px < cam.W && py1 < cam.H;
-    const float pxf = (float)px;
-    const f32x2 npy = f2_pack(-(float)py0, -(float)py1);
+    const float pxf = (float)(bx + (lane & 7));
+    const f32x2 npy = f2_pack(-(float)(by + (lane >> 3)), -(float)(by + (lane >> 3) + 4));
     const float cx = (float)bx + 3.5f, cy = (float)by + 3.5f;
-    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
-    const uint2 range = bins.tile_range[tile_slot];
-    const int n = (int)(range.y - range.x);
-    if (n == 0) { if (lane == 0) *out = 0.f; return; }
-    const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
-    const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
-    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
     WarpQ& q = q2.q;
-
-    f32x2 T = f2_dup(1.0f), Cp = f2_dup(0.f), Qaa = f2_dup(0.f), Qab = f2_dup(0.f), Qbb = f2_dup(0.f);
-#if FB_S2_STATS
-    float stat = 0.f;
-#endif
-    float athr0 = in0 ? 1.0f / 255.0f : 2.0f, athr1 = in1 ? 1.0f / 255.0f : 2.0f;
-    if (__any_sync(0xffffffffu, in0 || in1)) {
+    f32x2 T = S.T, Cp = S.Cp, Qaa = S.Qaa, Qab = S.Qab, Qbb = S.Qbb;
+    float athr0 = S.athr0, athr1 = S.athr1;
+    (void)stat;
+    {
         int qn = 0, qh = 0;
         const int nsteps = (n + 31) >> 5;
         // the 16-byte {px, py, hx, hy} gathers run D scan steps ahead of their use, the keys one more
@@ -368,7 +359,7 @@ __device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, floa
                     const float4* rb = reinterpret_cast<const float4*>(recB + gid * 80u);
                     __pipeline_memcpy_async(&q.b[slot], rb, 16);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + 1 + k, 16);
+                    for (int k = 0; k < (MODE == 0 ? 4 : 1); ++k) __pipeline_memcpy_async(&q.rb[k][slot], rb + 1 + k, 16);
                 }
                 __pipeline_commit();
                 qn += __popc(mask);
@@ -433,6 +424,14 @@ __device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, floa
                     //  skip, forward.cu:343, can only fire within ~1e-7 px of the mean and is not tested here)
                     // athr = 1/255 while the pixel is live, 2 once it is done (alpha <= 0.99 never reaches it)
                     const bool ok0 = al0 >= athr0, ok1 = al1 >= athr1;
+                    if constexpr (MODE == 1) {
+                        if (!__any_sync(0xffffffffu, ok0 || ok1)) continue;
+                        const f32x2 go1 = f2_pack(ok0 ? f2_lo(oG) : 0.f, ok1 ? f2_hi(oG) : 0.f);
+                        const f32x2 aT1 = f2_mul(f2_pack(fminf(0.99f, f2_lo(go1)), fminf(0.99f, f2_hi(go1))), T);
+                        f2_acc(Cp, f2_dup(q.rb[0][slot].x), aT1);
+                        f2_acc(T, aT1, f2_dup(-1.f));
+                        continue;
+                    }
                     const bool upd0 = ok0 && !(f2_lo(tT) < 0.0001f), upd1 = ok1 && !(f2_hi(tT) < 0.0001f);
                     athr0 = (ok0 && !upd0) ? 2.0f : athr0;               // stop BEFORE the Gaussian that takes T below 1e-4
                     athr1 = (ok1 && !upd1) ? 2.0f : athr1;
@@ -472,12 +471,39 @@ __device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, floa
                 }
                 __syncwarp();
                 qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
-                if (__all_sync(0xffffffffu, athr0 > 1.f && athr1 > 1.f)) break;
+                if constexpr (MODE == 1) {      // every pixel's product below the stop threshold: what follows cannot matter
+                    if (__all_sync(0xffffffffu, (athr0 > 1.f || f2_lo(T) < 0.0001f) && (athr1 > 1.f || f2_hi(T) < 0.0001f))) break;
+                } else if (__all_sync(0xffffffffu, athr0 > 1.f && athr1 > 1.f)) break;
             }
         }
         __pipeline_wait_prior(0);
         __syncwarp();
     }
+    S.T = T; S.Cp = Cp; S.Qaa = Qaa; S.Qab = Qab; S.Qbb = Qbb; S.athr0 = athr0; S.athr1 = athr1;
+}
+
+template <int D>
+__device__ __forceinline__ void sweep_px2(const Bins& bins, const Cam& cam, float grad_scale, int tile_slot, int warp,
+                                          WarpQ2& q2, float* __restrict__ out) {
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int lane = threadIdx.x & 31;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
+    const int px = bx + (lane & 7), py0 = by + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < cam.W && py0 < cam.H, in1 = px < cam.W && py1 < cam.H;
+    if (bins.total[1]) { if (lane == 0) *out = 0.f; return; }
+    const uint2 range = bins.tile_range[tile_slot];
+    const int n = (int)(range.y - range.x);
+    if (n == 0) { if (lane == 0) *out = 0.f; return; }
+    const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
+    const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
+    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x);   // low word = visible slot
+    Px2State S;
+    S.T = f2_dup(1.0f); S.Cp = f2_dup(0.f); S.Qaa = f2_dup(0.f); S.Qab = f2_dup(0.f); S.Qbb = f2_dup(0.f);
+    S.athr0 = in0 ? 1.0f / 255.0f : 2.0f; S.athr1 = in1 ? 1.0f / 255.0f : 2.0f;
+    float stat = 0.f;
+    if (__any_sync(0xffffffffu, in0 || in1)) sweep_px2_core<D, 0>(recA, recB, sorted, n, bx, by, q2, S, stat);
+    const f32x2 T = S.T, Cp = S.Cp, Qaa = S.Qaa, Qab = S.Qab, Qbb = S.Qbb;
     const float bgs = (cam.bg[0] + cam.bg[1]) + cam.bg[2];
     const float Cf0 = fmaf(f2_lo(T), bgs, f2_lo(Cp)), Cf1 = fmaf(f2_hi(T), bgs, f2_hi(Cp));     // C + T_final * bg
     const float s0 = fmaf(Cf0, fmaf(Cf0, f2_lo(Qbb), -2.f * f2_lo(Qab)), f2_lo(Qaa));
@@ -503,50 +529,179 @@ __global__ void __launch_bounds__(32 * FB_S2_WPC, FB_S2_MINB) k_tile_score2(Bins
                          partial + (size_t)tile_slot * FB_S2_BLOCKS + warp);
 }
 
-// ---- k_tile_score_mix: one launch, two sweep forms ------------------------------------------------------
+// ---- heavy tile lists: segments swept by different warps -------------------------------------------------
 // A warp walks its tile's list alone, so the longest list of the chunk bounds the kernel: a view along a 30 m floor
-// puts > 100 k tiny splats on each tile of the horizon row (cfg 4: ~30 tiles of a view hold 80 % of its instances) and
-// a lone 8x8 warp needs milliseconds for one of them while the rest of the GPU has drained (measured with clock64 at
-// 3M Gaussians: the longest warp of a view runs as long as the whole kernel; the sum of the warp times fills 7.6 of
-// the 32 resident warps per SM).  Lists of >= FB_HEAVY_KEYS keys therefore go to EIGHT warps of 8x4 pixels (sweep_px1:
-// twice the warps per tile, each with ~60 % of the hits and pixel blocks that saturate sooner) with the record gather
-// FB_HEAVY_PFD scan steps ahead; everything else stays on the 8x8 two-pixel form.
-// Grid: [2 CTAs per tile for the first FB_HEAVY_RANKS ranks of every view's tile order][1 CTA per tile].  A heavy CTA
-// whose tile is not heavy exits at once, and so does the ordinary CTA of a heavy tile.
-// partial: FB_TILE_WARPS floats per tile (the 8x8 form writes four and zeroes four).
-#ifndef FB_HEAVY_KEYS
-#define FB_HEAVY_KEYS 16384
-#endif
-#ifndef FB_HEAVY_RANKS
-#define FB_HEAVY_RANKS 64
-#endif
-#ifndef FB_HEAVY_PFD
-#define FB_HEAVY_PFD 1
-#endif
-#define FB_MIX_SMEM_BYTES ((int)sizeof(WarpQ2) * 4)
-__global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_score_mix(Bins bins, Cam cam, float grad_scale,
-                                                                    float* __restrict__ partial, int heavy_tiles) {
-    extern __shared__ float4 smem[];
-    const int wq = threadIdx.x >> 5;
-    const int heavy_ctas = heavy_tiles * 2;
-    if ((int)blockIdx.x < heavy_ctas) {
-        const int tile_slot = (int)bins.tile_order[blockIdx.x >> 1];
-        const uint2 r = bins.tile_range[tile_slot];
-        if ((int)(r.y - r.x) < FB_HEAVY_KEYS) return;
-        const int warp = (int)(blockIdx.x & 1) * 4 + wq;
-        sweep_px1<FB_HEAVY_PFD>(bins, cam, grad_scale, tile_slot, warp, reinterpret_cast<WarpQ2*>(smem)[wq].q,
-                                partial + (size_t)tile_slot * FB_TILE_WARPS + warp);
-    } else {
-        const int idx = (int)blockIdx.x - heavy_ctas;
-        const int tile_slot = (int)bins.tile_order[idx];
-        if (idx < heavy_tiles) {
-            const uint2 r = bins.tile_range[tile_slot];
-            if ((int)(r.y - r.x) >= FB_HEAVY_KEYS) return;
+// puts > 100 k tiny splats on each tile of the horizon row (cfg 4: ~30 tiles of a view hold 80 % of its instances, the
+// longest list 272 k keys) and a lone warp needs milliseconds for one of them while the rest of the GPU has drained
+// (clock64 per warp at 3M Gaussians: the longest warp of a view runs as long as the whole kernel).
+// The front-to-back recurrence is cut instead.  For a segment [k0, k1) of the list, the state of a pixel after it is
+//   T_out = T_in * Tl,   Cp_out = Cp_in + T_in * Cpl,      Tl = prod (1 - alpha_i),  Cpl = sum c_i alpha_i prod_{j<i} (1 - alpha_j)
+// (products over the pairs with alpha >= 1/255), and the stop rule -- stop BEFORE the Gaussian that takes T below 1e-4
+// -- is a threshold on the same monotone product: a pixel is done on entry to a segment iff T_in < 1e-4.  So
+//   pass 1  every segment but the last computes (Tl, Cpl) of its keys alone (exponent and alpha only: no polynomial,
+//           no accumulators, 32 of the record's 80 bytes), all segments of a list in parallel;
+//   chain   segment s waits for (T_in, Cp_in) of segment s - 1, publishes its own (T_out, Cp_out): a few us per link;
+//   pass 2  the ordinary scoring sweep of the segment's keys from (T_in, Cp_in), stop rule included.
+// The accumulators of the segments add (Q_AA, Q_AB, Q_BB are sums over the list), the final C + T bg is taken from
+// the segment in which the pixel stopped (or the last one), and the warp that finishes a (tile, pixel block) last
+// combines the segments in order: a fixed order of additions, no float atomics.  Against one sequential sweep only
+// the association of the product T_in differs (ulps; a stop decision at the 1e-4 threshold may move by one entry).
+// The heavy lists {tile slot, segments, first item} come from k_scan_tiles; the warps of the first `workers` CTAs of
+// the grid take tickets in the order (segment index, list, pixel block), so the segment a warp waits for has always
+// been started.  While there are more lists than warps the previous segment of a list has FINISHED by the time the next
+// one is taken up: its exact end state is there, pass 1 is skipped, and the list is swept segment after segment at
+// the cost of one sequential sweep (a list whose pixels are all done costs a flag read per remaining segment).  When
+// the lists run out -- the tail this is for -- idle warps take segments whose predecessor is still running, and those
+// go through pass 1 / chain / pass 2 in parallel.
+struct SegWs {
+    float4*   state;   // [items][4 blocks][32 lanes]      {T0, T1, Cp0, Cp1} after the segment (plain products)
+    float4*   out;     // [items][4 blocks][2][32 lanes]   {Qaa0, Qaa1, Qab0, Qab1}, {Qbb0, Qbb1, Cf0, Cf1} (Cf = NaN unless the pixel's final state is here)
+    unsigned* flag;    // [items][8]  0-3: state of the block published; 4-7: finished segments of the block, kept at the
+};                     //             list's first item (bins.seg_flags: zeroed by k_scan_tiles when it emits the item)
+#define FB_SEG_WS_BYTES_PER_ITEM (4 * 32 * 16 + 4 * 64 * 16 + 16 + 16)
+
+template <int D>
+__device__ __forceinline__ void sweep_px2_segment(const Bins& bins, const Cam& cam, float grad_scale, const SegWs& ws,
+                                                  const int tile_slot, const int seg, const int S, const unsigned base,
+                                                  const int warp, WarpQ2& q2, float* __restrict__ partial) {
+    const unsigned item = base + (unsigned)seg;
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int lane = threadIdx.x & 31;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
+    const int px = bx + (lane & 7), py0 = by + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < cam.W && py0 < cam.H, in1 = px < cam.W && py1 < cam.H;
+    const uint2 range = bins.tile_range[tile_slot];
+    const int k0 = seg * FB_SEG_KEYS, n = min((int)(range.y - range.x) - k0, FB_SEG_KEYS);
+    const char* __restrict__ recA = reinterpret_cast<const char*>(bins.recA + (size_t)v * bins.vis_stride);
+    const char* __restrict__ recB = reinterpret_cast<const char*>(bins.recB + (size_t)v * bins.vis_stride * 5);
+    const unsigned* __restrict__ sorted = reinterpret_cast<const unsigned*>(bins.keys + range.x + k0);
+    const bool last = seg + 1 == S;
+    const size_t me = (size_t)item * 4 + warp;
+    volatile unsigned* my_flag = ws.flag + (size_t)item * 8 + warp;
+    volatile unsigned* prev_flag = my_flag - 8;
+    float stat = 0.f;
+    Px2State P;
+    P.T = f2_dup(1.0f); P.Cp = f2_dup(0.f); P.Qaa = f2_dup(0.f); P.Qab = f2_dup(0.f); P.Qbb = f2_dup(0.f);
+    P.athr0 = in0 ? 1.0f / 255.0f : 2.0f; P.athr1 = in1 ? 1.0f / 255.0f : 2.0f;
+    // the state on entry: there already if the previous segment has finished (the usual case while the GPU is busy:
+    // the list is then swept segment after segment at no extra cost); else pass 1 runs on this segment meanwhile
+    f32x2 Tin = f2_dup(1.0f), Cin = f2_dup(0.f);
+    bool have_in = seg == 0;
+    if (seg > 0) {
+        unsigned f = 0;
+        if (lane == 0) f = *prev_flag;
+        f = __shfl_sync(0xffffffffu, f, 0);
+        if (f) {
+            __threadfence();
+            const float4 st = __ldcg(ws.state + (me - 4) * 32 + lane);
+            Tin = f2_pack(st.x, st.y); Cin = f2_pack(st.z, st.w);
+            have_in = true;
         }
-        float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + wq;
-        if ((threadIdx.x & 31) == 0) out[4] = 0.f;
-        sweep_px2<FB_S2_PFD>(bins, cam, grad_scale, tile_slot, wq, reinterpret_cast<WarpQ2*>(smem)[wq], out);
     }
+    const bool direct = have_in;                       // no pass 1: the state published is the exact one after pass 2
+    if (!direct && !last && __any_sync(0xffffffffu, in0 || in1)) sweep_px2_core<D, 1>(recA, recB, sorted, n, bx, by, q2, P, stat);
+    if (!have_in) {
+        if (lane == 0) { while (*prev_flag == 0u) __nanosleep(100); }
+        __syncwarp();
+        __threadfence();
+        const float4 st = __ldcg(ws.state + (me - 4) * 32 + lane);
+        Tin = f2_pack(st.x, st.y); Cin = f2_pack(st.z, st.w);
+    }
+    f32x2 Tout = f2_mul(Tin, P.T), Cout = f2_fma(Tin, P.Cp, Cin);
+    if (!direct && !last) {
+        __stcg(ws.state + me * 32 + lane, make_float4(f2_lo(Tout), f2_hi(Tout), f2_lo(Cout), f2_hi(Cout)));
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) *my_flag = 1u;
+    }
+    // pass 2: the scoring sweep of this segment's keys from (T_in, Cp_in); a pixel is done on entry iff T_in < 1e-4
+    const bool live0 = in0 && !(f2_lo(Tin) < 0.0001f), live1 = in1 && !(f2_hi(Tin) < 0.0001f);
+    P.T = Tin; P.Cp = Cin;
+    P.athr0 = live0 ? 1.0f / 255.0f : 2.0f; P.athr1 = live1 ? 1.0f / 255.0f : 2.0f;
+    if (__any_sync(0xffffffffu, live0 || live1)) sweep_px2_core<D, 0>(recA, recB, sorted, n, bx, by, q2, P, stat);
+    if (direct) {
+        // exact state after the segment; a pixel that stopped inside it is handed on as T = 0 (done)
+        Tout = f2_pack(P.athr0 > 1.f ? 0.f : f2_lo(P.T), P.athr1 > 1.f ? 0.f : f2_hi(P.T));
+        if (!last) {
+            __stcg(ws.state + me * 32 + lane, make_float4(f2_lo(Tout), f2_hi(Tout), f2_lo(P.Cp), f2_hi(P.Cp)));
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) *my_flag = 1u;
+        }
+    }
+    // the pixel's final state is here if it was live on entry and the next segment finds it done (or there is none)
+    const float bgs = (cam.bg[0] + cam.bg[1]) + cam.bg[2];
+    const float qnan = __int_as_float(0x7fc00000);
+    const bool own0 = live0 && (last || f2_lo(Tout) < 0.0001f), own1 = live1 && (last || f2_hi(Tout) < 0.0001f);
+    const float Cf0 = own0 ? fmaf(f2_lo(P.T), bgs, f2_lo(P.Cp)) : qnan, Cf1 = own1 ? fmaf(f2_hi(P.T), bgs, f2_hi(P.Cp)) : qnan;
+    __stcg(ws.out + me * 64 + lane, make_float4(f2_lo(P.Qaa), f2_hi(P.Qaa), f2_lo(P.Qab), f2_hi(P.Qab)));
+    __stcg(ws.out + me * 64 + 32 + lane, make_float4(f2_lo(P.Qbb), f2_hi(P.Qbb), Cf0, Cf1));
+    __threadfence();
+    __syncwarp();
+    unsigned fin = 0;
+    if (lane == 0) fin = atomicAdd(ws.flag + (size_t)base * 8 + 4 + warp, 1u);
+    fin = __shfl_sync(0xffffffffu, fin, 0);
+    if (fin + 1 != (unsigned)S) return;
+    // last to finish this (tile, pixel block): combine the segments in order
+    __threadfence();
+    float Qaa0 = 0.f, Qaa1 = 0.f, Qab0 = 0.f, Qab1 = 0.f, Qbb0 = 0.f, Qbb1 = 0.f, C0 = 0.f, C1 = 0.f;
+    for (int k = 0; k < S; ++k) {
+        const size_t o = ((size_t)(base + k) * 4 + warp) * 64;
+        const float4 u = __ldcg(ws.out + o + lane), w = __ldcg(ws.out + o + 32 + lane);
+        Qaa0 += u.x; Qaa1 += u.y; Qab0 += u.z; Qab1 += u.w; Qbb0 += w.x; Qbb1 += w.y;
+        if (w.z == w.z) C0 = w.z;
+        if (w.w == w.w) C1 = w.w;
+    }
+    const float s0 = fmaf(C0, fmaf(C0, Qbb0, -2.f * Qab0), Qaa0), s1 = fmaf(C1, fmaf(C1, Qbb1, -2.f * Qab1), Qaa1);
+    float score = (grad_scale * grad_scale) * ((in0 ? s0 : 0.f) + (in1 ? s1 : 0.f));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) score += __shfl_xor_sync(0xffffffffu, score, o);
+    if (lane == 0) { partial[(size_t)tile_slot * FB_TILE_WARPS + warp] = score; partial[(size_t)tile_slot * FB_TILE_WARPS + warp + 4] = 0.f; }
+}
+
+// k_tile_score_mix: grid = [workers: CTAs whose warps take (heavy work item, pixel block) tickets][1 CTA per tile, the
+// four 8x8 blocks of the tile; the CTA of a heavy tile exits].  partial: FB_TILE_WARPS floats per tile (four used).
+#define FB_MIX_SMEM_BYTES ((int)sizeof(WarpQ2) * 4)
+#ifndef FB_SEG_WORKERS
+#define FB_SEG_WORKERS (148 * 8)
+#endif
+__global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_score_mix(Bins bins, Cam cam, float grad_scale,
+                                                                    float* __restrict__ partial, SegWs ws, int workers) {
+    extern __shared__ float4 smem[];
+    const int wq = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (bins.total[1]) {
+        if ((int)blockIdx.x >= workers && lane == 0) {
+            float* out = partial + (size_t)bins.tile_order[blockIdx.x - workers] * FB_TILE_WARPS + wq;
+            out[0] = 0.f; out[4] = 0.f;
+        }
+        return;
+    }
+    if ((int)blockIdx.x < workers) {
+        // tickets in the order (segment index, list, pixel block): segment s of every list before any segment s + 1
+        const unsigned row = 4u * bins.total[12], tickets = row * bins.total[13];
+        for (;;) {
+            unsigned tk = 0;
+            if (lane == 0) tk = atomicAdd(&bins.total[11], 1u);
+            tk = __shfl_sync(0xffffffffu, tk, 0);
+            if (tk >= tickets) return;
+            const unsigned sgm = tk / row, r = tk - sgm * row;
+            const uint4 it = bins.seg_list[r >> 2];                        // {tile slot, segments, first item, -}
+            if (sgm < it.y)
+                sweep_px2_segment<FB_S2_PFD>(bins, cam, grad_scale, ws, (int)it.x, (int)sgm, (int)it.y, it.z, (int)(r & 3u),
+                                             reinterpret_cast<WarpQ2*>(smem)[wq], partial);
+            __syncwarp();
+        }
+    }
+    const int idx = (int)blockIdx.x - workers;
+    const int tile_slot = (int)bins.tile_order[idx];
+    if (idx < FB_HEAVY_RANKS * bins.V) {
+        const uint2 r = bins.tile_range[tile_slot];
+        if ((int)(r.y - r.x) >= FB_HEAVY_KEYS) return;                     // its segments are work items
+    }
+    float* out = partial + (size_t)tile_slot * FB_TILE_WARPS + wq;
+    if (lane == 0) out[4] = 0.f;
+    sweep_px2<FB_S2_PFD>(bins, cam, grad_scale, tile_slot, wq, reinterpret_cast<WarpQ2*>(smem)[wq], out);
 }
 
 // ---- per-Gaussian Hessian moments (compute_H_train), warp-autonomous form ----------------------------------

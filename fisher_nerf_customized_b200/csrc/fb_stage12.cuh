@@ -564,6 +564,18 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
         const unsigned c = tc[(size_t)i * FB_TC_STRIDE];
         const unsigned pos = atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
         bins.tile_order[(size_t)pos * V + v] = (unsigned)(v * n + i);
+        // a heavy list: ceil(c / FB_SEG_KEYS) segments, their state / output rows reserved consecutively
+        if (bins.seg_list && pos < FB_HEAVY_RANKS && c >= FB_HEAVY_KEYS) {
+            const unsigned S = (c + FB_SEG_KEYS - 1) / FB_SEG_KEYS;
+            const unsigned base = atomicAdd(&bins.total[10], S);           // items (state / output rows) of the chunk
+            const unsigned l = atomicAdd(&bins.total[12], 1u);             // lists
+            atomicMax(&bins.total[13], S);
+            bins.seg_list[l] = make_uint4((unsigned)(v * n + i), S, base, 0u);
+            for (unsigned k = 0; k < S; ++k) {
+                bins.seg_flags[2 * (base + k)] = make_uint4(0u, 0u, 0u, 0u);
+                bins.seg_flags[2 * (base + k) + 1] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
     }
 }
 

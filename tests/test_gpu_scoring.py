@@ -433,3 +433,42 @@ def test_morton_order_and_incremental_map(cuda):
                                scorer.score_candidates(full, poses[2:], w).cpu().numpy(), rtol=1e-4)
     with pytest.raises(RuntimeError):
         grown.append_rows(params, 5, 1)                                        # rows must start behind the live ones
+
+
+def test_heavy_tile_lists_split_sort_and_segmented_sweep(cuda):
+    """Tile lists of >= 16384 keys take their own paths: the sort partitions them by depth and sorts the pieces with
+    other CTAs, the pair sweep cuts them into segments chained through global memory.  120k small, faint Gaussians on a
+    32 x 32 image (4 tiles, ~200 distinct depths so that the pieces are full of ties) put > 30k keys on every tile with
+    pixels that stay live over several segments and others that stop inside one.  Checked against the caller's loop
+    through the drop-in rasteriser, whose kernels (single-view binning, k_render_warp / k_bwd_warp) share none of this."""
+    import torch
+    W = H = 32
+    P = 120_000
+    rng = np.random.default_rng(77)
+    sc = common.random_view_scene(P, 77, W, H)
+    z = np.round(rng.uniform(1.0, 3.0, P), 2).astype(np.float32)
+    sc["means3D"][:, 0] = rng.uniform(-0.8, 0.8, P).astype(np.float32)
+    sc["means3D"][:, 1] = rng.uniform(-0.8, 0.8, P).astype(np.float32)
+    sc["means3D"][:, 2] = z
+    sc["scales"][:] = rng.uniform(0.01, 0.03, (P, 3)).astype(np.float32)
+    sc["opacities"][:] = rng.uniform(0.01, 0.08, (P, 1)).astype(np.float32)
+    eye = np.eye(4, dtype=np.float32)
+    rs = cuda.setup_camera(W, H, common.K_for(W, H), eye)
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    gmap = cuda.GaussianMap(t["means3D"], t["rgb_colors"], t["rotations"], t["opacities"], t["scales"], spatial_order=False)
+    H_want = _caller_loop_H(cuda, torch, rs, sc, eye, 4)
+    scorer = cuda.FisherScorer(rs, C_H=4, views_per_chunk=2)
+    Hinv = torch.reciprocal(H_want + 0.1)
+    poses = torch.from_numpy(np.stack([eye, eye, eye])).cuda()
+    s = scorer.score_candidates(gmap, poses, Hinv).cpu().numpy()
+    assert scorer.last_status[2] >= 16384, scorer.last_status          # the longest tile list: the heavy paths ran
+    np.testing.assert_allclose(s, np.full(3, float((H_want * Hinv).sum())), rtol=RTOL)
+    assert s[0] == s[1] == s[2]                                         # same view, same bits: the combine order is fixed
+    # run to run as well
+    s2 = scorer.score_candidates(gmap, poses, Hinv).cpu().numpy()
+    np.testing.assert_array_equal(s, s2)
+    # the H_train path sorts the same lists through the split sort
+    H_got = scorer.compute_Hessian(gmap, torch.from_numpy(eye).cuda())
+    scale = H_want.abs().amax(dim=0, keepdim=True)
+    bad = (H_got - H_want).abs() > RTOL * H_want.abs() + RTOL * 1e-3 * scale
+    assert bad.float().mean().item() < 2e-3

@@ -13,6 +13,9 @@
 #ifndef FB_SORT_SUB_CTAS
 #define FB_SORT_SUB_CTAS (148 * 6)
 #endif
+#ifndef FB_HESS_PX2_MIN_TILES
+#define FB_HESS_PX2_MIN_TILES 8192     // (view, tile) pairs of a chunk from which k_tile_hessian2 is used
+#endif
 #ifndef FB_SCORE_PX2
 #define FB_SCORE_PX2 1
 #endif
@@ -377,6 +380,7 @@ int fb_accumulate_hessian_sets(const fb_camera* c, const fb_map* map, const floa
     if (!ds->hess_attr) {
         FB_CUDA(cudaFuncSetAttribute(k_sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SORT_SMEM_BYTES));
         FB_CUDA(cudaFuncSetAttribute(k_tile_hessian, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_SCORE_SMEM_BYTES));
+        FB_CUDA(cudaFuncSetAttribute(k_tile_hessian2, cudaFuncAttributeMaxDynamicSharedMemorySize, FB_MIX_SMEM_BYTES));
         ds->hess_attr = true; ds->sort_attr = true;
     }
     const int V = views_per_chunk;
@@ -408,6 +412,13 @@ int fb_accumulate_hessian_sets(const fb_camera* c, const fb_map* map, const floa
             { FB_PROF(FB_K_SORT); k_sort_tiles<<<b.tiles * Vc + sub_ctas, 256, FB_SORT_SMEM_BYTES, st>>>(b, (u64*)(ws + L.keys_alt), FB_SORT_SMEM_KEYS, b.tiles * Vc, split_slots); }
         }
         FB_LAUNCH_CHECK();
+#if FB_HESS_PX2
+        // the 8x8 two-pixel form issues fewer instructions; with few (view, tile) pairs the 8x4 form's twice as many warps win
+        // (at 256 tiles, 8x4 against 8x8 form: 4 keyframes 369 / 584 us, 16: 981 / 1041, 32: 2041 / 1857, 64: 4068 / 3559)
+        if ((long long)b.tiles * Vc >= FB_HESS_PX2_MIN_TILES)
+        { FB_PROF(FB_K_BWD_TILES); k_tile_hessian2<<<b.tiles * Vc, 128, FB_MIX_SMEM_BYTES, st>>>(b, cam, map->colors, grad_scale, mom); }
+        else
+#endif
         { FB_PROF(FB_K_BWD_TILES); k_tile_hessian<<<dim3(b.tiles * (FB_TILE_WARPS / FB_SCORE_WPC), Vc), 32 * FB_SCORE_WPC, FB_SCORE_SMEM_BYTES, st>>>(
               b, cam, map->colors, grad_scale, mom); }
         FB_LAUNCH_CHECK();

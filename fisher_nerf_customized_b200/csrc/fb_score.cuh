@@ -891,6 +891,183 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, C
     }
 }
 
+// ---- k_tile_hessian2: the H_train moments on 8x8 blocks, two pixels per lane ---------------------------------
+// Same quantities as k_tile_hessian in the form of the scoring sweep: a warp owns an 8x8 pixel block, a lane the pixels
+// (x, y) and (x, y + 4), packed FP32 where the two differ, the exact ellipse test on every ring batch.  Both passes run
+// FRONT TO BACK with the same recurrence (and therefore stop at the same entry): pass 0 leaves C' = C + T_final bg of
+// every pixel, pass 1 forms dL/dalpha_i = A_i - C' B_i as the scoring sweep does ("single sweep" above) -- no
+// back-to-front traversal, no T / (1 - alpha) reconstruction -- and adds  s^2 dx^i dy^j  of the 64 pixels to the
+// Gaussian's row: two pixels summed in the lane, the halving butterfly, one red.global.add.v4.f32 per quad.
+// Half as many (Gaussian, block) reductions and atomics as with 8x4 blocks, a sixth fewer bodies (exact test).
+#ifndef FB_HESS_PX2
+#define FB_HESS_PX2 1
+#endif
+template <int PASS>
+__device__ __forceinline__ void hess_px2_pass(const GRec* __restrict__ recs, const float* __restrict__ colors,
+                                              const u64* __restrict__ sorted, const int n, const int bx, const int by,
+                                              WarpQ2& q2, Px2State& S, const f32x2 Cf, const float dpix, float* __restrict__ mom) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const float pxf = (float)(bx + (lane & 7));
+    const f32x2 npy = f2_pack(-(float)(by + (lane >> 3)), -(float)(by + (lane >> 3) + 4));
+    const float cx = (float)bx + 3.5f, cy = (float)by + 3.5f;
+    WarpQ& q = q2.q;
+    f32x2 T = S.T, Cp = S.Cp;
+    float athr0 = S.athr0, athr1 = S.athr1;
+    const int rslot = reduce16_slot(lane);
+    int qn = 0, qh = 0;
+    const int nsteps = (n + 31) >> 5;
+    bool v_nxt = lane < n;
+    unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
+    float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+    u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+    for (int step = 0; step <= nsteps; ++step) {
+        if (step < nsteps) {
+            const float4 a = a_nxt;
+            const unsigned gid = gid_nxt;
+            const bool valid = v_nxt;
+            v_nxt = (step + 1) * 32 + lane < n;
+            gid_nxt = (unsigned)(key2 & 0xffffffffull);
+            if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
+            key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+            const bool hit = valid && (fabsf(a.x - cx) <= a.z + 3.5f) && (fabsf(a.y - cy) <= a.w + 3.5f);
+            const unsigned mask = __ballot_sync(0xffffffffu, hit);
+            if (hit) {
+                const int slot = (qh + qn + __popc(mask & lt)) & (FB_WQ - 1);
+                q.a[slot] = make_float4(a.x, a.y, 0.f, __uint_as_float(gid));
+                __pipeline_memcpy_async(&q.b[slot], reinterpret_cast<const float4*>(recs + gid) + 1, 16);
+                const float* c = colors + 3 * (size_t)gid;
+                float* dst = reinterpret_cast<float*>(&q.rb[0][slot]);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) __pipeline_memcpy_async(dst + k, c + k, 4);
+            }
+            __pipeline_commit();
+            qn += __popc(mask);
+        }
+        const bool flush = (step == nsteps);
+        if (qn >= 32 || (flush && qn > 0)) {
+            const int cnt = min(qn, 32);
+            __pipeline_wait_prior(0);
+            __syncwarp();
+            unsigned todo = cnt == 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+            {
+                // lane h owns ring entry qh + h: the conic goes into the exponent's log2 units (as the scoring records
+                // carry it), then the exact ellipse / block test of sweep_px2_core
+                float4 co = q.b[qh + lane];
+                co.x *= -0.72134752044448170f; co.y *= -1.4426950408889634f; co.z *= -0.72134752044448170f;
+                q.b[qh + lane] = co;
+                const float4 a = q.a[qh + lane];
+                const float X1 = a.x - (float)bx, X0 = X1 - 7.f, Y1 = a.y - (float)by, Y0 = Y1 - 7.f;
+                const float ia = score_rcp(co.x + co.x), ic = score_rcp(co.z + co.z);
+                auto pw = [&](float x, float y) { return fmaf(co.z, y * y, x * fmaf(co.y, y, co.x * x)); };
+                auto ex_ = [&](float Y) { return pw(fminf(fmaxf(-co.y * Y * ia, X0), X1), Y); };
+                auto ey_ = [&](float X) { return pw(X, fminf(fmaxf(-co.y * X * ic, Y0), Y1)); };
+                float m = fmaxf(fmaxf(ex_(Y0), ex_(Y1)), fmaxf(ey_(X0), ey_(X1)));
+                if (X0 <= 0.f && X1 >= 0.f && Y0 <= 0.f && Y1 >= 0.f) m = 0.f;
+                float lg;
+                asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(255.0f * co.w));
+                const bool keep = !(m < -lg - 0.02f);
+                todo &= __ballot_sync(0xffffffffu, keep);
+            }
+            if ((todo >> lane) & 1u) q2.list[__popc(todo & lt)] = (unsigned char)(qh + lane);
+            __syncwarp();
+            const int nkeep = __popc(todo);
+            for (int i = 0; i < nkeep; ++i) {
+                const int slot = q2.list[i];
+                const float4 mu = q.a[slot];
+                const float4 co = q.b[slot];
+                const float dx = mu.x - pxf;
+                const f32x2 dy = f2_add(f2_dup(mu.y), npy);
+                const float Adx = co.x * dx;
+                const float q0 = Adx * dx, q1 = co.y * dx;
+                const f32x2 pw = f2_fma(f2_fma(f2_dup(co.z), dy, f2_dup(q1)), dy, f2_dup(q0));
+                const float G0 = score_ex2(f2_lo(pw)), G1 = score_ex2(f2_hi(pw));
+                const f32x2 oG = f2_mul(f2_dup(co.w), f2_pack(G0, G1));
+                const float al0 = fminf(0.99f, f2_lo(oG)), al1 = fminf(0.99f, f2_hi(oG));
+                const f32x2 oma = f2_fma(f2_pack(al0, al1), f2_dup(-1.f), f2_dup(1.f));
+                const f32x2 tT = f2_mul(T, oma);
+                const bool ok0 = al0 >= athr0, ok1 = al1 >= athr1;
+                const bool upd0 = ok0 && !(f2_lo(tT) < 0.0001f), upd1 = ok1 && !(f2_hi(tT) < 0.0001f);
+                athr0 = (ok0 && !upd0) ? 2.0f : athr0;
+                athr1 = (ok1 && !upd1) ? 2.0f : athr1;
+                if (!__any_sync(0xffffffffu, upd0 || upd1)) continue;
+                const float4 c3 = q.rb[0][slot];
+                const float csum = (c3.x + c3.y) + c3.z;
+                const f32x2 go = f2_pack(upd0 ? f2_lo(oG) : 0.f, upd1 ? f2_hi(oG) : 0.f);
+                const f32x2 aT = f2_mul(f2_pack(fminf(0.99f, f2_lo(go)), fminf(0.99f, f2_hi(go))), T);
+                if constexpr (PASS == 0) {
+                    f2_acc(Cp, f2_dup(csum), aT);
+                    f2_acc(T, aT, f2_dup(-1.f));
+                } else {
+                    const f32x2 inv = f2_pack(score_rcp(f2_lo(oma)), score_rcp(f2_hi(oma)));
+                    f2_acc(Cp, f2_dup(csum), aT);
+                    const f32x2 A = f2_fma(T, f2_dup(csum), f2_mul(Cp, inv));
+                    f2_acc(T, aT, f2_dup(-1.f));
+                    const f32x2 dLda = f2_fma(f2_mul(Cf, f2_dup(-1.f)), inv, A);               // A - C' B
+                    const f32x2 sv = f2_mul(f2_mul(go, dLda), f2_dup(dpix));
+                    const f32x2 qq = f2_mul(sv, sv);
+                    const f32x2 dxx = f2_dup(dx);
+                    const f32x2 qx = f2_mul(qq, dxx), qy = f2_mul(qq, dy);
+                    const f32x2 m20 = f2_mul(qx, dxx), m11 = f2_mul(qx, dy), m02 = f2_mul(qy, dy);
+                    const f32x2 m30 = f2_mul(m20, dxx), m21 = f2_mul(m20, dy), m12 = f2_mul(m02, dxx), m03 = f2_mul(m02, dy);
+                    const f32x2 m40 = f2_mul(m30, dxx), m31 = f2_mul(m30, dy), m22 = f2_mul(m21, dy), m13 = f2_mul(m03, dxx), m04 = f2_mul(m03, dy);
+                    float m[FB_NACC];
+                    m[0] = f2_lo(qq) + f2_hi(qq);   m[1] = f2_lo(m20) + f2_hi(m20); m[2] = f2_lo(m11) + f2_hi(m11);
+                    m[3] = f2_lo(m02) + f2_hi(m02); m[4] = f2_lo(m30) + f2_hi(m30); m[5] = f2_lo(m21) + f2_hi(m21);
+                    m[6] = f2_lo(m12) + f2_hi(m12); m[7] = f2_lo(m03) + f2_hi(m03); m[8] = f2_lo(m40) + f2_hi(m40);
+                    m[9] = f2_lo(m31) + f2_hi(m31); m[10] = f2_lo(m22) + f2_hi(m22); m[11] = f2_lo(m13) + f2_hi(m13);
+                    m[12] = f2_lo(m04) + f2_hi(m04); m[13] = 0.f; m[14] = 0.f; m[15] = 0.f;
+                    const float tot = warp_reduce16(m, lane);        // even lane L holds the block sum of moment rslot
+                    float4 quad;
+                    quad.x = tot;
+                    quad.y = __shfl_down_sync(0xffffffffu, tot, 2);
+                    quad.z = __shfl_down_sync(0xffffffffu, tot, 4);
+                    quad.w = __shfl_down_sync(0xffffffffu, tot, 6);
+                    if ((lane & 7) == 0 && (quad.x != 0.f || quad.y != 0.f || quad.z != 0.f || quad.w != 0.f))
+                        atomicAdd(reinterpret_cast<float4*>(mom + (size_t)__float_as_uint(mu.w) * FB_NACC) + (rslot >> 2), quad);
+                }
+            }
+            __syncwarp();
+            qn -= cnt; qh = (qh + cnt) & (FB_WQ - 1);
+            if (__all_sync(0xffffffffu, athr0 > 1.f && athr1 > 1.f)) break;
+        }
+    }
+    __pipeline_wait_prior(0);
+    __syncwarp();
+    S.T = T; S.Cp = Cp; S.athr0 = athr0; S.athr1 = athr1;
+}
+
+__global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_hessian2(Bins bins, Cam cam, const float* __restrict__ colors,
+                                                                   float grad_scale, float* __restrict__ mom_all) {
+    extern __shared__ float4 smem[];
+    const int tile_slot = (int)bins.tile_order[blockIdx.x];
+    const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tx = t % cam.tiles_x, ty = t / cam.tiles_x;
+    const int bx = tx * FB_TILE_X + (warp & 1) * 8, by = ty * FB_TILE_Y + (warp >> 1) * 8;
+    const int px = bx + (lane & 7), py0 = by + (lane >> 3), py1 = py0 + 4;
+    const bool in0 = px < cam.W && py0 < cam.H, in1 = px < cam.W && py1 < cam.H;
+    if (bins.total[1]) return;
+    const uint2 range = bins.tile_range[tile_slot];
+    const int n = (int)(range.y - range.x);
+    if (n == 0 || !__any_sync(0xffffffffu, in0 || in1)) return;
+    const GRec* __restrict__ recs = bins.recs + (size_t)v * bins.P;
+    float* __restrict__ mom = mom_all + (size_t)v * bins.P * FB_NACC;
+    const u64* __restrict__ sorted = bins.keys + range.x;
+    WarpQ2& q2 = reinterpret_cast<WarpQ2*>(smem)[warp];
+    Px2State S;
+    S.T = f2_dup(1.0f); S.Cp = f2_dup(0.f);
+    S.athr0 = in0 ? 1.0f / 255.0f : 2.0f; S.athr1 = in1 ? 1.0f / 255.0f : 2.0f;
+    hess_px2_pass<0>(recs, colors, sorted, n, bx, by, q2, S, f2_dup(0.f), 0.f, nullptr);
+    const float bgs = (cam.bg[0] + cam.bg[1]) + cam.bg[2];
+    const f32x2 Cf = f2_pack(fmaf(f2_lo(S.T), bgs, f2_lo(S.Cp)), fmaf(f2_hi(S.T), bgs, f2_hi(S.Cp)));
+    S.T = f2_dup(1.0f); S.Cp = f2_dup(0.f);
+    S.athr0 = in0 ? 1.0f / 255.0f : 2.0f; S.athr1 = in1 ? 1.0f / 255.0f : 2.0f;
+    __syncwarp();
+    hess_px2_pass<1>(recs, colors, sorted, n, bx, by, q2, S, Cf, grad_scale, mom);
+}
+
 // scores[k0 + v] = sum over (tile, pixel block) of partial[v][t][w], fixed order (deterministic given partials).
 __global__ void k_score_finalize(const float* __restrict__ partial, int tiles, float* __restrict__ scores) {
     const int v = blockIdx.x;

@@ -568,6 +568,9 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
         if (bins.seg_list && pos < FB_HEAVY_RANKS && c >= FB_HEAVY_KEYS) {
             const unsigned S = (c + FB_SEG_KEYS - 1) / FB_SEG_KEYS;
             const unsigned base = atomicAdd(&bins.total[10], S);           // items (state / output rows) of the chunk
+            // (the rows are sized for `capacity` instances; a chunk that needs more raises the overflow flag below and
+            //  none of its later kernels runs, so the list is simply not written)
+            if ((size_t)base + S > seg_item_capacity(bins.capacity, (long long)V * FB_HEAVY_RANKS)) continue;
             const unsigned l = atomicAdd(&bins.total[12], 1u);             // lists
             atomicMax(&bins.total[13], S);
             bins.seg_list[l] = make_uint4((unsigned)(v * n + i), S, base, 0u);

@@ -467,6 +467,11 @@ def test_heavy_tile_lists_split_sort_and_segmented_sweep(cuda):
     # run to run as well
     s2 = scorer.score_candidates(gmap, poses, Hinv).cpu().numpy()
     np.testing.assert_array_equal(s, s2)
+    # an instance capacity that is far too small at first: the chunk is flagged, nothing of it runs, the driver grows and repeats
+    tight = cuda.FisherScorer(rs, C_H=4, views_per_chunk=2, inst_capacity=1000)
+    s3 = tight.score_candidates(gmap, poses, Hinv).cpu().numpy()
+    assert tight.inst_capacity > 1000
+    np.testing.assert_array_equal(s3, s)
     # the H_train path sorts the same lists through the split sort
     H_got = scorer.compute_Hessian(gmap, torch.from_numpy(eye).cuda())
     scale = H_want.abs().amax(dim=0, keepdim=True)

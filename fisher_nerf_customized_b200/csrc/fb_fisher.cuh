@@ -281,12 +281,61 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
     }
 }
 
+#ifndef FB_COEF11_DIRECT
+#define FB_COEF11_DIRECT 1
+#endif
 template <int CH, bool FAST = false, bool IDENT = false>
 __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, const SRCtx& sr, float A, float B, float C,
                                             float op, const float* __restrict__ w, float* coef) {
     constexpr int NOUT = (CH == 11) ? 10 : 3;
-    float col[5][NOUT];
     const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
+    if constexpr (CH == 11 && FB_COEF11_DIRECT) {
+        // The mean columns as for C_H = 4; the scale / rotation columns depend on phi only through the conic
+        // (phi0..2): dL/dcov3D = N K e_i with K as in mean_chain_matrix and N the T-products of backward.cu:370-390,
+        // then chain_scale_rot -- three short passes instead of five through the whole chain, and no 5 x 10 array
+        // (which cost 708 bytes of spills at 80 registers).
+        float M[3][5];
+        mean_chain_matrix<FAST, IDENT>(ctx, cam, A, B, C, halfW, halfH, M);
+        const float a = ctx.c2.a, b = ctx.c2.b, c = ctx.c2.c, denom = ctx.denom;
+        const float h = -0.5f * ctx.d2i, dmac = denom - a * c;
+        float K[3][3];
+        K[0][0] = h * (-c * c);        K[0][1] = h * (2.f * b * c);                 K[0][2] = h * dmac;
+        K[1][0] = 2.f * h * (b * c);   K[1][1] = -2.f * h * (denom + 2.f * b * b);  K[1][2] = 2.f * h * (a * b);
+        K[2][0] = h * dmac;            K[2][1] = h * (2.f * a * b);                 K[2][2] = h * (-a * a);
+        const M3& T = ctx.c2.T;
+        float Z[3][7];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const float da = K[0][i], db = K[1][i], dc = K[2][i];
+            float d6[6];
+            d6[0] = T.c[0][0] * T.c[0][0] * da + T.c[0][0] * T.c[1][0] * db + T.c[1][0] * T.c[1][0] * dc;
+            d6[3] = T.c[0][1] * T.c[0][1] * da + T.c[0][1] * T.c[1][1] * db + T.c[1][1] * T.c[1][1] * dc;
+            d6[5] = T.c[0][2] * T.c[0][2] * da + T.c[0][2] * T.c[1][2] * db + T.c[1][2] * T.c[1][2] * dc;
+            d6[1] = 2 * T.c[0][0] * T.c[0][1] * da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][1] * dc;
+            d6[2] = 2 * T.c[0][0] * T.c[0][2] * da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][2] * dc;
+            d6[4] = 2 * T.c[0][2] * T.c[0][1] * da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * db + 2 * T.c[1][1] * T.c[1][2] * dc;
+            chain_scale_rot(sr, d6, &Z[i][0], &Z[i][3]);
+        }
+#pragma unroll
+        for (int m = 0; m < 13; ++m) coef[m] = 0.f;
+        coef[0] = fdiv<FAST>(w[3], op * op);
+        const int tab[5][5] = {{8, 9, 10, 4, 5}, {9, 10, 11, 5, 6}, {10, 11, 12, 6, 7}, {4, 5, 6, 1, 2}, {5, 6, 7, 2, 3}};
+#pragma unroll
+        for (int i = 0; i < 5; ++i)
+#pragma unroll
+            for (int j = i; j < 5; ++j) {
+                float bsum = 0.f;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) bsum += w[k] * M[k][i] * M[k][j];
+                if (i < 3 && j < 3) {
+#pragma unroll
+                    for (int k = 0; k < 7; ++k) bsum += w[4 + k] * Z[i][k] * Z[j][k];
+                }
+                coef[tab[i][j]] += (i == j) ? bsum : 2.f * bsum;
+            }
+        return;
+    }
+    float col[5][NOUT];
     if (CH == 4) {
         float M[3][5];
         mean_chain_matrix<FAST, IDENT>(ctx, cam, A, B, C, halfW, halfH, M);

@@ -314,7 +314,10 @@ template <int CH>
 #ifndef FB_PS_MINB
 #define FB_PS_MINB 3
 #endif
-__global__ void __launch_bounds__(FB_PS_THREADS, FB_PS_MINB) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
+#ifndef FB_PS_MINB11
+#define FB_PS_MINB11 3          // C_H = 11 (2: 128 registers, no spills, 907 us; 3: 80 registers, 184 B of spills, 890 us per 64 views)
+#endif
+__global__ void __launch_bounds__(FB_PS_THREADS, (CH > 4 ? FB_PS_MINB11 : FB_PS_MINB)) k_preprocess_score(GaussIn g, Cam cam, const float* __restrict__ w2c,
                                                                     Bins bins, const float* __restrict__ weight,
                                                                     const int* __restrict__ weight_set) {
     // weight_set (optional): view v scores against weight tensor weight_set[v] of a [sets][P][CH] array (path

@@ -510,31 +510,32 @@ __global__ void __launch_bounds__(128) k_expand_H(Bins bins, GaussIn g, Cam cam,
         pc.y = fmaf(w2c[6], p.z, fmaf(w2c[5], p.y, w2c[4] * p.x)) + w2c[7];
         pc.z = fmaf(w2c[10], p.z, fmaf(w2c[9], p.y, w2c[8] * p.x)) + w2c[11];
         const GCtx ctx = make_ctx(pc, cov6, cam);
-        float col[5][NOUT];
+        // columns of the chain: means through mean_chain_matrix, scale / rotation through scale_rot_matrix (they
+        // depend on phi only through its conic part) -- one pass each instead of five through chain_geom
         const float halfW = 0.5f * cam.W, halfH = 0.5f * cam.H;
+        float M[3][5];
+        mean_chain_matrix(ctx, cam, r.b.x, r.b.y, r.b.z, halfW, halfH, M);
 #pragma unroll
-        for (int b = 0; b < 5; ++b) {
-            float e[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-            e[b] = 1.f;
-            float u[5];
-            phi_to_u(e, r.b.x, r.b.y, r.b.z, halfW, halfH, u);
-            ChainOut co = chain_geom(ctx, cam, u[0], u[1], u[2], u[3], u[4]);
-            col[b][0] = co.mean[0]; col[b][1] = co.mean[1]; col[b][2] = co.mean[2];
-            if (CH == 11) {
-                float ds[3], dr[4];
-                chain_scale_rot(sr, co.cov3D, ds, dr);
-                col[b][3] = ds[0]; col[b][4] = ds[1]; col[b][5] = ds[2];
-                col[b][6] = dr[0]; col[b][7] = dr[1]; col[b][8] = dr[2]; col[b][9] = dr[3];
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < NOUT; ++k) {
+        for (int k = 0; k < 3; ++k) {
             double sum = 0.0;
 #pragma unroll
             for (int a = 0; a < 5; ++a)
 #pragma unroll
-                for (int b = 0; b < 5; ++b) sum += (double)col[a][k] * (double)col[b][k] * (double)moment_phi(acc, a, b);
+                for (int b = 0; b < 5; ++b) sum += (double)M[k][a] * (double)M[k][b] * (double)moment_phi(acc, a, b);
             Hk[k] += (double)(float)sum;          // each view's term is rounded to float as the per-view tensor is
+        }
+        if (CH == 11) {
+            float Z[3][7];
+            scale_rot_matrix(ctx, sr, Z);
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                double sum = 0.0;
+#pragma unroll
+                for (int a = 0; a < 3; ++a)
+#pragma unroll
+                    for (int b = 0; b < 3; ++b) sum += (double)Z[a][k] * (double)Z[b][k] * (double)moment_phi(acc, a, b);
+                Hk[(CH == 11) ? 3 + k : 0] += (double)(float)sum;
+            }
         }
         Hop += (double)(acc[0] / (r.b.w * r.b.w));          // batched record layout: opacity in b.w
     }

@@ -281,6 +281,31 @@ __device__ __forceinline__ void mean_chain_matrix(const GCtx& g, const Cam& cam,
     }
 }
 
+// Z[i][0..6] = d(scale 3, rotation 4) / d(phi_i) for the three conic components of phi (the mean2D components do not
+// reach cov3D): dL/dcov3D = N K e_i with K as in mean_chain_matrix (the -1/2 of phi_to_u folded in) and N the
+// T-products of backward.cu:370-390, then chain_scale_rot.  Equal to chain_geom + chain_scale_rot on unit vectors.
+__device__ __forceinline__ void scale_rot_matrix(const GCtx& g, const SRCtx& sr, float Z[3][7]) {
+    const float a = g.c2.a, b = g.c2.b, c = g.c2.c, denom = g.denom;
+    const float h = -0.5f * g.d2i, dmac = denom - a * c;
+    float K[3][3];
+    K[0][0] = h * (-c * c);        K[0][1] = h * (2.f * b * c);                 K[0][2] = h * dmac;
+    K[1][0] = 2.f * h * (b * c);   K[1][1] = -2.f * h * (denom + 2.f * b * b);  K[1][2] = 2.f * h * (a * b);
+    K[2][0] = h * dmac;            K[2][1] = h * (2.f * a * b);                 K[2][2] = h * (-a * a);
+    const M3& T = g.c2.T;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const float da = K[0][i], db = K[1][i], dc = K[2][i];
+        float d6[6];
+        d6[0] = T.c[0][0] * T.c[0][0] * da + T.c[0][0] * T.c[1][0] * db + T.c[1][0] * T.c[1][0] * dc;
+        d6[3] = T.c[0][1] * T.c[0][1] * da + T.c[0][1] * T.c[1][1] * db + T.c[1][1] * T.c[1][1] * dc;
+        d6[5] = T.c[0][2] * T.c[0][2] * da + T.c[0][2] * T.c[1][2] * db + T.c[1][2] * T.c[1][2] * dc;
+        d6[1] = 2 * T.c[0][0] * T.c[0][1] * da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][1] * dc;
+        d6[2] = 2 * T.c[0][0] * T.c[0][2] * da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][2] * dc;
+        d6[4] = 2 * T.c[0][2] * T.c[0][1] * da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * db + 2 * T.c[1][1] * T.c[1][2] * dc;
+        chain_scale_rot(sr, d6, &Z[i][0], &Z[i][3]);
+    }
+}
+
 #ifndef FB_COEF11_DIRECT
 #define FB_COEF11_DIRECT 1
 #endif
@@ -296,26 +321,8 @@ __device__ __forceinline__ void score_coefs(const GCtx& ctx, const Cam& cam, con
         // (which cost 708 bytes of spills at 80 registers).
         float M[3][5];
         mean_chain_matrix<FAST, IDENT>(ctx, cam, A, B, C, halfW, halfH, M);
-        const float a = ctx.c2.a, b = ctx.c2.b, c = ctx.c2.c, denom = ctx.denom;
-        const float h = -0.5f * ctx.d2i, dmac = denom - a * c;
-        float K[3][3];
-        K[0][0] = h * (-c * c);        K[0][1] = h * (2.f * b * c);                 K[0][2] = h * dmac;
-        K[1][0] = 2.f * h * (b * c);   K[1][1] = -2.f * h * (denom + 2.f * b * b);  K[1][2] = 2.f * h * (a * b);
-        K[2][0] = h * dmac;            K[2][1] = h * (2.f * a * b);                 K[2][2] = h * (-a * a);
-        const M3& T = ctx.c2.T;
         float Z[3][7];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            const float da = K[0][i], db = K[1][i], dc = K[2][i];
-            float d6[6];
-            d6[0] = T.c[0][0] * T.c[0][0] * da + T.c[0][0] * T.c[1][0] * db + T.c[1][0] * T.c[1][0] * dc;
-            d6[3] = T.c[0][1] * T.c[0][1] * da + T.c[0][1] * T.c[1][1] * db + T.c[1][1] * T.c[1][1] * dc;
-            d6[5] = T.c[0][2] * T.c[0][2] * da + T.c[0][2] * T.c[1][2] * db + T.c[1][2] * T.c[1][2] * dc;
-            d6[1] = 2 * T.c[0][0] * T.c[0][1] * da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][1] * dc;
-            d6[2] = 2 * T.c[0][0] * T.c[0][2] * da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * db + 2 * T.c[1][0] * T.c[1][2] * dc;
-            d6[4] = 2 * T.c[0][2] * T.c[0][1] * da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * db + 2 * T.c[1][1] * T.c[1][2] * dc;
-            chain_scale_rot(sr, d6, &Z[i][0], &Z[i][3]);
-        }
+        scale_rot_matrix(ctx, sr, Z);
 #pragma unroll
         for (int m = 0; m < 13; ++m) coef[m] = 0.f;
         coef[0] = fdiv<FAST>(w[3], op * op);

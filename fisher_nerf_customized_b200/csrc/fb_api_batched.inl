@@ -19,7 +19,7 @@
 #ifndef FB_SCORE_PX2
 #define FB_SCORE_PX2 1
 #endif
-// FB_SCORE_MIX (default, with FB_SCORE_PX2): k_tile_score_mix -- lists of >= FB_HEAVY_KEYS keys go to the 8x4 form.
+// FB_SCORE_MIX (default, with FB_SCORE_PX2): k_tile_score_mix -- lists of >= FB_HEAVY_KEYS keys are swept in chained depth segments.
 #ifndef FB_SCORE_MIX
 #define FB_SCORE_MIX FB_SCORE_PX2
 #endif

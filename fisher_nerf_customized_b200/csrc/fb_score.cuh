@@ -20,6 +20,9 @@
 
 namespace fb {
 
+#ifndef FB_HESS_PFD
+#define FB_HESS_PFD 1  // the same for k_tile_hessian; 4 keyframes: 1 / 2 / 4 / 8 ahead -> 0.60 / 0.62 / 0.58 / 0.58 ms per H_train call, 16 keyframes: 1.52 / 1.57 / 1.61 / 1.89
+#endif
 #ifndef FB_S2_PFD
 #define FB_S2_PFD 1    // scan steps the record gather of the pair sweeps runs ahead of its use
 #endif
@@ -745,20 +748,28 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, C
     if (!__all_sync(0xffffffffu, done)) {
         int qn = 0, qh = 0;
         const int nsteps = (n + 31) >> 5;
-        bool v_nxt = lane < n;
-        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[lane] & 0xffffffffull) : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-        u64 key2 = (32 + lane < n) ? sorted[32 + lane] : 0ull;
+        // record gathers FB_HESS_PFD scan steps ahead of their use, keys one more (measured: no gain from more than one)
+        constexpr int D = FB_HESS_PFD;
+        bool vq[D]; unsigned gq[D]; float4 aq[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            vq[d] = d * 32 + lane < n;
+            gq[d] = vq[d] ? (unsigned)(sorted[d * 32 + lane] & 0xffffffffull) : 0u;
+            aq[d] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (vq[d]) aq[d] = __ldg(reinterpret_cast<const float4*>(recs + gq[d]));
+        }
+        u64 key2 = (D * 32 + lane < n) ? sorted[D * 32 + lane] : 0ull;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < n;
-                gid_nxt = (unsigned)(key2 & 0xffffffffull);
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-                key2 = ((step + 2) * 32 + lane < n) ? sorted[(step + 2) * 32 + lane] : 0ull;
+                const float4 a = aq[0];
+                const unsigned gid = gq[0];
+                const bool valid = vq[0];
+#pragma unroll
+                for (int d = 0; d + 1 < D; ++d) { vq[d] = vq[d + 1]; gq[d] = gq[d + 1]; aq[d] = aq[d + 1]; }
+                vq[D - 1] = (step + D) * 32 + lane < n;
+                gq[D - 1] = (unsigned)(key2 & 0xffffffffull);
+                if (vq[D - 1]) aq[D - 1] = __ldg(reinterpret_cast<const float4*>(recs + gq[D - 1]));
+                key2 = ((step + D + 1) * 32 + lane < n) ? sorted[(step + D + 1) * 32 + lane] : 0ull;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
@@ -809,20 +820,27 @@ __global__ void __launch_bounds__(32 * FB_SCORE_WPC) k_tile_hessian(Bins bins, C
     {
         int qn = 0, qh = 0;
         const int nsteps = (warp_last + 31) >> 5;
-        bool v_nxt = lane < warp_last;
-        unsigned gid_nxt = v_nxt ? (unsigned)(sorted[warp_last - 1 - lane] & 0xffffffffull) : 0u;
-        float4 a_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-        u64 key2 = (32 + lane < warp_last) ? sorted[warp_last - 1 - 32 - lane] : 0ull;
+        constexpr int D = FB_HESS_PFD;
+        bool vq[D]; unsigned gq[D]; float4 aq[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            vq[d] = d * 32 + lane < warp_last;
+            gq[d] = vq[d] ? (unsigned)(sorted[warp_last - 1 - d * 32 - lane] & 0xffffffffull) : 0u;
+            aq[d] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (vq[d]) aq[d] = __ldg(reinterpret_cast<const float4*>(recs + gq[d]));
+        }
+        u64 key2 = (D * 32 + lane < warp_last) ? sorted[warp_last - 1 - D * 32 - lane] : 0ull;
         for (int step = 0; step <= nsteps; ++step) {
             if (step < nsteps) {
-                const float4 a = a_nxt;
-                const unsigned gid = gid_nxt;
-                const bool valid = v_nxt;
-                v_nxt = (step + 1) * 32 + lane < warp_last;
-                gid_nxt = (unsigned)(key2 & 0xffffffffull);
-                if (v_nxt) a_nxt = __ldg(reinterpret_cast<const float4*>(recs + gid_nxt));
-                key2 = ((step + 2) * 32 + lane < warp_last) ? sorted[warp_last - 1 - (step + 2) * 32 - lane] : 0ull;
+                const float4 a = aq[0];
+                const unsigned gid = gq[0];
+                const bool valid = vq[0];
+#pragma unroll
+                for (int d = 0; d + 1 < D; ++d) { vq[d] = vq[d + 1]; gq[d] = gq[d + 1]; aq[d] = aq[d + 1]; }
+                vq[D - 1] = (step + D) * 32 + lane < warp_last;
+                gq[D - 1] = (unsigned)(key2 & 0xffffffffull);
+                if (vq[D - 1]) aq[D - 1] = __ldg(reinterpret_cast<const float4*>(recs + gq[D - 1]));
+                key2 = ((step + D + 1) * 32 + lane < warp_last) ? sorted[warp_last - 1 - (step + D + 1) * 32 - lane] : 0ull;
                 const bool hit = valid && (fabsf(a.x - cx) <= a.z + ex) && (fabsf(a.y - cy) <= a.w + ey);
                 const unsigned mask = __ballot_sync(0xffffffffu, hit);
                 if (hit) {

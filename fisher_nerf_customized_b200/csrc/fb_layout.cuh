@@ -43,6 +43,23 @@ static inline __host__ __device__ size_t seg_item_capacity(long long instances, 
     return (size_t)(instances / FB_SEG_KEYS + slots + 1);
 }
 
+// Work order of the sort / sweep kernels: tile slots by descending instance count inside a view, the views of a GROUP of
+// FB_ORDER_GROUP interleaved (rank-major inside the group), the groups one after the other.  A group of V views is the
+// plain interleave tile_order[rank * V + v]; smaller groups keep the records of fewer views in flight (L2).
+#ifndef FB_ORDER_GROUP
+#define FB_ORDER_GROUP 64
+#endif
+static inline __host__ __device__ unsigned order_index(unsigned rank, unsigned v, unsigned V, unsigned tiles) {
+    const unsigned g = v / FB_ORDER_GROUP, g0 = g * FB_ORDER_GROUP;
+    const unsigned gs = (V - g0 < FB_ORDER_GROUP) ? V - g0 : FB_ORDER_GROUP;
+    return g0 * tiles + rank * gs + (v - g0);
+}
+static inline __host__ __device__ unsigned order_rank(unsigned idx, unsigned V, unsigned tiles) {
+    const unsigned g0 = (idx / (FB_ORDER_GROUP * tiles)) * FB_ORDER_GROUP;
+    const unsigned gs = (V - g0 < FB_ORDER_GROUP) ? V - g0 : FB_ORDER_GROUP;
+    return (idx - g0 * tiles) / gs;
+}
+
 struct Bins {
     GRec*     recs;        // [V][P]   drop-in and H_train paths: indexed by Gaussian id
     float4*   recsB;       // unused by the kernels (the H_train path keeps its moment rows in that region)

@@ -698,7 +698,7 @@ __global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_score_mix(Bins bins, C
     }
     const int idx = (int)blockIdx.x - workers;
     const int tile_slot = (int)bins.tile_order[idx];
-    if (idx < FB_HEAVY_RANKS * bins.V) {
+    if (order_rank((unsigned)idx, (unsigned)bins.V, (unsigned)bins.tiles) < FB_HEAVY_RANKS) {
         const uint2 r = bins.tile_range[tile_slot];
         if ((int)(r.y - r.x) >= FB_HEAVY_KEYS) return;                     // its segments are work items
     }

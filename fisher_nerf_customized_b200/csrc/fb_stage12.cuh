@@ -566,7 +566,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(Bins bins) {
     for (int i = tid; i < n; i += 1024) {
         const unsigned c = tc[(size_t)i * FB_TC_STRIDE];
         const unsigned pos = atomicAdd(&bucket[1023u - (unsigned)(((u64)c * 1023ull) / maxc)], 1u);
-        bins.tile_order[(size_t)pos * V + v] = (unsigned)(v * n + i);
+        bins.tile_order[order_index(pos, (unsigned)v, (unsigned)V, (unsigned)n)] = (unsigned)(v * n + i);
         // a heavy list: ceil(c / FB_SEG_KEYS) segments, their state / output rows reserved consecutively
         if (bins.seg_list && pos < FB_HEAVY_RANKS && c >= FB_HEAVY_KEYS) {
             const unsigned S = (c + FB_SEG_KEYS - 1) / FB_SEG_KEYS;
@@ -969,6 +969,10 @@ __device__ __forceinline__ void sort_segment(u64* seg, u64* alt, const int n, co
 // `sub_ctas` CTAs of the grid wait until the first split_slots CTAs have reported (bins.total[9]) and sort the pieces
 // (keys_alt -> keys) in shared memory.  CTAs start in index order, so every CTA a waiting one depends on is resident
 // or done (the argument of the chained scan).
+#ifndef FB_SPLIT_RANKS
+#define FB_SPLIT_RANKS 64
+#endif
+#define FB_SPLIT_RANKS_ FB_SPLIT_RANKS
 #ifndef FB_SPLIT_MIN
 #define FB_SPLIT_MIN 16384
 #endif
@@ -1082,7 +1086,7 @@ __global__ void __launch_bounds__(FB_TILE_PIX, FB_SORT_MINB) k_sort_tiles(Bins b
     const unsigned slot = bins.tile_order ? bins.tile_order[lin] : lin;    // heaviest segments first
     const uint2 r = bins.tile_range[slot];
     const int n = (int)(r.y - r.x);
-    const bool reports = (int)lin < split_slots;
+    const bool reports = split_slots > 0 && order_rank(lin, (unsigned)bins.V, (unsigned)bins.tiles) < FB_SPLIT_RANKS_;
     if (reports && sort_is_split(n)) {
         split_segment(bins, bins.keys + r.x, keys_alt + r.x, n, r.x, slot / (unsigned)bins.tiles, reinterpret_cast<unsigned*>(s_keys), sh);
         __threadfence();

@@ -145,6 +145,8 @@ static Bins single_bins(int P, const Cam& cam, void* geom, void* image, void* in
 #define FB_SORT_SMEM_KEYS 1024
 #endif
 #define FB_SORT_SMEM_BYTES ((FB_SORT_STAGE ? 2 : 1) * FB_SORT_SMEM_KEYS * 8)
+static_assert(FB_SORT_SMEM_BYTES >= FB_SPLIT_FINE * 4, "split_segment keeps its 4096 bucket counters in the sort's dynamic shared memory");
+static_assert(FB_SPLIT_MAXJ <= (int)(sizeof(fb::SortShared::work) / 4), "the piece table of split_segment lives in SortShared::work");
 
 extern "C" {
 

@@ -561,6 +561,9 @@ struct SegWs {
     float4*   out;     // [items][4 blocks][2][32 lanes]   {Qaa0, Qaa1, Qab0, Qab1}, {Qbb0, Qbb1, Cf0, Cf1} (Cf = NaN unless the pixel's final state is here)
     unsigned* flag;    // [items][8]  0-3: state of the block published; 4-7: finished segments of the block, kept at the
 };                     //             list's first item (bins.seg_flags: zeroed by k_scan_tiles when it emits the item)
+#ifndef FB_SEG_SLEEP_NS
+#define FB_SEG_SLEEP_NS 100   // pause between two looks at the predecessor's flag
+#endif
 #define FB_SEG_WS_BYTES_PER_ITEM (4 * 32 * 16 + 4 * 64 * 16 + 16 + 16)
 
 template <int D>
@@ -605,7 +608,7 @@ __device__ __forceinline__ void sweep_px2_segment(const Bins& bins, const Cam& c
     const bool direct = have_in;                       // no pass 1: the state published is the exact one after pass 2
     if (!direct && !last && __any_sync(0xffffffffu, in0 || in1)) sweep_px2_core<D, 1>(recA, recB, sorted, n, bx, by, q2, P, stat);
     if (!have_in) {
-        if (lane == 0) { while (*prev_flag == 0u) __nanosleep(100); }
+        if (lane == 0) { while (*prev_flag == 0u) __nanosleep(FB_SEG_SLEEP_NS); }
         __syncwarp();
         __threadfence();
         const float4 st = __ldcg(ws.state + (me - 4) * 32 + lane);

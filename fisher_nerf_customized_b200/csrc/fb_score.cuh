@@ -561,6 +561,9 @@ struct SegWs {
     float4*   out;     // [items][4 blocks][2][32 lanes]   {Qaa0, Qaa1, Qab0, Qab1}, {Qbb0, Qbb1, Cf0, Cf1} (Cf = NaN unless the pixel's final state is here)
     unsigned* flag;    // [items][8]  0-3: state of the block published; 4-7: finished segments of the block, kept at the
 };                     //             list's first item (bins.seg_flags: zeroed by k_scan_tiles when it emits the item)
+#ifndef FB_SEG_AHEAD_WAVES
+#define FB_SEG_AHEAD_WAVES 100000   // pass 1 may run ahead of an unfinished predecessor only in the last so many waves of worker warps (100000: always)
+#endif
 #ifndef FB_SEG_SLEEP_NS
 #define FB_SEG_SLEEP_NS 100   // pause between two looks at the predecessor's flag
 #endif
@@ -569,7 +572,8 @@ struct SegWs {
 template <int D>
 __device__ __forceinline__ void sweep_px2_segment(const Bins& bins, const Cam& cam, float grad_scale, const SegWs& ws,
                                                   const int tile_slot, const int seg, const int S, const unsigned base,
-                                                  const int warp, WarpQ2& q2, float* __restrict__ partial) {
+                                                  const int warp, const bool may_run_ahead, WarpQ2& q2,
+                                                  float* __restrict__ partial) {
     const unsigned item = base + (unsigned)seg;
     const int t = tile_slot % bins.tiles, v = tile_slot / bins.tiles;
     const int lane = threadIdx.x & 31;
@@ -604,6 +608,16 @@ __device__ __forceinline__ void sweep_px2_segment(const Bins& bins, const Cam& c
             Tin = f2_pack(st.x, st.y); Cin = f2_pack(st.z, st.w);
             have_in = true;
         }
+    }
+    if (!have_in && !may_run_ahead) {
+        // plenty of other lists are waiting for a warp: pass 1 would spend issue slots they can use, so wait for the
+        // predecessor (picked a whole row of tickets earlier: nearly done) and sweep from its exact end state
+        if (lane == 0) { while (*prev_flag == 0u) __nanosleep(FB_SEG_SLEEP_NS); }
+        __syncwarp();
+        __threadfence();
+        const float4 st = __ldcg(ws.state + (me - 4) * 32 + lane);
+        Tin = f2_pack(st.x, st.y); Cin = f2_pack(st.z, st.w);
+        have_in = true;
     }
     const bool direct = have_in;                       // no pass 1: the state published is the exact one after pass 2
     if (!direct && !last && __any_sync(0xffffffffu, in0 || in1)) sweep_px2_core<D, 1>(recA, recB, sorted, n, bx, by, q2, P, stat);
@@ -695,6 +709,7 @@ __global__ void __launch_bounds__(128, FB_S2_MINB) k_tile_score_mix(Bins bins, C
             const uint4 it = bins.seg_list[r >> 2];                        // {tile slot, segments, first item, -}
             if (sgm < it.y)
                 sweep_px2_segment<FB_S2_PFD>(bins, cam, grad_scale, ws, (int)it.x, (int)sgm, (int)it.y, it.z, (int)(r & 3u),
+                                             tk + (unsigned)(FB_SEG_AHEAD_WAVES * 4 * workers) >= tickets,
                                              reinterpret_cast<WarpQ2*>(smem)[wq], partial);
             __syncwarp();
         }
